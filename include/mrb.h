@@ -1,0 +1,162 @@
+/*
+ * mrb.h -- C-ABI of mesh_reconstruction_b200 (libmrb.so).
+ *
+ * Drop-in boundary for the volumetric surface-extraction hot path of
+ * CRLab/Mesh_Reconstruction:  occupancy grid -> exact EDT -> narrow band ->
+ * bound-constrained smoothness QP (damped projected Jacobi) -> marching cubes
+ * with hash vertex de-duplication.  The reference has no FFI layer; its
+ * boundary is the C++ module API called from mesh_reconstruction.cpp:119-134.
+ * Every entry point below names the reference function it replaces.  The C++
+ * shim in compat/ re-creates the reference signatures (gridPtr etc.) on top of
+ * these symbols; INTEGRATION.md shows the binding.
+ *
+ * Conventions
+ *  - Grids are flat fp32 arrays in the reference's storage order
+ *    voxels[x][y][z] (z contiguous, grid.cpp:41-48): element (x,y,z) lives at
+ *    (x*dims[1] + y)*dims[2] + z.  dims = {nx, ny, nz}.
+ *  - "Linear indexes" handed across the API (findIndexes, getSurface) are the
+ *    reference's x-fastest index  z*nx*ny + y*nx + x  (grid.cpp:172-174).
+ *  - Every pointer argument may be a host pointer or a device pointer
+ *    (detected with cudaPointerGetAttributes); host buffers are staged through
+ *    the context's stream.  No entry point falls back to a CPU implementation:
+ *    without a usable GPU mrb_ctx_create fails.
+ *  - All functions return 0 on success, a negative MRB_E* code on failure;
+ *    mrb_last_error() returns the message of the calling thread's last failure.
+ *    (The reference prints and exit(1)s -- the compat shim reproduces that.)
+ *  - One mrb_ctx per host thread / per GPU; calls on one ctx are serialised on
+ *    its stream and are synchronous on return unless stated otherwise.
+ */
+#ifndef MRB_H
+#define MRB_H
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MRB_OK            0
+#define MRB_EINVAL       -1   /* bad argument */
+#define MRB_ECUDA        -2   /* CUDA runtime error */
+#define MRB_ENOMEM       -3   /* allocation failed */
+#define MRB_EBORDER      -4   /* band touches the grid border (reference: exit(1), grid.cpp:20-37) */
+#define MRB_ECAPACITY    -5   /* caller-provided buffer too small */
+#define MRB_EHASH        -6   /* vertex hash lookup failed (reference: mcubes.cpp:652-656) */
+
+typedef struct mrb_ctx mrb_ctx;
+
+/* Reference constants (quadprog.cu:237, primeqp.cpp:219, dfields.cpp:50). */
+#define MRB_BAND_SIZE_DEFAULT   4
+#define MRB_QP_ITERS_DEFAULT    500
+#define MRB_SQDIST_CLAMP        100000
+
+/* ---- context ---------------------------------------------------------- */
+/* Creates a context on CUDA device `device` (stream + grow-only scratch arena). */
+int  mrb_ctx_create(int device, mrb_ctx** out);
+void mrb_ctx_destroy(mrb_ctx* ctx);
+/* The CUDA stream (cudaStream_t) all work of this ctx is issued on. */
+void* mrb_ctx_stream(mrb_ctx* ctx);
+const char* mrb_last_error(void);
+/* Library build info: "mrb <version> sm_100a". */
+const char* mrb_version(void);
+/* Number of kernel launches issued by this ctx since creation (bench: gpu_launches). */
+uint64_t mrb_ctx_launch_count(mrb_ctx* ctx);
+
+/* ---- stage 1: distance field (distance_fields/) ------------------------ */
+/* fastPerim (dfields.cpp:7-37) / fastPerimGPU (dfields.cu:62-89):
+ * out = 1, or 0 if any voxel of the border-clamped 3x3x3 window differs from the centre. */
+int mrb_fast_perim(mrb_ctx* ctx, const float* volume, const int dims[3], float* out);
+/* getsqdist (dfields.cpp:41-99) / sqdistpt1-3 (dfields.cu:91-151):
+ * out = min(100000, exact squared Euclidean distance to the nearest voxel with in == 0). */
+int mrb_sqdist(mrb_ctx* ctx, const float* in, const int dims[3], float* out);
+/* getsqrt (dfields.cpp:182-192) / sqrtgpu (dfields.cu:153-159): correctly rounded sqrtf. */
+int mrb_sqrt(mrb_ctx* ctx, const float* in, const int dims[3], float* out);
+/* dfield_gpu (dfields.cu:161-200) == getsqrt(getsqdist(fastPerim(volume))). */
+int mrb_dfield(mrb_ctx* ctx, const float* volume, const int dims[3], float* margin);
+
+/* ---- stage 2: narrow band (narrow_band/, grid/) ------------------------ */
+/* erode_grid / dilate_grid (narrowBand.cpp:10-79): 6-neighbour, interior voxels only. */
+int mrb_erode(mrb_ctx* ctx, const float* in, const int dims[3], float* out);
+int mrb_dilate(mrb_ctx* ctx, const float* in, const int dims[3], float* out);
+/* createBands (narrowBand.cpp:82-102): band0 = margin<=band_size; tight = erode(band0);
+ * band = dilate(tight).  band/tight are 0/1 float grids. */
+int mrb_create_bands(mrb_ctx* ctx, const float* margin, const int dims[3], float band_size,
+                     float* band, float* tight);
+/* findIndexes (grid.cpp:350-371): non-zero voxels in (x,y,z)-lexicographic order, values are
+ * x-fastest linear indexes.  idx_out may be NULL (count only); otherwise capacity entries. */
+int mrb_find_indexes(mrb_ctx* ctx, const float* grid, const int dims[3],
+                     int* idx_out, int capacity, int* n_out);
+/* getIndexMap (grid.cpp:374-389): map = -1 everywhere, map(indexes[i]) = (float)i. */
+int mrb_index_map(mrb_ctx* ctx, const int dims[3], const int* indexes, int n, float* map_out);
+
+/* ---- stage 3: QP (optimize/) ------------------------------------------- */
+/* primeQP (primeqp.cpp:168-223) + getIr/getJc/getPr (quadprog.cpp:8-42).
+ * n must equal the band count.  Outputs (each may be NULL to skip):
+ *   lb, ub, x0, invdg : n floats;  jc : n+1 ints;  ir, pr : nnz_capacity entries;
+ *   *nnz_out = number of off-diagonal non-zeros of R = H - diag(H).
+ * Fails with MRB_EBORDER when a tight-band voxel lies on the grid border. */
+int mrb_prime_qp(mrb_ctx* ctx, const float* volume, const float* margin,
+                 const float* band, const float* tight, const int dims[3], int n,
+                 float* lb, float* ub, float* x0, float* invdg,
+                 int* jc, int* ir, float* pr, int nnz_capacity, int* nnz_out);
+/* runQP (quadprog.cpp:64-105) / runQPGPU (quadprog.cu:107-186): `iters` damped projected
+ * Jacobi sweeps on an explicit CSC matrix, then the reference's feature reset loop. */
+int mrb_run_qp(mrb_ctx* ctx, int n, const int* jc, const int* ir, const float* pr,
+               const float* invdg, const float* lb, const float* ub, const float* x0,
+               int iters, const int* feature_idx, int nfeat, int using_features,
+               float* x_out);
+
+typedef struct mrb_qp_stats {
+    int     n_band;          /* B: band voxels */
+    int     n_tight;         /* T: tight-band voxels */
+    int     iters;           /* sweeps executed */
+    float   last_max_delta;  /* max |x_new - x_old| over the band in the last sweep (warp-shuffle reduced) */
+    float   ms_dfield, ms_band, ms_qp, ms_mc;   /* device time per stage of the last fused call */
+} mrb_qp_stats;
+
+/* optimize (quadprog.cu:236-280): stages 1-3 device-resident; F = +-(band_size+1) off band,
+ * QP solution on the band.  feature_map may be NULL when !using_features.
+ * band_size / iters: reference constants are 4 / 500 (hard-coded there). */
+int mrb_optimize(mrb_ctx* ctx, const float* volume, const float* feature_map, const int dims[3],
+                 int using_features, int band_size, int iters, float* F_out, mrb_qp_stats* stats);
+
+/* ---- stage 4: marching cubes + hasher (marching_cubes/) ----------------- */
+typedef struct mrb_mesh {
+    float*  verts;     /* nverts * 3, grid coordinates (before getCloudPoint), first-appearance order */
+    int*    faces;     /* nfaces * 3 vertex ids, reference triangle order */
+    int     nverts;
+    int     nfaces;
+    int     on_device; /* 1: verts/faces are device pointers owned by the ctx arena (valid until next call) */
+} mrb_mesh;
+
+/* mcubes (mcubes.cpp:592-662) without the PLY write, default (non-feature) path:
+ * getGridCells + Polygonise + pointHashmap.  Result arrays are malloc'd host memory
+ * (release with mrb_mesh_free) unless device_out != 0. */
+int  mrb_mcubes(mrb_ctx* ctx, const float* F, const int dims[3], float isolevel,
+                int device_out, mrb_mesh* out);
+void mrb_mesh_free(mrb_mesh* mesh);
+/* hashXYZ (hasher.h:99-104) for n points (xyz interleaved); keys_out: n uint64. */
+int  mrb_hash_points(mrb_ctx* ctx, const float* xyz, int n, const int dims[3], uint64_t* keys_out);
+/* ASCII PLY exactly as mcubes.cpp:626-660 (vertices through grid::getCloudPoint, grid.cpp:204-210). */
+int  mrb_write_ply(const char* path, const float* verts, int nverts, const int* faces, int nfaces,
+                   const float scale[3], const float shift[3], int pad);
+
+/* ---- fused path --------------------------------------------------------- */
+typedef struct mrb_options {
+    int   using_features;     /* --feature-detection (0: default path) */
+    int   band_size;          /* 4 */
+    int   iters;              /* 500 */
+    float isolevel;           /* 0.0 (mesh_reconstruction.cpp:134) */
+    float feature_threshold;  /* 0.75 */
+    float corner_threshold;   /* 0.8 */
+} mrb_options;
+void mrb_options_default(mrb_options* o);
+/* optimize + mcubes with everything resident on the device between the stages. */
+int mrb_reconstruct(mrb_ctx* ctx, const float* volume, const int dims[3], const mrb_options* opt,
+                    int device_out, mrb_mesh* out, mrb_qp_stats* stats);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MRB_H */

@@ -1,0 +1,117 @@
+"""Synthetic occupancy grids for the BASELINE configs.
+
+All generators return float32 arrays of exactly 0.0 / 1.0 in the reference storage order
+[x][y][z], with the shape kept >= `pad` voxels away from every border (the reference pads
+its grids by 6 voxels, grid.cpp:91-114).
+"""
+import numpy as np
+
+
+def _coords(n):
+    if isinstance(n, int):
+        n = (n, n, n)
+    return np.meshgrid(*[np.arange(s, dtype=np.float32) for s in n], indexing="ij")
+
+
+def sphere(n, radius, center=None):
+    if isinstance(n, int):
+        n = (n, n, n)
+    if center is None:
+        center = [(s - 1) / 2.0 for s in n]
+    x, y, z = _coords(n)
+    d2 = (x - center[0]) ** 2 + (y - center[1]) ** 2 + (z - center[2]) ** 2
+    return (d2 <= radius * radius).astype(np.float32)
+
+
+def torus(n, R, r, center=None):
+    if isinstance(n, int):
+        n = (n, n, n)
+    if center is None:
+        center = [(s - 1) / 2.0 for s in n]
+    x, y, z = _coords(n)
+    q = np.sqrt((x - center[0]) ** 2 + (y - center[1]) ** 2) - R
+    return ((q * q + (z - center[2]) ** 2) <= r * r).astype(np.float32)
+
+
+def box(n, half, center=None, rot_z_deg=0.0, rot_x_deg=0.0):
+    if isinstance(n, int):
+        n = (n, n, n)
+    if center is None:
+        center = [(s - 1) / 2.0 for s in n]
+    x, y, z = _coords(n)
+    x = x - center[0]; y = y - center[1]; z = z - center[2]
+    a = np.deg2rad(rot_z_deg); b = np.deg2rad(rot_x_deg)
+    x1 = np.cos(a) * x + np.sin(a) * y
+    y1 = -np.sin(a) * x + np.cos(a) * y
+    y2 = np.cos(b) * y1 + np.sin(b) * z
+    z2 = -np.sin(b) * y1 + np.cos(b) * z
+    return ((np.abs(x1) <= half[0]) & (np.abs(y2) <= half[1]) & (np.abs(z2) <= half[2])).astype(np.float32)
+
+
+def ellipsoid(n, radii, center=None):
+    if isinstance(n, int):
+        n = (n, n, n)
+    if center is None:
+        center = [(s - 1) / 2.0 for s in n]
+    x, y, z = _coords(n)
+    q = ((x - center[0]) / radii[0]) ** 2 + ((y - center[1]) / radii[1]) ** 2 + ((z - center[2]) / radii[2]) ** 2
+    return (q <= 1.0).astype(np.float32)
+
+
+def union(*vols):
+    out = vols[0].copy()
+    for v in vols[1:]:
+        out = np.maximum(out, v)
+    return out
+
+
+def random_spheres(n, count, rmin, rmax, seed, pad=6):
+    """Union of `count` random spheres fully inside the padded interior (config 1)."""
+    rng = np.random.default_rng(seed)
+    if isinstance(n, int):
+        n = (n, n, n)
+    out = np.zeros(n, np.float32)
+    for _ in range(count):
+        r = rng.uniform(rmin, rmax)
+        c = [rng.uniform(pad + r + 1, s - pad - r - 2) for s in n]
+        out = np.maximum(out, sphere(n, r, c))
+    return out
+
+
+def random_object(seed, n=52, pad=6):
+    """Config 5: one random 40^3-class object (sphere, ellipsoid, box, torus or 2-sphere union)."""
+    rng = np.random.default_rng(seed)
+    kind = int(rng.integers(0, 5))
+    inner = n - 2 * pad
+    c = [(n - 1) / 2.0] * 3
+    if kind == 0:
+        return sphere(n, rng.uniform(8, inner / 2 - 2))
+    if kind == 1:
+        return ellipsoid(n, [rng.uniform(6, inner / 2 - 2) for _ in range(3)])
+    if kind == 2:
+        return box(n, [rng.uniform(5, inner / 2 - 8) for _ in range(3)], c, rng.uniform(0, 45), rng.uniform(0, 45))
+    if kind == 3:
+        r = rng.uniform(3, 5)
+        return torus(n, rng.uniform(8, inner / 2 - r - 2), r)
+    return random_spheres(n, 2, 6, 10, seed + 7, pad)
+
+
+def config_volume(cfg):
+    """The headline synthetic volume of BASELINE config `cfg` (1..4)."""
+    if cfg == 1:
+        return sphere(52, 17.0)
+    if cfg == 2:
+        return union(box(172, (50, 40, 30), None, 20.0, 35.0), sphere(172, 40.0))
+    if cfg == 3:
+        return sphere(256, 110.0)
+    if cfg == 4:
+        v = sphere(512, 220.0)
+        rng = np.random.default_rng(4)
+        for _ in range(8):
+            r = rng.uniform(20, 40)
+            u = rng.normal(size=3); u /= np.linalg.norm(u)
+            c = [255.5 + 215.0 * u[i] for i in range(3)]
+            c = [min(max(ci, 6 + r + 1), 512 - 6 - r - 2) for ci in c]
+            v = np.maximum(v, sphere(512, r, c))
+        return v
+    raise ValueError(cfg)
