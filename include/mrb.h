@@ -62,6 +62,9 @@ const char* mrb_last_error(void);
 const char* mrb_version(void);
 /* Number of kernel launches issued by this ctx since creation (bench: gpu_launches). */
 uint64_t mrb_ctx_launch_count(mrb_ctx* ctx);
+/* Utility: copies nbytes between any two host/device buffers on the ctx stream and waits
+ * (used by bindings to take device-resident results that live in the ctx arena). */
+int  mrb_copy(mrb_ctx* ctx, void* dst, const void* src, size_t nbytes);
 
 /* ---- stage 1: distance field (distance_fields/) ------------------------ */
 /* fastPerim (dfields.cpp:7-37) / fastPerimGPU (dfields.cu:62-89):

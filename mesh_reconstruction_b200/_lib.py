@@ -1,0 +1,81 @@
+"""ctypes loader for libmrb.so (the C-ABI declared in include/mrb.h).
+
+The library is built in-tree by `make -C mesh_reconstruction_b200/csrc` (or __graft_entry__.build()).
+There is no Python or CPU fallback: if the shared library is missing, or no GPU is usable,
+importing / creating a context raises.
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+SO_PATH = os.path.join(_HERE, "libmrb.so")
+
+c_float_p = C.POINTER(C.c_float)
+c_int_p = C.POINTER(C.c_int)
+
+
+class QPStats(C.Structure):
+    _fields_ = [("n_band", C.c_int), ("n_tight", C.c_int), ("iters", C.c_int), ("last_max_delta", C.c_float),
+                ("ms_dfield", C.c_float), ("ms_band", C.c_float), ("ms_qp", C.c_float), ("ms_mc", C.c_float)]
+
+
+class Mesh(C.Structure):
+    _fields_ = [("verts", c_float_p), ("faces", c_int_p), ("nverts", C.c_int), ("nfaces", C.c_int),
+                ("on_device", C.c_int)]
+
+
+class Options(C.Structure):
+    _fields_ = [("using_features", C.c_int), ("band_size", C.c_int), ("iters", C.c_int), ("isolevel", C.c_float),
+                ("feature_threshold", C.c_float), ("corner_threshold", C.c_float)]
+
+
+# every symbol include/mrb.h declares: name -> (restype, argtypes)
+_VP = C.c_void_p
+SYMBOLS = {
+    "mrb_ctx_create": (C.c_int, [C.c_int, C.POINTER(_VP)]),
+    "mrb_ctx_destroy": (None, [_VP]),
+    "mrb_ctx_stream": (_VP, [_VP]),
+    "mrb_last_error": (C.c_char_p, []),
+    "mrb_version": (C.c_char_p, []),
+    "mrb_ctx_launch_count": (C.c_uint64, [_VP]),
+    "mrb_copy": (C.c_int, [_VP, _VP, _VP, C.c_size_t]),
+    "mrb_fast_perim": (C.c_int, [_VP, _VP, c_int_p, _VP]),
+    "mrb_sqdist": (C.c_int, [_VP, _VP, c_int_p, _VP]),
+    "mrb_sqrt": (C.c_int, [_VP, _VP, c_int_p, _VP]),
+    "mrb_dfield": (C.c_int, [_VP, _VP, c_int_p, _VP]),
+    "mrb_erode": (C.c_int, [_VP, _VP, c_int_p, _VP]),
+    "mrb_dilate": (C.c_int, [_VP, _VP, c_int_p, _VP]),
+    "mrb_create_bands": (C.c_int, [_VP, _VP, c_int_p, C.c_float, _VP, _VP]),
+    "mrb_find_indexes": (C.c_int, [_VP, _VP, c_int_p, _VP, C.c_int, c_int_p]),
+    "mrb_index_map": (C.c_int, [_VP, c_int_p, _VP, C.c_int, _VP]),
+    "mrb_prime_qp": (C.c_int, [_VP, _VP, _VP, _VP, _VP, c_int_p, C.c_int, _VP, _VP, _VP, _VP, _VP, _VP, _VP,
+                               C.c_int, c_int_p]),
+    "mrb_run_qp": (C.c_int, [_VP, C.c_int, _VP, _VP, _VP, _VP, _VP, _VP, _VP, C.c_int, _VP, C.c_int, C.c_int, _VP]),
+    "mrb_optimize": (C.c_int, [_VP, _VP, _VP, c_int_p, C.c_int, C.c_int, C.c_int, _VP, C.POINTER(QPStats)]),
+    "mrb_mcubes": (C.c_int, [_VP, _VP, c_int_p, C.c_float, C.c_int, C.POINTER(Mesh)]),
+    "mrb_mesh_free": (None, [C.POINTER(Mesh)]),
+    "mrb_hash_points": (C.c_int, [_VP, _VP, C.c_int, c_int_p, _VP]),
+    "mrb_write_ply": (C.c_int, [C.c_char_p, _VP, C.c_int, _VP, C.c_int, c_float_p, c_float_p, C.c_int]),
+    "mrb_options_default": (None, [C.POINTER(Options)]),
+    "mrb_reconstruct": (C.c_int, [_VP, _VP, c_int_p, C.POINTER(Options), C.c_int, C.POINTER(Mesh),
+                                  C.POINTER(QPStats)]),
+}
+
+_lib = None
+
+
+def load():
+    """Loads libmrb.so and binds every declared symbol.  Raises if the library is not built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(SO_PATH):
+        raise ImportError("libmrb.so is not built (%s). Run `make -C mesh_reconstruction_b200/csrc` or "
+                          "__graft_entry__.build(); there is no CPU fallback." % SO_PATH)
+    lib = C.CDLL(SO_PATH)
+    for name, (res, args) in SYMBOLS.items():
+        fn = getattr(lib, name)      # AttributeError if the symbol is missing
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib

@@ -1,0 +1,166 @@
+// mrb_api.cu -- fused device-resident path: optimize (stages 1-3), reconstruct (stages 1-4), PLY writer.
+//
+// Replaces optimize (optimize/quadprog.cu:236-280 / quadprog.cpp:111-147) and the driver part of
+// mcubes (marching_cubes/mcubes.cpp:592-662).  The reference moves the grid host<->device around
+// every GPU stage and does perimeter->band->H assembly->F->marching cubes on the CPU even with
+// --cuda; here the occupancy grid is uploaded once and only the mesh comes back.
+#include "mrb_internal.cuh"
+
+#include <stdlib.h>
+#include <string.h>
+#include <string>
+
+namespace mrb {
+
+int export_mesh(mrb_ctx* ctx, float* verts_dev, int* faces_dev, int nverts, int nfaces, int device_out, mrb_mesh* out);
+
+// getFeatureIndexes (primeqp.cpp:231-244) + the reset loop of runQP (quadprog.cpp:92-101):
+// the sorted id list contains -1 for every feature voxel outside the band, and a single -1 blocks
+// all resets; otherwise every feature voxel of the band is set to 0.2.
+__global__ void k_feat_check(const float* __restrict__ fmap, const int* __restrict__ band_id, size_t n, int* __restrict__ any_off) {
+    for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < n; idx += (size_t)gridDim.x * blockDim.x)
+        if (fmap[idx] == 1.0f && band_id[idx] < 0) *any_off = 1;
+}
+__global__ void k_feat_apply(const float* __restrict__ fmap, const int* __restrict__ band_id, size_t n,
+                             const int* __restrict__ any_off, float* __restrict__ x) {
+    if (*any_off) return;
+    for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < n; idx += (size_t)gridDim.x * blockDim.x)
+        if (fmap[idx] == 1.0f) x[band_id[idx]] = 0.2f;
+}
+
+// Stages 1-3 on device pointers.  F_dev: N^3 floats.
+static int optimize_dev(mrb_ctx* ctx, const float* vol, const float* fmap, Dims d, int using_features, int band_size,
+                        int iters, float* F_dev, mrb_qp_stats* stats) {
+    const size_t n = d.count();
+    MRB_CUDA(cudaEventRecord(ctx->ev[0], ctx->stream));
+    float* margin = nullptr;
+    MRB_TRY(arena_alloc(ctx, n, &margin));
+    MRB_TRY(dev_dfield(ctx, vol, d, margin));
+    MRB_CUDA(cudaEventRecord(ctx->ev[1], ctx->stream));
+    float *b0 = nullptr, *tight = nullptr, *band = nullptr;
+    MRB_TRY(arena_alloc(ctx, n, &b0));
+    MRB_TRY(arena_alloc(ctx, n, &tight));
+    band = F_dev;   // F is written last; reuse it for the band grid until then
+    MRB_TRY(dev_threshold(ctx, margin, n, (float)band_size, b0));
+    MRB_TRY(dev_erode(ctx, b0, d, tight));
+    MRB_TRY(dev_dilate(ctx, tight, d, band));
+    BandDev bd;
+    MRB_TRY(dev_qp_build(ctx, vol, margin, band, tight, d, &bd));
+    MRB_CUDA(cudaEventRecord(ctx->ev[2], ctx->stream));
+    float* x = nullptr;
+    MRB_TRY(arena_alloc(ctx, (size_t)(bd.n_band > 0 ? bd.n_band : 1), &x));
+    float last_delta = 0.0f;
+    MRB_TRY(dev_qp_solve(ctx, bd, d, band_size, iters, x, stats ? &last_delta : nullptr));
+    if (using_features && fmap && bd.n_band > 0) {
+        int* flag = ctx->d_mail + 16;
+        MRB_CUDA(cudaMemsetAsync(flag, 0, sizeof(int), ctx->stream));
+        size_t want = (n + 255) / 256, cap = (size_t)ctx->sm_count * 16;
+        unsigned g = (unsigned)(want < cap ? want : cap);
+        MRB_LAUNCH(ctx, k_feat_check, g, 256, 0, fmap, bd.band_id, n, flag);
+        MRB_LAUNCH(ctx, k_feat_apply, g, 256, 0, fmap, bd.band_id, n, flag, x);
+    }
+    MRB_TRY(dev_assemble_F(ctx, vol, bd, x, d, band_size, F_dev));
+    MRB_CUDA(cudaEventRecord(ctx->ev[3], ctx->stream));
+    if (stats) {
+        MRB_CUDA(cudaEventSynchronize(ctx->ev[3]));
+        stats->n_band = bd.n_band;
+        stats->n_tight = bd.n_tight;
+        stats->iters = iters;
+        stats->last_max_delta = last_delta;
+        cudaEventElapsedTime(&stats->ms_dfield, ctx->ev[0], ctx->ev[1]);
+        cudaEventElapsedTime(&stats->ms_band, ctx->ev[1], ctx->ev[2]);
+        cudaEventElapsedTime(&stats->ms_qp, ctx->ev[2], ctx->ev[3]);
+        stats->ms_mc = 0.0f;
+    }
+    return MRB_OK;
+}
+
+}  // namespace mrb
+
+using namespace mrb;
+
+extern "C" {
+
+int mrb_optimize(mrb_ctx* ctx, const float* volume, const float* feature_map, const int dims[3], int using_features,
+                 int band_size, int iters, float* F_out, mrb_qp_stats* stats) {
+    MRB_REQUIRE(ctx && volume && dims && F_out, "NULL argument");
+    MRB_REQUIRE(band_size >= 1 && band_size <= 64 && iters >= 0, "bad band_size / iters");
+    MRB_REQUIRE(!using_features || feature_map, "using_features needs a feature map");
+    MRB_CUDA(cudaSetDevice(ctx->device));
+    MRB_TRY(ctx->arena.reset());
+    Dims d = mkdims(dims);
+    MRB_REQUIRE(d.count() <= (size_t)0x7fffffff, "grid too large");
+    const float *dv = nullptr, *df = nullptr;
+    MRB_TRY(stage_in(ctx, volume, d.count(), &dv));
+    if (using_features) MRB_TRY(stage_in(ctx, feature_map, d.count(), &df));
+    Out<float> oF;
+    MRB_TRY(oF.init(ctx, F_out, d.count()));
+    MRB_TRY(optimize_dev(ctx, dv, df, d, using_features, band_size, iters, oF.dev, stats));
+    MRB_TRY(oF.commit(ctx));
+    return sync(ctx);
+}
+
+int mrb_reconstruct(mrb_ctx* ctx, const float* volume, const int dims[3], const mrb_options* opt, int device_out,
+                    mrb_mesh* out, mrb_qp_stats* stats) {
+    MRB_REQUIRE(ctx && volume && dims && out, "NULL argument");
+    mrb_options o;
+    if (opt) o = *opt; else mrb_options_default(&o);
+    MRB_REQUIRE(o.band_size >= 1 && o.band_size <= 64 && o.iters >= 0, "bad band_size / iters");
+    if (o.using_features) {
+        set_error("mrb_reconstruct: the --feature-detection path (getSurfaceNormals/getFeatureMap/feature MC) "
+                  "is not implemented on the GPU yet");
+        return MRB_EINVAL;
+    }
+    MRB_CUDA(cudaSetDevice(ctx->device));
+    MRB_TRY(ctx->arena.reset());
+    memset(out, 0, sizeof(*out));
+    Dims d = mkdims(dims);
+    MRB_REQUIRE(d.count() <= (size_t)0x7fffffff, "grid too large");
+    const float* dv = nullptr;
+    MRB_TRY(stage_in(ctx, volume, d.count(), &dv));
+    float* F = nullptr;
+    MRB_TRY(arena_alloc(ctx, d.count(), &F));
+    MRB_TRY(optimize_dev(ctx, dv, nullptr, d, 0, o.band_size, o.iters, F, stats));
+    MRB_CUDA(cudaEventRecord(ctx->ev[4], ctx->stream));
+    float* verts = nullptr;
+    int* faces = nullptr;
+    int nv = 0, nf = 0;
+    MRB_TRY(dev_mcubes(ctx, F, d, o.isolevel, &verts, &faces, &nv, &nf));
+    MRB_CUDA(cudaEventRecord(ctx->ev[5], ctx->stream));
+    MRB_TRY(export_mesh(ctx, verts, faces, nv, nf, device_out, out));
+    if (stats) cudaEventElapsedTime(&stats->ms_mc, ctx->ev[4], ctx->ev[5]);
+    return MRB_OK;
+}
+
+// ASCII PLY, mcubes.cpp:626-660.  "%g" == default ostream float formatting (6 significant digits).
+int mrb_write_ply(const char* path, const float* verts, int nverts, const int* faces, int nfaces, const float scale[3],
+                  const float shift[3], int pad) {
+    if (!path || (nverts > 0 && !verts) || (nfaces > 0 && !faces) || !scale || !shift) { set_error("mrb_write_ply: NULL argument"); return MRB_EINVAL; }
+    FILE* f = fopen(path, "w");
+    if (!f) { set_error("mrb_write_ply: cannot open %s", path); return MRB_EINVAL; }
+    std::string buf;
+    buf.reserve(1 << 20);
+    char line[160];
+    int len = snprintf(line, sizeof(line),
+                       "ply\nformat ascii 1.0\nelement vertex %d\nproperty float x\nproperty float y\nproperty float z\n"
+                       "element face %d\nproperty list uchar int vertex_indices\nend_header\n", nverts, nfaces);
+    buf.append(line, len);
+    for (int i = 0; i < nverts; i++) {
+        float p[3];
+        // grid::getCloudPoint, grid.cpp:204-210
+        for (int a = 0; a < 3; a++) p[a] = ((verts[3 * (size_t)i + a] - (float)pad) * scale[a]) + shift[a];
+        len = snprintf(line, sizeof(line), "%g %g %g\n", p[0], p[1], p[2]);
+        buf.append(line, len);
+        if (buf.size() > (1 << 20) - 256) { fwrite(buf.data(), 1, buf.size(), f); buf.clear(); }
+    }
+    for (int i = 0; i < nfaces; i++) {
+        len = snprintf(line, sizeof(line), "3 %d %d %d\n", faces[3 * (size_t)i], faces[3 * (size_t)i + 1], faces[3 * (size_t)i + 2]);
+        buf.append(line, len);
+        if (buf.size() > (1 << 20) - 256) { fwrite(buf.data(), 1, buf.size(), f); buf.clear(); }
+    }
+    fwrite(buf.data(), 1, buf.size(), f);
+    fclose(f);
+    return MRB_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,262 @@
+// mrb_ctx.cu -- context, device arena, error reporting, device-wide scan.
+#include "mrb_internal.cuh"
+
+#include <stdarg.h>
+#include <string.h>
+
+namespace mrb {
+
+static thread_local char g_err[1024] = "";
+
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+bool is_device_ptr(const void* p) {
+    cudaPointerAttributes a;
+    cudaError_t e = cudaPointerGetAttributes(&a, p);
+    if (e != cudaSuccess) { cudaGetLastError(); return false; }
+    return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
+}
+
+// ---- arena ----------------------------------------------------------------------------------
+static const size_t kAlign = 256;
+
+int Arena::alloc(size_t bytes, void** out) {
+    bytes = (bytes + kAlign - 1) / kAlign * kAlign;
+    if (bytes == 0) bytes = kAlign;
+    high_water += bytes;
+    if (!blocks.empty()) {
+        Block& b = blocks.back();
+        if (b.used + bytes <= b.cap) {
+            *out = b.base + b.used;
+            b.used += bytes;
+            return MRB_OK;
+        }
+    }
+    size_t cap = bytes;
+    size_t prev = blocks.empty() ? 0 : blocks.back().cap;
+    if (cap < prev) cap = prev;                 // grow geometrically-ish
+    if (cap < (size_t)(16u << 20)) cap = 16u << 20;
+    char* base = nullptr;
+    cudaError_t e = cudaMalloc((void**)&base, cap);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        set_error("arena: cudaMalloc(%zu) failed: %s", cap, cudaGetErrorString(e));
+        return MRB_ENOMEM;
+    }
+    blocks.push_back(Block{base, cap, bytes});
+    *out = base;
+    return MRB_OK;
+}
+
+int Arena::reset() {
+    if (blocks.size() > 1) {
+        // Consolidate: the previous call needed several blocks; replace them by one big block so
+        // that steady-state calls allocate nothing.
+        size_t need = high_water + (high_water >> 3);
+        for (auto& b : blocks) cudaFree(b.base);
+        blocks.clear();
+        char* base = nullptr;
+        cudaError_t e = cudaMalloc((void**)&base, need);
+        if (e != cudaSuccess) {
+            cudaGetLastError();
+            set_error("arena: consolidate cudaMalloc(%zu) failed: %s", need, cudaGetErrorString(e));
+            return MRB_ENOMEM;
+        }
+        blocks.push_back(Block{base, need, 0});
+    }
+    for (auto& b : blocks) b.used = 0;
+    high_water = 0;
+    return MRB_OK;
+}
+
+void Arena::release() {
+    for (auto& b : blocks) cudaFree(b.base);
+    blocks.clear();
+}
+
+int read_int(mrb_ctx* ctx, const int* dev, int* host) {
+    MRB_CUDA(cudaMemcpyAsync(ctx->h_mail, dev, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    MRB_CUDA(cudaStreamSynchronize(ctx->stream));
+    *host = ctx->h_mail[0];
+    return MRB_OK;
+}
+
+// ---- exclusive scan ---------------------------------------------------------------------------
+// Three small kernels: per-block reduce, single-block scan of the partials, per-block downsweep.
+// Block = 256 threads x 8 items = 2048 items.
+static const int kScanThreads = 256;
+static const int kScanItems = 8;
+static const int kScanTile = kScanThreads * kScanItems;
+
+__device__ __forceinline__ int warp_incl_scan(int v) {
+    const int lane = threadIdx.x & 31;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        int t = __shfl_up_sync(0xffffffffu, v, o);
+        if (lane >= o) v += t;
+    }
+    return v;
+}
+
+// Block-wide exclusive scan of one value per thread (blockDim.x <= 1024); returns the exclusive
+// prefix, *total receives the block sum.
+__device__ __forceinline__ int block_excl_scan(int v, int* total) {
+    __shared__ int wsum[32];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    int incl = warp_incl_scan(v);
+    if (lane == 31) wsum[wid] = incl;
+    __syncthreads();
+    if (wid == 0) {
+        int nw = (blockDim.x + 31) >> 5;
+        int s = lane < nw ? wsum[lane] : 0;
+        int si = warp_incl_scan(s);
+        wsum[lane] = si - s;
+        if (lane == nw - 1) *total = si;
+    }
+    __syncthreads();
+    int res = incl - v + wsum[wid];
+    __syncthreads();
+    return res;
+}
+
+__global__ void k_scan_reduce(const int* __restrict__ in, int* __restrict__ partial, size_t n) {
+    size_t base = (size_t)blockIdx.x * kScanTile;
+    int s = 0;
+#pragma unroll
+    for (int i = 0; i < kScanItems; i++) {
+        size_t idx = base + (size_t)i * kScanThreads + threadIdx.x;
+        if (idx < n) s += in[idx];
+    }
+    __shared__ int tot;
+    block_excl_scan(s, &tot);
+    if (threadIdx.x == 0) partial[blockIdx.x] = tot;
+}
+
+__global__ void k_scan_partials(int* __restrict__ partial, int nblocks, int* __restrict__ total_out) {
+    __shared__ int tot;
+    __shared__ int carry_s;
+    if (threadIdx.x == 0) carry_s = 0;
+    __syncthreads();
+    for (int base = 0; base < nblocks; base += blockDim.x) {
+        int idx = base + threadIdx.x;
+        int v = idx < nblocks ? partial[idx] : 0;
+        int ex = block_excl_scan(v, &tot);
+        int carry = carry_s;
+        if (idx < nblocks) partial[idx] = ex + carry;
+        __syncthreads();
+        if (threadIdx.x == 0) carry_s = carry + tot;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0 && total_out) *total_out = carry_s;
+}
+
+__global__ void k_scan_down(const int* __restrict__ in, int* __restrict__ out, const int* __restrict__ partial,
+                            size_t n) {
+    // items are laid out blocked per thread so the per-thread running sum is sequential in index
+    size_t base = (size_t)blockIdx.x * kScanTile + (size_t)threadIdx.x * kScanItems;
+    int v[kScanItems];
+    int s = 0;
+#pragma unroll
+    for (int i = 0; i < kScanItems; i++) {
+        size_t idx = base + i;
+        v[i] = idx < n ? in[idx] : 0;
+        s += v[i];
+    }
+    __shared__ int tot;
+    int ex = block_excl_scan(s, &tot) + partial[blockIdx.x];
+#pragma unroll
+    for (int i = 0; i < kScanItems; i++) {
+        size_t idx = base + i;
+        if (idx < n) out[idx] = ex;
+        ex += v[i];
+    }
+}
+
+int scan_exclusive(mrb_ctx* ctx, const int* in, int* out, size_t n, int* total_dev) {
+    if (n == 0) {
+        if (total_dev) MRB_CUDA(cudaMemsetAsync(total_dev, 0, sizeof(int), ctx->stream));
+        return MRB_OK;
+    }
+    unsigned nblocks = cdiv(n, kScanTile);
+    int* partial = nullptr;
+    MRB_TRY(arena_alloc(ctx, nblocks, &partial));
+    MRB_LAUNCH(ctx, k_scan_reduce, nblocks, kScanThreads, 0, in, partial, n);
+    MRB_LAUNCH(ctx, k_scan_partials, 1, 1024, 0, partial, (int)nblocks, total_dev);
+    MRB_LAUNCH(ctx, k_scan_down, nblocks, kScanThreads, 0, in, out, partial, n);
+    return MRB_OK;
+}
+
+}  // namespace mrb
+
+// ---- C-ABI: context ---------------------------------------------------------------------------
+extern "C" {
+
+const char* mrb_last_error(void) { return mrb::g_err; }
+const char* mrb_version(void) { return "mrb 0.1 sm_100a"; }
+
+int mrb_ctx_create(int device, mrb_ctx** out) {
+    if (!out) { mrb::set_error("mrb_ctx_create: out is NULL"); return MRB_EINVAL; }
+    *out = nullptr;
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        mrb::set_error("mrb_ctx_create: no CUDA device available (%s); libmrb has no CPU fallback",
+                       e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
+        return MRB_ECUDA;
+    }
+    if (device < 0 || device >= ndev) { mrb::set_error("mrb_ctx_create: bad device %d", device); return MRB_EINVAL; }
+    MRB_CUDA(cudaSetDevice(device));
+    mrb_ctx* c = new mrb_ctx();
+    c->device = device;
+    cudaDeviceProp prop;
+    MRB_CUDA(cudaGetDeviceProperties(&prop, device));
+    c->sm_count = prop.multiProcessorCount;
+    MRB_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    for (int i = 0; i < 6; i++) MRB_CUDA(cudaEventCreate(&c->ev[i]));
+    MRB_CUDA(cudaMallocHost((void**)&c->h_mail, 64 * sizeof(int)));
+    MRB_CUDA(cudaMalloc((void**)&c->d_mail, 64 * sizeof(int)));
+    *out = c;
+    return MRB_OK;
+}
+
+void mrb_ctx_destroy(mrb_ctx* ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    ctx->arena.release();
+    for (int i = 0; i < 6; i++) if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
+    if (ctx->h_mail) cudaFreeHost(ctx->h_mail);
+    if (ctx->d_mail) cudaFree(ctx->d_mail);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+void* mrb_ctx_stream(mrb_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
+uint64_t mrb_ctx_launch_count(mrb_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+int mrb_copy(mrb_ctx* ctx, void* dst, const void* src, size_t nbytes) {
+    if (!ctx || (nbytes && (!dst || !src))) { mrb::set_error("mrb_copy: NULL argument"); return MRB_EINVAL; }
+    if (nbytes == 0) return MRB_OK;
+    MRB_CUDA(cudaSetDevice(ctx->device));
+    MRB_CUDA(cudaMemcpyAsync(dst, src, nbytes, cudaMemcpyDefault, ctx->stream));
+    MRB_CUDA(cudaStreamSynchronize(ctx->stream));
+    return MRB_OK;
+}
+
+void mrb_options_default(mrb_options* o) {
+    if (!o) return;
+    o->using_features = 0;
+    o->band_size = MRB_BAND_SIZE_DEFAULT;
+    o->iters = MRB_QP_ITERS_DEFAULT;
+    o->isolevel = 0.0f;
+    o->feature_threshold = 0.75f;
+    o->corner_threshold = 0.8f;
+}
+
+}  // extern "C"

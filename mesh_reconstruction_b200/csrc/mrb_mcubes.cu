@@ -1,0 +1,353 @@
+// mrb_mcubes.cu -- stage 4: marching cubes with hasher-equivalent vertex de-duplication.
+//
+// Replaces getGridCells / Polygonise / getSamplePoints / VertexInterp (marching_cubes/mcubes.cpp:
+// 157-392) and pointHashmap (hasher.h:84-106, hasher.cpp:10-32) for the default (non-feature) path.
+//
+// The reference materialises one ~200-byte GRIDCELL per cell and walks them sequentially.  Here:
+//   1. classify   one thread per cell (lanes along z): cube index from the 8 corner values;
+//                 surface-crossing cells are compacted in (i,j,k) order (ballot + scan);
+//   2. count      per crossing cell: interpolated edge vertices, triangles of the case table,
+//                 degenerate-triangle filter (any side < 1e-5)  -> triangle count; exclusive scan;
+//   3. emit       triangle corners (xyz) and their 64-bit hashXYZ keys at the scanned offsets:
+//                 the triangle soup is in exactly the reference's concatenation order;
+//   4. de-dup     open-addressing hash table on the 64-bit key, value = atomicMin(first position);
+//                 a corner is a "first appearance" iff it holds the minimum position of its key;
+//                 exclusive scan of those flags = the reference's vertex ids (first-appearance
+//                 order), coordinates of the first occurrence are kept (hasher.cpp:13-23).
+// Everything order-defining is a scan or a min, so the result is deterministic and identical to the
+// sequential reference regardless of thread scheduling.
+#include "mrb_internal.cuh"
+#include "mrb_compact.cuh"
+#include "mc_tables.h"
+
+#include <stdlib.h>
+#include <string.h>
+
+namespace mrb {
+
+__constant__ uint64_t c_tri[256] = MRB_MC_TRI_WORDS;
+// edge e joins corners kEdgeA[e], kEdgeB[e] (mcubes.cpp:317-364)
+__constant__ int c_edge_a[12] = {0, 1, 2, 3, 4, 5, 6, 7, 0, 1, 2, 3};
+__constant__ int c_edge_b[12] = {1, 2, 3, 0, 5, 6, 7, 4, 4, 5, 6, 7};
+
+struct CellDims {
+    int nx, ny, nz;      // grid dims
+    int cx, cy, cz;      // cell dims = grid dims - 1
+};
+
+// corner n of cell (i,j,k): (i + [n%4 in {1,2}], j + (n%4)/2, k + n/4)  (mcubes.cpp:166-168)
+__device__ __forceinline__ void cell_corner_values(const float* __restrict__ F, const CellDims& cd, int i, int j, int k,
+                                                   float v[8]) {
+    const size_t sx = (size_t)cd.ny * cd.nz, sy = cd.nz;
+    const float* p = F + ((size_t)i * cd.ny + j) * cd.nz + k;
+    v[0] = __ldg(p);
+    v[1] = __ldg(p + sx);
+    v[2] = __ldg(p + sx + sy);
+    v[3] = __ldg(p + sy);
+    v[4] = __ldg(p + 1);
+    v[5] = __ldg(p + sx + 1);
+    v[6] = __ldg(p + sx + sy + 1);
+    v[7] = __ldg(p + sy + 1);
+}
+
+__device__ __forceinline__ int cube_index(const float v[8], float iso) {
+    int c = 0;
+#pragma unroll
+    for (int n = 0; n < 8; n++) c |= (v[n] < iso) ? (1 << n) : 0;
+    return c;
+}
+
+struct ActiveCellPred {
+    const float* F;
+    CellDims cd;
+    float iso;
+    __device__ bool operator()(size_t cell) const {
+        int k = (int)(cell % cd.cz);
+        size_t t = cell / cd.cz;
+        int j = (int)(t % cd.cy);
+        int i = (int)(t / cd.cy);
+        float v[8];
+        cell_corner_values(F, cd, i, j, k, v);
+        int c = cube_index(v, iso);
+        return c != 0 && c != 255;     // edgeTable[c] != 0
+    }
+};
+
+struct F3 { float x, y, z; };
+
+__device__ __forceinline__ bool lex_less(const F3& a, const F3& b) {   // XYZ::operator<, hasher.h:41-58
+    if (a.x < b.x) return true; else if (a.x > b.x) return false;
+    if (a.y < b.y) return true; else if (a.y > b.y) return false;
+    if (a.z < b.z) return true;
+    return false;
+}
+
+// VertexInterp, mcubes.cpp:369-392 (fp32, IEEE division, no contraction).
+__device__ __forceinline__ F3 vertex_interp(float iso, F3 p1, F3 p2, float v1, float v2) {
+    if (lex_less(p2, p1)) { F3 t = p1; p1 = p2; p2 = t; float tv = v1; v1 = v2; v2 = tv; }
+    F3 p;
+    if ((double)fabsf(__fsub_rn(v1, v2)) > 0.00001) {
+        float den = __fsub_rn(v2, v1), num = __fsub_rn(iso, v1);
+        p.x = __fadd_rn(p1.x, __fmul_rn(__fdiv_rn(__fsub_rn(p2.x, p1.x), den), num));
+        p.y = __fadd_rn(p1.y, __fmul_rn(__fdiv_rn(__fsub_rn(p2.y, p1.y), den), num));
+        p.z = __fadd_rn(p1.z, __fmul_rn(__fdiv_rn(__fsub_rn(p2.z, p1.z), den), num));
+    } else {
+        p = p1;
+    }
+    return p;
+}
+
+// XYZ::dist < 0.00001, hasher.h:28-33 / mcubes.cpp:227-229
+__device__ __forceinline__ bool too_close(const F3& l, const F3& r) {
+    float dx = __fsub_rn(r.x, l.x), dy = __fsub_rn(r.y, l.y), dz = __fsub_rn(r.z, l.z);
+    float d = __fmul_rn(dx, dx);
+    d = __fadd_rn(d, __fmul_rn(dy, dy));
+    d = __fadd_rn(d, __fmul_rn(dz, dz));
+    return (double)__fsqrt_rn(d) < 0.00001;
+}
+
+// pointHashmap::hashXYZ, hasher.h:99-104
+__device__ __forceinline__ unsigned long long hash_xyz(const F3& s, int ny, int nz) {
+    unsigned long long val = (unsigned long long)__dmul_rn(__dmul_rn((double)s.x, 1000000000.0), (double)(ny * nz));
+    val += (unsigned long long)__dmul_rn(__dmul_rn((double)s.y, 1000000.0), (double)nz);
+    val += (unsigned long long)__dmul_rn((double)s.z, 1000.0);
+    return val;
+}
+
+// Polygonise (mcubes.cpp:194-232) for one crossing cell.  Emit == false: returns the triangle count only.
+template <bool Emit>
+__device__ __forceinline__ int polygonise(const float* __restrict__ F, const CellDims& cd, int cell, float iso,
+                                          float* __restrict__ soup, unsigned long long* __restrict__ keys, int first_tri) {
+    int k = cell % cd.cz;
+    int t = cell / cd.cz;
+    int j = t % cd.cy;
+    int i = t / cd.cy;
+    float v[8];
+    cell_corner_values(F, cd, i, j, k, v);
+    int ci = cube_index(v, iso);
+    uint64_t w = c_tri[ci];
+    int ntri = (int)(w & 15);
+    F3 vert[12];
+#pragma unroll
+    for (int e = 0; e < 12; e++) {
+        int a = c_edge_a[e], b = c_edge_b[e];
+        if (((ci >> a) & 1) != ((ci >> b) & 1)) {
+            F3 pa = {(float)(i + (((a & 3) == 1) || ((a & 3) == 2))), (float)(j + ((a & 3) >> 1)), (float)(k + (a >> 2))};
+            F3 pb = {(float)(i + (((b & 3) == 1) || ((b & 3) == 2))), (float)(j + ((b & 3) >> 1)), (float)(k + (b >> 2))};
+            vert[e] = vertex_interp(iso, pa, pb, v[a], v[b]);
+        } else {
+            vert[e] = F3{-1.0f, -1.0f, -1.0f};
+        }
+    }
+    int out = 0;
+    for (int q = 0; q < ntri; q++) {
+        F3 a = vert[(w >> (4 + 12 * q)) & 15];
+        F3 b = vert[(w >> (8 + 12 * q)) & 15];
+        F3 c = vert[(w >> (12 + 12 * q)) & 15];
+        if (too_close(a, b)) continue;
+        if (too_close(b, c)) continue;
+        if (too_close(c, a)) continue;
+        if (Emit) {
+            size_t o = (size_t)(first_tri + out) * 9;
+            soup[o + 0] = a.x; soup[o + 1] = a.y; soup[o + 2] = a.z;
+            soup[o + 3] = b.x; soup[o + 4] = b.y; soup[o + 5] = b.z;
+            soup[o + 6] = c.x; soup[o + 7] = c.y; soup[o + 8] = c.z;
+            size_t kq = (size_t)(first_tri + out) * 3;
+            keys[kq + 0] = hash_xyz(a, cd.ny, cd.nz);
+            keys[kq + 1] = hash_xyz(b, cd.ny, cd.nz);
+            keys[kq + 2] = hash_xyz(c, cd.ny, cd.nz);
+        }
+        out++;
+    }
+    return out;
+}
+
+__global__ void __launch_bounds__(128) k_mc_count(const float* __restrict__ F, CellDims cd, const int* __restrict__ cells,
+                                                  int ncells, float iso, int* __restrict__ ntri) {
+    int a = blockIdx.x * blockDim.x + threadIdx.x;
+    if (a >= ncells) return;
+    ntri[a] = polygonise<false>(F, cd, cells[a], iso, nullptr, nullptr, 0);
+}
+
+__global__ void __launch_bounds__(128) k_mc_emit(const float* __restrict__ F, CellDims cd, const int* __restrict__ cells,
+                                                 int ncells, float iso, const int* __restrict__ tri_off,
+                                                 float* __restrict__ soup, unsigned long long* __restrict__ keys) {
+    int a = blockIdx.x * blockDim.x + threadIdx.x;
+    if (a >= ncells) return;
+    polygonise<true>(F, cd, cells[a], iso, soup, keys, tri_off[a]);
+}
+
+// ---- hash de-duplication ------------------------------------------------------------------------------
+static const unsigned long long kEmptyKey = 0xffffffffffffffffull;
+
+__device__ __forceinline__ uint32_t mix64(unsigned long long k) {
+    k ^= k >> 33; k *= 0xff51afd7ed558ccdull; k ^= k >> 33; k *= 0xc4ceb9fe1a85ec53ull; k ^= k >> 33;
+    return (uint32_t)k;
+}
+
+__global__ void k_hash_clear(unsigned long long* __restrict__ tkeys, int* __restrict__ tfirst, size_t cap) {
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < cap; i += (size_t)gridDim.x * blockDim.x) {
+        tkeys[i] = kEmptyKey;
+        tfirst[i] = 0x7fffffff;
+    }
+}
+
+__global__ void k_hash_insert(const unsigned long long* __restrict__ keys, int ncorner, unsigned long long* tkeys,
+                              int* tfirst, uint32_t mask, int* __restrict__ slot_of) {
+    int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= ncorner) return;
+    unsigned long long key = keys[p];
+    uint32_t s = mix64(key) & mask;
+    while (true) {
+        unsigned long long prev = atomicCAS(&tkeys[s], kEmptyKey, key);
+        if (prev == kEmptyKey || prev == key) break;
+        s = (s + 1) & mask;
+    }
+    atomicMin(&tfirst[s], p);
+    slot_of[p] = (int)s;
+}
+
+__global__ void k_mark_first(const int* __restrict__ slot_of, const int* __restrict__ tfirst, int ncorner,
+                             int* __restrict__ is_first) {
+    int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= ncorner) return;
+    is_first[p] = (tfirst[slot_of[p]] == p) ? 1 : 0;
+}
+
+__global__ void k_assign_ids(const int* __restrict__ slot_of, const int* __restrict__ tfirst, const int* __restrict__ vid,
+                             const float* __restrict__ soup, int ncorner, int* __restrict__ faces, float* __restrict__ verts) {
+    int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= ncorner) return;
+    int fp = tfirst[slot_of[p]];
+    int id = vid[fp];
+    faces[p] = id;
+    if (fp == p) {
+        verts[(size_t)id * 3 + 0] = soup[(size_t)p * 3 + 0];
+        verts[(size_t)id * 3 + 1] = soup[(size_t)p * 3 + 1];
+        verts[(size_t)id * 3 + 2] = soup[(size_t)p * 3 + 2];
+    }
+}
+
+// keys -> (vertex ids per corner, unique vertices).  Scratch comes from the ctx arena.
+int dev_dedup(mrb_ctx* ctx, const float* soup, const unsigned long long* keys, int ncorner, int* faces, float** verts_out,
+              int* nverts_out) {
+    size_t cap = 1024;
+    while (cap < (size_t)ncorner * 2) cap <<= 1;
+    unsigned long long* tkeys = nullptr;
+    int *tfirst = nullptr, *slot_of = nullptr, *is_first = nullptr;
+    MRB_TRY(arena_alloc(ctx, cap, &tkeys));
+    MRB_TRY(arena_alloc(ctx, cap, &tfirst));
+    MRB_TRY(arena_alloc(ctx, (size_t)ncorner, &slot_of));
+    MRB_TRY(arena_alloc(ctx, (size_t)ncorner, &is_first));
+    size_t want = (cap + 255) / 256, lim = (size_t)ctx->sm_count * 16;
+    MRB_LAUNCH(ctx, k_hash_clear, (unsigned)(want < lim ? want : lim), 256, 0, tkeys, tfirst, cap);
+    MRB_LAUNCH(ctx, k_hash_insert, cdiv(ncorner, 256), 256, 0, keys, ncorner, tkeys, tfirst, (uint32_t)(cap - 1), slot_of);
+    MRB_LAUNCH(ctx, k_mark_first, cdiv(ncorner, 256), 256, 0, slot_of, tfirst, ncorner, is_first);
+    MRB_TRY(scan_exclusive(ctx, is_first, is_first, (size_t)ncorner, ctx->d_mail));
+    int nverts = 0;
+    MRB_TRY(read_int(ctx, ctx->d_mail, &nverts));
+    float* verts = nullptr;
+    MRB_TRY(arena_alloc(ctx, (size_t)(nverts > 0 ? nverts : 1) * 3, &verts));
+    MRB_LAUNCH(ctx, k_assign_ids, cdiv(ncorner, 256), 256, 0, slot_of, tfirst, is_first, soup, ncorner, faces, verts);
+    *verts_out = verts;
+    *nverts_out = nverts;
+    return MRB_OK;
+}
+
+int dev_mcubes(mrb_ctx* ctx, const float* F, Dims d, float isolevel, float** verts_dev, int** faces_dev, int* nverts,
+               int* nfaces) {
+    *verts_dev = nullptr; *faces_dev = nullptr; *nverts = 0; *nfaces = 0;
+    if (d.nx < 2 || d.ny < 2 || d.nz < 2) return MRB_OK;
+    CellDims cd{d.nx, d.ny, d.nz, d.nx - 1, d.ny - 1, d.nz - 1};
+    size_t ncell_total = (size_t)cd.cx * cd.cy * cd.cz;
+    int* cells = nullptr;
+    int ncells = 0;
+    MRB_TRY(compact(ctx, ActiveCellPred{F, cd, isolevel}, ncell_total, &cells, &ncells));
+    if (ncells == 0) return MRB_OK;
+    int* tri_off = nullptr;
+    MRB_TRY(arena_alloc(ctx, (size_t)ncells, &tri_off));
+    MRB_LAUNCH(ctx, k_mc_count, cdiv(ncells, 128), 128, 0, F, cd, cells, ncells, isolevel, tri_off);
+    MRB_TRY(scan_exclusive(ctx, tri_off, tri_off, (size_t)ncells, ctx->d_mail));
+    int ntri = 0;
+    MRB_TRY(read_int(ctx, ctx->d_mail, &ntri));
+    if (ntri == 0) return MRB_OK;
+    float* soup = nullptr;
+    unsigned long long* keys = nullptr;
+    int* faces = nullptr;
+    MRB_TRY(arena_alloc(ctx, (size_t)ntri * 9, &soup));
+    MRB_TRY(arena_alloc(ctx, (size_t)ntri * 3, &keys));
+    MRB_TRY(arena_alloc(ctx, (size_t)ntri * 3, &faces));
+    MRB_LAUNCH(ctx, k_mc_emit, cdiv(ncells, 128), 128, 0, F, cd, cells, ncells, isolevel, tri_off, soup, keys);
+    MRB_TRY(dev_dedup(ctx, soup, keys, ntri * 3, faces, verts_dev, nverts));
+    *faces_dev = faces;
+    *nfaces = ntri;
+    return MRB_OK;
+}
+
+__global__ void k_hash_points(const float* __restrict__ xyz, int n, int ny, int nz, unsigned long long* __restrict__ keys) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    F3 p = {xyz[3 * (size_t)i], xyz[3 * (size_t)i + 1], xyz[3 * (size_t)i + 2]};
+    keys[i] = hash_xyz(p, ny, nz);
+}
+
+// Copies a device-resident mesh into the caller-visible mrb_mesh (host malloc or device arena pointers).
+int export_mesh(mrb_ctx* ctx, float* verts_dev, int* faces_dev, int nverts, int nfaces, int device_out, mrb_mesh* out) {
+    out->nverts = nverts;
+    out->nfaces = nfaces;
+    out->on_device = device_out ? 1 : 0;
+    if (device_out) {
+        out->verts = verts_dev;
+        out->faces = faces_dev;
+        return sync(ctx);
+    }
+    out->verts = (float*)malloc(sizeof(float) * 3 * (size_t)(nverts > 0 ? nverts : 1));
+    out->faces = (int*)malloc(sizeof(int) * 3 * (size_t)(nfaces > 0 ? nfaces : 1));
+    if (!out->verts || !out->faces) { set_error("export_mesh: host malloc failed"); return MRB_ENOMEM; }
+    if (nverts > 0) MRB_CUDA(cudaMemcpyAsync(out->verts, verts_dev, sizeof(float) * 3 * (size_t)nverts, cudaMemcpyDeviceToHost, ctx->stream));
+    if (nfaces > 0) MRB_CUDA(cudaMemcpyAsync(out->faces, faces_dev, sizeof(int) * 3 * (size_t)nfaces, cudaMemcpyDeviceToHost, ctx->stream));
+    return sync(ctx);
+}
+
+}  // namespace mrb
+
+using namespace mrb;
+
+extern "C" {
+
+int mrb_mcubes(mrb_ctx* ctx, const float* F, const int dims[3], float isolevel, int device_out, mrb_mesh* out) {
+    MRB_REQUIRE(ctx && F && dims && out, "NULL argument");
+    MRB_CUDA(cudaSetDevice(ctx->device));
+    MRB_TRY(ctx->arena.reset());
+    memset(out, 0, sizeof(*out));
+    Dims d = mkdims(dims);
+    const float* dF = nullptr;
+    MRB_TRY(stage_in(ctx, F, d.count(), &dF));
+    float* verts = nullptr;
+    int* faces = nullptr;
+    int nv = 0, nf = 0;
+    MRB_TRY(dev_mcubes(ctx, dF, d, isolevel, &verts, &faces, &nv, &nf));
+    return export_mesh(ctx, verts, faces, nv, nf, device_out, out);
+}
+
+void mrb_mesh_free(mrb_mesh* mesh) {
+    if (!mesh) return;
+    if (!mesh->on_device) { free(mesh->verts); free(mesh->faces); }
+    mesh->verts = nullptr; mesh->faces = nullptr; mesh->nverts = 0; mesh->nfaces = 0;
+}
+
+int mrb_hash_points(mrb_ctx* ctx, const float* xyz, int n, const int dims[3], uint64_t* keys_out) {
+    MRB_REQUIRE(ctx && dims && (n == 0 || (xyz && keys_out)) && n >= 0, "bad argument");
+    MRB_CUDA(cudaSetDevice(ctx->device));
+    MRB_TRY(ctx->arena.reset());
+    if (n == 0) return MRB_OK;
+    const float* dx = nullptr;
+    MRB_TRY(stage_in(ctx, xyz, (size_t)n * 3, &dx));
+    Out<unsigned long long> o;
+    MRB_TRY(o.init(ctx, (unsigned long long*)keys_out, (size_t)n));
+    MRB_LAUNCH(ctx, k_hash_points, cdiv(n, 256), 256, 0, dx, n, dims[1], dims[2], o.dev);
+    MRB_TRY(o.commit(ctx));
+    return sync(ctx);
+}
+
+}  // extern "C"

@@ -1,0 +1,226 @@
+"""GPU parity tests, stage by stage, through the C-ABI (libmrb.so) against the CPU oracle.
+
+Integer / index / topology outputs must be bit-exact; the margin and the QP iterate are compared
+with tolerance 0 as well (design target: bit-exact), the documented bound being 1e-4 voxel units.
+"""
+import numpy as np
+import pytest
+
+from conftest import random_blobs
+
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-4   # north_star tolerance for float outputs (voxel units); we assert exact equality first
+
+
+def volumes(synth):
+    yield "sphere52", synth.sphere(52, 17.0)
+    yield "blobs40", random_blobs((40, 44, 48), seed=1)
+    yield "box_rot", synth.box(48, (12, 9, 7), None, 20.0, 35.0)
+    yield "torus", synth.torus(56, 14.0, 5.0)
+
+
+def test_fast_perim(ctx, O, synth):
+    for name, v in volumes(synth):
+        assert np.array_equal(ctx.fastPerim(v), O.fast_perim(v)), name
+    # arbitrary float values (the reference compares with !=)
+    rng = np.random.default_rng(0)
+    v = rng.integers(0, 3, size=(9, 10, 11)).astype(np.float32) * 0.5
+    assert np.array_equal(ctx.fastPerim(v), O.fast_perim(v))
+
+
+def test_sqdist_exact(ctx, O, synth):
+    for name, v in volumes(synth):
+        p = O.fast_perim(v)
+        assert np.array_equal(ctx.getsqdist(p), O.sqdist(p, brute=True)), name
+    # sparse sites, non-cubic grid
+    rng = np.random.default_rng(3)
+    g = (rng.random((17, 23, 29)) > 0.002).astype(np.float32)
+    assert np.array_equal(ctx.getsqdist(g), O.sqdist(g, brute=True))
+    # no zero voxel at all -> 100000 everywhere (dfields.cpp:50-58)
+    g = np.ones((8, 9, 10), np.float32)
+    assert np.array_equal(ctx.getsqdist(g), np.full(g.shape, 100000.0, np.float32))
+
+
+def test_sqdist_clamp(ctx, O):
+    # a single zero voxel in a long grid: squared distances beyond 100000 are clamped (needs > 317 voxels)
+    g = np.ones((340, 3, 4), np.float32)
+    g[2, 1, 1] = 0.0
+    got = ctx.getsqdist(g)
+    ref = O.sqdist(g, brute=True)
+    assert got.max() == 100000.0
+    assert np.array_equal(got, ref)
+    g = np.ones((3, 4, 350), np.float32)
+    g[1, 2, 340] = 0.0
+    assert np.array_equal(ctx.getsqdist(g), O.sqdist(g, brute=True))
+    g = np.ones((3, 345, 4), np.float32)
+    g[1, 5, 2] = 0.0
+    assert np.array_equal(ctx.getsqdist(g), O.sqdist(g, brute=True))
+
+
+def test_sqrt_and_dfield(ctx, O, synth):
+    for name, v in volumes(synth):
+        m_ref = O.dfield(v, brute=True)
+        m = ctx.dfield_gpu(v)
+        assert np.array_equal(m, m_ref), name
+        s = O.sqdist(O.fast_perim(v))
+        assert np.array_equal(ctx.getsqrt(s), O.sqrt(s)), name
+
+
+def test_bands(ctx, O, synth):
+    for name, v in volumes(synth):
+        m = O.dfield(v)
+        band_ref, tight_ref = O.create_bands(m, 4.0)
+        band, tight = ctx.createBands(m, 4.0)
+        assert np.array_equal(band, band_ref) and np.array_equal(tight, tight_ref), name
+        assert np.array_equal(ctx.erode_grid(band_ref), O.erode(band_ref)), name
+        assert np.array_equal(ctx.dilate_grid(tight_ref), O.dilate(tight_ref)), name
+    # border voxels are copied, not morphed (narrowBand.cpp:11-14)
+    rng = np.random.default_rng(5)
+    g = (rng.random((7, 8, 9)) > 0.4).astype(np.float32)
+    assert np.array_equal(ctx.erode_grid(g), O.erode(g))
+    assert np.array_equal(ctx.dilate_grid(g), O.dilate(g))
+
+
+def test_find_indexes_and_index_map(ctx, O, synth):
+    for name, v in volumes(synth):
+        band, _ = O.create_bands(O.dfield(v), 4.0)
+        idx_ref = O.find_indexes(band)
+        idx = ctx.findIndexes(band)
+        assert np.array_equal(idx, idx_ref), name
+        assert np.array_equal(ctx.getIndexMap(band.shape, idx), O.index_map(band.shape, idx_ref)), name
+    empty = np.zeros((5, 6, 7), np.float32)
+    assert len(ctx.findIndexes(empty)) == 0
+
+
+def test_prime_qp(ctx, O, synth):
+    for name, v in volumes(synth):
+        m = O.dfield(v)
+        band, tight = O.create_bands(m, 4.0)
+        ref = O.prime_qp(v, m, band, tight)
+        got = ctx.primeQP(v, m, band, tight)
+        assert got["n"] == ref["n"], name
+        for k in ("lb", "ub", "x0", "invdg", "jc", "ir", "pr"):
+            assert np.array_equal(got[k], ref[k]), (name, k)
+
+
+def test_run_qp_csc(ctx, O, synth):
+    for name, v in volumes(synth):
+        m = O.dfield(v)
+        band, tight = O.create_bands(m, 4.0)
+        q = O.prime_qp(v, m, band, tight)
+        for iters in (1, 2, 37):
+            assert np.array_equal(ctx.runQP(q, iters=iters), O.run_qp(q, iters=iters)), (name, iters)
+
+
+def test_run_qp_feature_reset(ctx, O, synth):
+    v = synth.sphere(40, 11.0)
+    m = O.dfield(v)
+    band, tight = O.create_bands(m, 4.0)
+    q = O.prime_qp(v, m, band, tight)
+    n = q["n"]
+    for feat in ([5, 17, 300], [-1, 5, 17], [n - 1], []):
+        f = np.array(feat, np.int32)
+        ref = O.run_qp(q, iters=5, feature_idx=f, using_features=True)
+        got = ctx.runQP(q, f, True, iters=5)
+        assert np.array_equal(got, ref), feat
+
+
+def test_optimize_matrix_free(ctx, O, synth):
+    """The matrix-free persistent stencil kernel == 500 CSC sweeps of the reference, bit for bit."""
+    for name, v in volumes(synth):
+        for iters in (3, 500):
+            F_ref, info = O.optimize(v, iters=iters, return_info=True)
+            F, st = ctx.optimize(v, iters=iters, return_stats=True)
+            assert st["n_band"] == info["n_band"], name
+            assert np.abs(F - F_ref).max() <= TOL, name
+            assert np.array_equal(F, F_ref), (name, iters)
+
+
+def test_optimize_band_sizes(ctx, O, synth):
+    v = synth.sphere(64, 20.0)
+    for bs in (2, 8):
+        F_ref = O.optimize(v, band_size=bs, iters=20)
+        F = ctx.optimize(v, band_size=bs, iters=20)
+        assert np.array_equal(F, F_ref), bs
+
+
+def test_optimize_sign_constraints(ctx, O, synth):
+    v = synth.sphere(52, 17.0)
+    F = ctx.optimize(v)
+    m = O.dfield(v)
+    band, _ = O.create_bands(m, 4.0)
+    inb = band != 0
+    inside = v == 1
+    assert np.all(F[inb & inside] >= m[inb & inside])     # x >= lb = margin inside
+    assert np.all(F[inb & ~inside] <= -m[inb & ~inside])  # x <= ub = -margin outside
+    assert np.all(F[~inb & inside] == 5.0) and np.all(F[~inb & ~inside] == -5.0)
+
+
+def test_border_band_is_an_error(ctx):
+    import mesh_reconstruction_b200 as mrb
+    v = np.zeros((20, 20, 20), np.float32)
+    v[0:8, 5:15, 5:15] = 1.0      # object touches the border -> tight band on the border
+    with pytest.raises(mrb.MrbError) as e:
+        ctx.optimize(v)
+    assert e.value.code == -4
+
+
+def test_mcubes_topology(ctx, O, synth):
+    for name, v in volumes(synth):
+        F = O.optimize(v)
+        verts_ref, faces_ref = O.mcubes(F, 0.0)
+        verts, faces = ctx.mcubes(F, 0.0)
+        assert faces.shape == faces_ref.shape and verts.shape == verts_ref.shape, name
+        assert np.array_equal(faces, faces_ref), name
+        assert np.array_equal(verts, verts_ref), name
+
+
+def test_mcubes_binary_volume_isolevel_half(ctx, O, synth):
+    # m_cubes.cpp:80: plain MC on a 0/1 grid at isolevel 0.5 (exact corner hits, degenerate filter, hash merges)
+    v = synth.box(30, (6, 5, 4), None, 0.0, 0.0)
+    verts_ref, faces_ref = O.mcubes(v, 0.5)
+    verts, faces = ctx.mcubes(v, 0.5)
+    assert np.array_equal(faces, faces_ref) and np.array_equal(verts, verts_ref)
+    # isolevel 0 on a grid with exact zeros: vertices land on grid corners, triangles degenerate
+    g = np.zeros((6, 6, 6), np.float32) - 1.0
+    g[2:4, 2:4, 2:4] = 1.0
+    g[3, 3, 3] = 0.0
+    g[1, 2, 2] = 0.0
+    verts_ref, faces_ref = O.mcubes(g, 0.0)
+    verts, faces = ctx.mcubes(g, 0.0)
+    assert np.array_equal(faces, faces_ref) and np.array_equal(verts, verts_ref)
+
+
+def test_hash_points(ctx, O):
+    rng = np.random.default_rng(11)
+    pts = (rng.random((5000, 3)) * np.array([255, 255, 255])).astype(np.float32)
+    pts[:100] = np.round(pts[:100])
+    assert np.array_equal(ctx.hashXYZ(pts, (256, 256, 256)), O.hash_points(pts, (256, 256, 256)))
+
+
+def test_reconstruct_end_to_end(ctx, O, synth, tmp_path):
+    for name, v in volumes(synth):
+        verts_ref, faces_ref = O.mcubes(O.optimize(v), 0.0)
+        verts, faces, st = ctx.reconstruct(v, return_stats=True)
+        assert np.array_equal(faces, faces_ref) and np.array_equal(verts, verts_ref), name
+        assert st["iters"] == 500
+    # PLY bytes identical to the oracle writer (mcubes.cpp:626-660)
+    a, b = tmp_path / "a.ply", tmp_path / "b.ply"
+    ctx.write_ply(str(a), verts, faces, (0.01, 0.02, 0.03), (-0.5, 0.25, 1.0), 6)
+    O.write_ply(str(b), verts_ref, faces_ref, (0.01, 0.02, 0.03), (-0.5, 0.25, 1.0), 6)
+    assert a.read_bytes() == b.read_bytes()
+
+
+def test_device_pointers(ctx, O, synth):
+    """Same entry points with device buffers (torch tensors passed by pointer)."""
+    import torch
+    v = synth.sphere(52, 17.0)
+    vt = torch.from_numpy(v).cuda()
+    F = ctx.optimize(vt)
+    assert F.is_cuda
+    F_ref = O.optimize(v)
+    assert np.array_equal(F.cpu().numpy(), F_ref)
+    verts, faces = ctx.reconstruct(vt)
+    verts_ref, faces_ref = O.mcubes(F_ref, 0.0)
+    assert np.array_equal(verts.cpu().numpy(), verts_ref) and np.array_equal(faces.cpu().numpy(), faces_ref)
