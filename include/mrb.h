@@ -116,6 +116,7 @@ typedef struct mrb_qp_stats {
     int     iters;           /* sweeps executed */
     float   last_max_delta;  /* max |x_new - x_old| over the band in the last sweep (warp-shuffle reduced) */
     float   ms_dfield, ms_band, ms_qp, ms_mc;   /* device time per stage of the last fused call */
+    float   ms_qp_kernel;    /* device time of the persistent sweep kernel alone (roofline denominator) */
 } mrb_qp_stats;
 
 /* optimize (quadprog.cu:236-280): stages 1-3 device-resident; F = +-(band_size+1) off band,

@@ -16,7 +16,8 @@ c_int_p = C.POINTER(C.c_int)
 
 class QPStats(C.Structure):
     _fields_ = [("n_band", C.c_int), ("n_tight", C.c_int), ("iters", C.c_int), ("last_max_delta", C.c_float),
-                ("ms_dfield", C.c_float), ("ms_band", C.c_float), ("ms_qp", C.c_float), ("ms_mc", C.c_float)]
+                ("ms_dfield", C.c_float), ("ms_band", C.c_float), ("ms_qp", C.c_float), ("ms_mc", C.c_float),
+                ("ms_qp_kernel", C.c_float)]
 
 
 class Mesh(C.Structure):

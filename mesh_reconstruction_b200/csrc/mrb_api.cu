@@ -71,6 +71,8 @@ static int optimize_dev(mrb_ctx* ctx, const float* vol, const float* fmap, Dims 
         cudaEventElapsedTime(&stats->ms_band, ctx->ev[1], ctx->ev[2]);
         cudaEventElapsedTime(&stats->ms_qp, ctx->ev[2], ctx->ev[3]);
         stats->ms_mc = 0.0f;
+        stats->ms_qp_kernel = 0.0f;
+        if (iters > 0 && bd.n_band > 0) cudaEventElapsedTime(&stats->ms_qp_kernel, ctx->ev[6], ctx->ev[7]);
     }
     return MRB_OK;
 }
@@ -140,7 +142,7 @@ int mrb_write_ply(const char* path, const float* verts, int nverts, const int* f
     if (!f) { set_error("mrb_write_ply: cannot open %s", path); return MRB_EINVAL; }
     std::string buf;
     buf.reserve(1 << 20);
-    char line[160];
+    char line[512];
     int len = snprintf(line, sizeof(line),
                        "ply\nformat ascii 1.0\nelement vertex %d\nproperty float x\nproperty float y\nproperty float z\n"
                        "element face %d\nproperty list uchar int vertex_indices\nend_header\n", nverts, nfaces);

@@ -218,7 +218,7 @@ int mrb_ctx_create(int device, mrb_ctx** out) {
     MRB_CUDA(cudaGetDeviceProperties(&prop, device));
     c->sm_count = prop.multiProcessorCount;
     MRB_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
-    for (int i = 0; i < 6; i++) MRB_CUDA(cudaEventCreate(&c->ev[i]));
+    for (int i = 0; i < 8; i++) MRB_CUDA(cudaEventCreate(&c->ev[i]));
     MRB_CUDA(cudaMallocHost((void**)&c->h_mail, 64 * sizeof(int)));
     MRB_CUDA(cudaMalloc((void**)&c->d_mail, 64 * sizeof(int)));
     *out = c;
@@ -230,7 +230,7 @@ void mrb_ctx_destroy(mrb_ctx* ctx) {
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     ctx->arena.release();
-    for (int i = 0; i < 6; i++) if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
+    for (int i = 0; i < 8; i++) if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
     if (ctx->h_mail) cudaFreeHost(ctx->h_mail);
     if (ctx->d_mail) cudaFree(ctx->d_mail);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);

@@ -59,7 +59,7 @@ struct mrb_ctx {
     int device = 0;
     int sm_count = 0;
     cudaStream_t stream = nullptr;
-    cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t ev[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     mrb::Arena arena;
     uint64_t launches = 0;
     // small pinned host mailbox for scalar read-backs

@@ -250,7 +250,9 @@ int dev_qp_solve(mrb_ctx* ctx, const BandDev& bd, Dims d, int band_size, int ite
         float* pb = xb + 2;
         int nn = n, its = iters;
         void* args[] = {(void*)&code, (void*)&m, (void*)&nbr, (void*)&pa, (void*)&pb, (void*)&nn, (void*)&its, (void*)&md};
+        MRB_CUDA(cudaEventRecord(ctx->ev[6], ctx->stream));
         MRB_CUDA(cudaLaunchCooperativeKernel((void*)k_qp_persistent, dim3(grid), dim3(block), args, 0, ctx->stream));
+        MRB_CUDA(cudaEventRecord(ctx->ev[7], ctx->stream));
         ctx->launches++;
     }
     // result = buffer written by the last sweep (iters odd -> xb, even -> xa; iters == 0 -> x0)
