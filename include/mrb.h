@@ -93,6 +93,32 @@ int mrb_find_indexes(mrb_ctx* ctx, const float* grid, const int dims[3],
 /* getIndexMap (grid.cpp:374-389): map = -1 everywhere, map(indexes[i]) = (float)i. */
 int mrb_index_map(mrb_ctx* ctx, const int dims[3], const int* indexes, int n, float* map_out);
 
+/* mrb_find_indexes for callers that must not allocate.  No counterpart in the reference.
+ *
+ * Same result as mrb_find_indexes (band voxels in reference order, x-fastest linear indexes), but
+ * the call makes no cudaMalloc / cudaFree / allocating library call of any kind and needs no
+ * mrb_ctx.  It exists for programs that cannot let a library allocate device memory: the card's
+ * memory already belongs to the host application's own pool (a deep-learning framework's caching
+ * allocator, a fixed perception arena on a robot), or the call sits in a loop with a deadline
+ * where the device-wide stall of cudaMalloc/cudaFree is not acceptable, or the process runs under
+ * a fixed memory quota.  Its scratch (one counter per 1024-voxel tile) is a fixed 64.25 KiB array
+ * inside the library image, held by every GPU that loads libmrb until the process exits.
+ *
+ *  - grid_dev, idx_out_dev: DEVICE pointers provided by the caller (host buffers are rejected:
+ *    staging them would need an allocation).  idx_out_dev may be NULL to get the count only.
+ *  - *n_out (host) receives the number of non-zero voxels; capacity = entries idx_out_dev can hold.
+ *  - Limit: dims[0]*dims[1]*dims[2] <= MRB_NOALLOC_MAX_VOXELS (256^3); larger grids are refused
+ *    with MRB_ECAPACITY and a message -- use mrb_find_indexes for them.
+ *  - stream: a cudaStream_t (NULL = the default stream); the call returns after the work finished.
+ *  - The first call on each GPU looks up the scratch array's device address (the current device
+ *    must be the one the buffers live on).  Make that first call before starting any stream capture.
+ *  - All calls on a GPU share the one array, which keeps the previous call's contents (the part a
+ *    call reads is cleared first).  Two calls that overlap on the same GPU -- different streams or
+ *    different host threads -- race on it: serialise them. */
+#define MRB_NOALLOC_MAX_VOXELS  (256 * 256 * 256)
+int mrb_find_indexes_noalloc(const float* grid_dev, const int dims[3], int* idx_out_dev, int capacity,
+                             int* n_out, void* stream);
+
 /* ---- stage 3: QP (optimize/) ------------------------------------------- */
 /* primeQP (primeqp.cpp:168-223) + getIr/getJc/getPr (quadprog.cpp:8-42).
  * n must equal the band count.  Outputs (each may be NULL to skip):

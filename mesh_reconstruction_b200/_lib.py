@@ -49,6 +49,7 @@ SYMBOLS = {
     "mrb_create_bands": (C.c_int, [_VP, _VP, c_int_p, C.c_float, _VP, _VP]),
     "mrb_find_indexes": (C.c_int, [_VP, _VP, c_int_p, _VP, C.c_int, c_int_p]),
     "mrb_index_map": (C.c_int, [_VP, c_int_p, _VP, C.c_int, _VP]),
+    "mrb_find_indexes_noalloc": (C.c_int, [_VP, c_int_p, _VP, C.c_int, c_int_p, _VP]),
     "mrb_prime_qp": (C.c_int, [_VP, _VP, _VP, _VP, _VP, c_int_p, C.c_int, _VP, _VP, _VP, _VP, _VP, _VP, _VP,
                                C.c_int, c_int_p]),
     "mrb_run_qp": (C.c_int, [_VP, C.c_int, _VP, _VP, _VP, _VP, _VP, _VP, _VP, C.c_int, _VP, C.c_int, C.c_int, _VP]),
