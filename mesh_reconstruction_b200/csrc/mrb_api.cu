@@ -14,67 +14,13 @@ namespace mrb {
 
 int export_mesh(mrb_ctx* ctx, float* verts_dev, int* faces_dev, int nverts, int nfaces, int device_out, mrb_mesh* out);
 
-// getFeatureIndexes (primeqp.cpp:231-244) + the reset loop of runQP (quadprog.cpp:92-101):
-// the sorted id list contains -1 for every feature voxel outside the band, and a single -1 blocks
-// all resets; otherwise every feature voxel of the band is set to 0.2.
-__global__ void k_feat_check(const float* __restrict__ fmap, const int* __restrict__ band_id, size_t n, int* __restrict__ any_off) {
-    for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < n; idx += (size_t)gridDim.x * blockDim.x)
-        if (fmap[idx] == 1.0f && band_id[idx] < 0) *any_off = 1;
-}
-__global__ void k_feat_apply(const float* __restrict__ fmap, const int* __restrict__ band_id, size_t n,
-                             const int* __restrict__ any_off, float* __restrict__ x) {
-    if (*any_off) return;
-    for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < n; idx += (size_t)gridDim.x * blockDim.x)
-        if (fmap[idx] == 1.0f) x[band_id[idx]] = 0.2f;
-}
+// stages 1-3, implemented in mrb_strips.cu
+int optimize_strips(mrb_ctx* ctx, const float* vol, const float* fmap, Dims d, int using_features, int band_size,
+                    int iters, float* F_dev, mrb_qp_stats* stats);
 
-// Stages 1-3 on device pointers.  F_dev: N^3 floats.
 static int optimize_dev(mrb_ctx* ctx, const float* vol, const float* fmap, Dims d, int using_features, int band_size,
                         int iters, float* F_dev, mrb_qp_stats* stats) {
-    const size_t n = d.count();
-    MRB_CUDA(cudaEventRecord(ctx->ev[0], ctx->stream));
-    float* margin = nullptr;
-    MRB_TRY(arena_alloc(ctx, n, &margin));
-    MRB_TRY(dev_dfield(ctx, vol, d, margin));
-    MRB_CUDA(cudaEventRecord(ctx->ev[1], ctx->stream));
-    float *b0 = nullptr, *tight = nullptr, *band = nullptr;
-    MRB_TRY(arena_alloc(ctx, n, &b0));
-    MRB_TRY(arena_alloc(ctx, n, &tight));
-    band = F_dev;   // F is written last; reuse it for the band grid until then
-    MRB_TRY(dev_threshold(ctx, margin, n, (float)band_size, b0));
-    MRB_TRY(dev_erode(ctx, b0, d, tight));
-    MRB_TRY(dev_dilate(ctx, tight, d, band));
-    BandDev bd;
-    MRB_TRY(dev_qp_build(ctx, vol, margin, band, tight, d, &bd));
-    MRB_CUDA(cudaEventRecord(ctx->ev[2], ctx->stream));
-    float* x = nullptr;
-    MRB_TRY(arena_alloc(ctx, (size_t)(bd.n_band > 0 ? bd.n_band : 1), &x));
-    float last_delta = 0.0f;
-    MRB_TRY(dev_qp_solve(ctx, bd, d, band_size, iters, x, stats ? &last_delta : nullptr));
-    if (using_features && fmap && bd.n_band > 0) {
-        int* flag = ctx->d_mail + 16;
-        MRB_CUDA(cudaMemsetAsync(flag, 0, sizeof(int), ctx->stream));
-        size_t want = (n + 255) / 256, cap = (size_t)ctx->sm_count * 16;
-        unsigned g = (unsigned)(want < cap ? want : cap);
-        MRB_LAUNCH(ctx, k_feat_check, g, 256, 0, fmap, bd.band_id, n, flag);
-        MRB_LAUNCH(ctx, k_feat_apply, g, 256, 0, fmap, bd.band_id, n, flag, x);
-    }
-    MRB_TRY(dev_assemble_F(ctx, vol, bd, x, d, band_size, F_dev));
-    MRB_CUDA(cudaEventRecord(ctx->ev[3], ctx->stream));
-    if (stats) {
-        MRB_CUDA(cudaEventSynchronize(ctx->ev[3]));
-        stats->n_band = bd.n_band;
-        stats->n_tight = bd.n_tight;
-        stats->iters = iters;
-        stats->last_max_delta = last_delta;
-        cudaEventElapsedTime(&stats->ms_dfield, ctx->ev[0], ctx->ev[1]);
-        cudaEventElapsedTime(&stats->ms_band, ctx->ev[1], ctx->ev[2]);
-        cudaEventElapsedTime(&stats->ms_qp, ctx->ev[2], ctx->ev[3]);
-        stats->ms_mc = 0.0f;
-        stats->ms_qp_kernel = 0.0f;
-        if (iters > 0 && bd.n_band > 0) cudaEventElapsedTime(&stats->ms_qp_kernel, ctx->ev[6], ctx->ev[7]);
-    }
-    return MRB_OK;
+    return optimize_strips(ctx, vol, fmap, d, using_features, band_size, iters, F_dev, stats);
 }
 
 }  // namespace mrb
