@@ -221,6 +221,7 @@ int mrb_ctx_create(int device, mrb_ctx** out) {
     for (int i = 0; i < 8; i++) MRB_CUDA(cudaEventCreate(&c->ev[i]));
     MRB_CUDA(cudaMallocHost((void**)&c->h_mail, 64 * sizeof(int)));
     MRB_CUDA(cudaMalloc((void**)&c->d_mail, 64 * sizeof(int)));
+    MRB_CUDA(cudaMalloc((void**)&c->d_bar, 64 * sizeof(int)));
     *out = c;
     return MRB_OK;
 }
@@ -233,6 +234,7 @@ void mrb_ctx_destroy(mrb_ctx* ctx) {
     for (int i = 0; i < 8; i++) if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
     if (ctx->h_mail) cudaFreeHost(ctx->h_mail);
     if (ctx->d_mail) cudaFree(ctx->d_mail);
+    if (ctx->d_bar) cudaFree(ctx->d_bar);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }

@@ -65,6 +65,7 @@ struct mrb_ctx {
     // small pinned host mailbox for scalar read-backs
     int* h_mail = nullptr;      // 64 ints, pinned
     int* d_mail = nullptr;      // 64 ints, device
+    int* d_bar = nullptr;       // 64 ints, device: grid-barrier words (two 128-byte lines)
 };
 
 namespace mrb {

@@ -33,6 +33,8 @@ namespace mrb {
 
 static const int kFar = 255;      // u8 "beyond the window"
 
+__constant__ float c_invdg_s[19];   // (float)(1.0/(double)d), d = 0..18; entry 0 is 0 (primeqp.cpp:189-197)
+
 static unsigned grid_for(mrb_ctx* ctx, size_t n, int block) {
     size_t want = (n + block - 1) / block;
     size_t cap = (size_t)ctx->sm_count * 16;
@@ -218,7 +220,7 @@ template <typename MarginFn>
 __global__ void __launch_bounds__(128) k_strip_build(const float* __restrict__ vol, MarginFn margin, const uint8_t* __restrict__ flags,
                                                      const int* __restrict__ sid, const int* __restrict__ spos, int S, StripDims sd,
                                                      uint32_t* __restrict__ code, float4* __restrict__ lb4, float4* __restrict__ ub4,
-                                                     float4* __restrict__ x0, int4* __restrict__ nbA, int4* __restrict__ nbB,
+                                                     float4* __restrict__ inv4, float4* __restrict__ x0, int4* __restrict__ nbA, int4* __restrict__ nbB,
                                                      int2* __restrict__ nbC, int* __restrict__ err) {
     int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= S) return;
@@ -271,6 +273,17 @@ __global__ void __launch_bounds__(128) k_strip_build(const float* __restrict__ v
     lb4[s] = make_float4(lbv[0], lbv[1], lbv[2], lbv[3]);
     ub4[s] = make_float4(ubv[0], ubv[1], ubv[2], ubv[3]);
     x0[s] = make_float4(xv[0], xv[1], xv[2], xv[3]);
+    {   // d = 12 T(v) + the six neighbour T bits; invdg from the table (0 where d == 0)
+        float iv[4];
+        for (int j = 0; j < 4; j++) {
+            uint32_t tzm = j > 0 ? (c >> (j - 1)) & 1u : (c >> 4) & 1u;
+            uint32_t tzp = j < 3 ? (c >> (j + 1)) & 1u : (c >> 5) & 1u;
+            int dg = 12 * (int)((c >> j) & 1u) + (int)((c >> (6 + j)) & 1u) + (int)((c >> (10 + j)) & 1u) +
+                     (int)((c >> (14 + j)) & 1u) + (int)((c >> (18 + j)) & 1u) + (int)tzm + (int)tzp;
+            iv[j] = c_invdg_s[dg];
+        }
+        inv4[s] = make_float4(iv[0], iv[1], iv[2], iv[3]);
+    }
     auto nid = [&](bool ok, long long dstrip) {
         int id = ok ? sid[p + dstrip] : -1;
         return id >= 0 ? id : S;           // slot S = the all-zero dummy strip
@@ -289,13 +302,12 @@ struct StripBand {
     int* sid = nullptr;         // nx*ny*nz4 strip id or -1
     int* spos = nullptr;        // S
     uint32_t* code = nullptr;   // S
-    float4 *lb4 = nullptr, *ub4 = nullptr;   // S
+    float4 *lb4 = nullptr, *ub4 = nullptr, *inv4 = nullptr;   // S
     float4 *xa = nullptr, *xb = nullptr;     // S+1 (slot S = zeros)
     int4 *nbA = nullptr, *nbB = nullptr;     // S
     int2* nbC = nullptr;                     // S
 };
 
-__constant__ float c_invdg_s[19];
 static int upload_invdg_s(int device) {
     static bool ready[64] = {false};
     if (ready[device & 63]) return MRB_OK;
@@ -325,6 +337,7 @@ static int build_strips(mrb_ctx* ctx, const float* vol, MarginFn margin, uint8_t
     MRB_TRY(arena_alloc(ctx, Sn, &sb->code));
     MRB_TRY(arena_alloc(ctx, Sn, &sb->lb4));
     MRB_TRY(arena_alloc(ctx, Sn, &sb->ub4));
+    MRB_TRY(arena_alloc(ctx, Sn, &sb->inv4));
     MRB_TRY(arena_alloc(ctx, Sn + 1, &sb->xa));
     MRB_TRY(arena_alloc(ctx, Sn + 1, &sb->xb));
     MRB_TRY(arena_alloc(ctx, Sn, &sb->nbA));
@@ -337,33 +350,35 @@ static int build_strips(mrb_ctx* ctx, const float* vol, MarginFn margin, uint8_t
     MRB_CUDA(cudaMemsetAsync(sb->xa + S, 0, sizeof(float4), ctx->stream));
     MRB_CUDA(cudaMemsetAsync(sb->xb, 0, (Sn + 1) * sizeof(float4), ctx->stream));
     MRB_LAUNCH(ctx, (k_strip_build<MarginFn>), cdiv(S, 128), 128, 0, vol, margin, flags, sb->sid, sb->spos, S, sb->sd, sb->code,
-               sb->lb4, sb->ub4, sb->xa, sb->nbA, sb->nbB, sb->nbC, err);
+               sb->lb4, sb->ub4, sb->inv4, sb->xa, sb->nbA, sb->nbB, sb->nbC, err);
     return MRB_OK;
 }
 
 // ---- the persistent sweep kernel --------------------------------------------------------------------------
-// One voxel update.  T bits: a = T(v); the six neighbour bits select the coefficients.
-//   c(+-e)  = a ? (t ? -4 : -2) : (t ? -2 : 0)      c(+-2e) = t ? 1 : 0
-__device__ __forceinline__ float qp_voxel(float xc, float xm2, float xm1, float ym2, float ym1, float zm2, float zm1,
-                                          float zp1, float zp2, float yp1, float yp2, float xp1, float xp2, bool a, bool txm,
-                                          bool txp, bool tym, bool typ, bool tzm, bool tzp, float lb, float ub) {
+// One voxel update.  Bits of the strip code word are tested in place (one LOP3 -> predicate each):
+//   MA: T(v); MXM/MXP/MYM/MYP/MZM/MZP: T of the six neighbours.
+//   c(+-e)  = T(v) ? (t ? -4 : -2) : (t ? -2 : 0)      c(+-2e) = t ? 1 : 0
+// inv = (float)(1.0/(double)d) precomputed per voxel (0 where d == 0), primeqp.cpp:189-197.
+template <uint32_t MA, uint32_t MXM, uint32_t MXP, uint32_t MYM, uint32_t MYP, uint32_t MZM, uint32_t MZP>
+__device__ __forceinline__ float qp_voxel(uint32_t c, float xc, float xm2, float xm1, float ym2, float ym1, float zm2,
+                                          float zm1, float zp1, float zp2, float yp1, float yp2, float xp1, float xp2,
+                                          float inv, float lb, float ub) {
+    const bool a = c & MA;
     const float cA = a ? -4.0f : -2.0f;      // neighbour tight
     const float cB = a ? -2.0f : 0.0f;       // neighbour not tight
-    float res = 0.0f;
-    if (txm) res = __fadd_rn(res, xm2);
-    res = __fmaf_rn(txm ? cA : cB, xm1, res);
-    if (tym) res = __fadd_rn(res, ym2);
-    res = __fmaf_rn(tym ? cA : cB, ym1, res);
-    if (tzm) res = __fadd_rn(res, zm2);
-    res = __fmaf_rn(tzm ? cA : cB, zm1, res);
-    res = __fmaf_rn(tzp ? cA : cB, zp1, res);
-    if (tzp) res = __fadd_rn(res, zp2);
-    res = __fmaf_rn(typ ? cA : cB, yp1, res);
-    if (typ) res = __fadd_rn(res, yp2);
-    res = __fmaf_rn(txp ? cA : cB, xp1, res);
-    if (txp) res = __fadd_rn(res, xp2);
-    const int dg = (a ? 12 : 0) + (int)txm + (int)txp + (int)tym + (int)typ + (int)tzm + (int)tzp;
-    float t = __fsub_rn(xc, __fmul_rn(res, c_invdg_s[dg]));
+    float res = (c & MXM) ? xm2 : 0.0f;
+    res = __fmaf_rn((c & MXM) ? cA : cB, xm1, res);
+    if (c & MYM) res = __fadd_rn(res, ym2);
+    res = __fmaf_rn((c & MYM) ? cA : cB, ym1, res);
+    if (c & MZM) res = __fadd_rn(res, zm2);
+    res = __fmaf_rn((c & MZM) ? cA : cB, zm1, res);
+    res = __fmaf_rn((c & MZP) ? cA : cB, zp1, res);
+    if (c & MZP) res = __fadd_rn(res, zp2);
+    res = __fmaf_rn((c & MYP) ? cA : cB, yp1, res);
+    if (c & MYP) res = __fadd_rn(res, yp2);
+    res = __fmaf_rn((c & MXP) ? cA : cB, xp1, res);
+    if (c & MXP) res = __fadd_rn(res, xp2);
+    float t = __fsub_rn(xc, __fmul_rn(res, inv));
     t = t * 0.5f;
     if (t < lb) t = lb;
     if (t > ub) t = ub;
@@ -372,38 +387,102 @@ __device__ __forceinline__ float qp_voxel(float xc, float xm2, float xm1, float 
 
 __device__ __forceinline__ float4 ld4(const float4* p) { return *p; }
 
-__global__ void __launch_bounds__(512) k_qp_strips(const uint32_t* __restrict__ code, const float4* __restrict__ lb4,
-                                                   const float4* __restrict__ ub4, const int4* __restrict__ nbA,
-                                                   const int4* __restrict__ nbB, const int2* __restrict__ nbC, float4* xa,
-                                                   float4* xb, int S, int iters, unsigned* __restrict__ maxdelta_bits) {
-    cg::grid_group grid = cg::this_grid();
-    const int gsize = gridDim.x * blockDim.x;
-    const int gtid = blockIdx.x * blockDim.x + threadIdx.x;
+// Lightweight grid barrier: one arrival counter that only grows during a launch; every block adds 1
+// (release) and polls it (acquire) until it reaches epoch * nblocks.  Together with the two bar.sync
+// this makes every block's sweep-k stores visible to every block's sweep-k+1 loads.
+// (Measured on B200, 148..296 blocks: ~1.5 us per barrier; a separate release flag written by the
+// last arriver was slower, ~1.9 us.)
+__device__ __forceinline__ void grid_barrier(unsigned* bar, unsigned epoch, unsigned nblocks) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned target = epoch * nblocks;
+        asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(bar) : "memory");
+        unsigned v;
+        do {
+            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(bar) : "memory");
+        } while (v < target);
+    }
+    __syncthreads();
+}
+
+// Streaming (evict-first, no L1 allocation) loads for the per-strip constants, so that the L1 keeps
+// the iterate lines that neighbouring strips of the same SM re-read.
+__device__ __forceinline__ float4 ldcs4(const float4* p) { return __ldcs(p); }
+__device__ __forceinline__ int4 ldcs4i(const int4* p) { return __ldcs(p); }
+__device__ __forceinline__ int2 ldcs2i(const int2* p) { return __ldcs(p); }
+
+struct StripIds { int4 a, b; int2 c; };
+
+// Mode 0: neighbour ids of the block's strips resident in shared memory (copied once).
+// Mode 1: ids from L2 every sweep.
+// Mode 2: ids from L2, software-pipelined one strip ahead (the ids -> x dependent round trip of the
+//         next strip overlaps the arithmetic of the current one); constants with streaming loads.
+template <int Mode, int Threads>
+__global__ void __launch_bounds__(Threads) k_qp_strips(const uint32_t* __restrict__ code, const float4* __restrict__ lb4,
+                                                       const float4* __restrict__ ub4, const float4* __restrict__ inv4,
+                                                       const int4* __restrict__ nbA, const int4* __restrict__ nbB,
+                                                       const int2* __restrict__ nbC, float4* xa, float4* xb, int S, int iters,
+                                                       int cap, unsigned* __restrict__ maxdelta_bits,
+                                                       unsigned* barrier_counter, int dbg) {
+    extern __shared__ int4 s_ids[];      // Mode 0: [cap] A, [cap] B, then [cap] int2 C
+    // each block owns a contiguous range of strips (balanced to +-1 strip across blocks; neighbouring
+    // y rows stay on the same SM, which keeps most y/z neighbour loads in L1)
+    const int s_begin = (int)((long long)S * blockIdx.x / gridDim.x);
+    int s_end = (int)((long long)S * (blockIdx.x + 1) / gridDim.x);
+    if (dbg & 2) s_end = s_begin;     // tuning aid: barrier cost only
+    int4* sA = s_ids;
+    int4* sB = s_ids + cap;
+    int2* sC = (int2*)(s_ids + 2 * cap);
+    if (Mode == 0) {
+        for (int s = s_begin + threadIdx.x; s < s_end; s += Threads) {
+            sA[s - s_begin] = __ldg(nbA + s);
+            sB[s - s_begin] = __ldg(nbB + s);
+            sC[s - s_begin] = __ldg(nbC + s);
+        }
+        __syncthreads();
+    }
+    auto load_ids = [&](int s) {
+        StripIds r;
+        if (Mode == 0) { r.a = sA[s - s_begin]; r.b = sB[s - s_begin]; r.c = sC[s - s_begin]; }
+        else if (Mode == 1) { r.a = __ldg(nbA + s); r.b = __ldg(nbB + s); r.c = __ldg(nbC + s); }
+        else { r.a = ldcs4i(nbA + s); r.b = ldcs4i(nbB + s); r.c = ldcs2i(nbC + s); }
+        return r;
+    };
     const float4* in = xa;
     float4* out = xb;
+    const int s0 = s_begin + threadIdx.x;
+    StripIds nxt;
+    if (Mode == 2 && s0 < s_end) nxt = load_ids(s0);
     for (int it = 0; it < iters; it++) {
         float dmax = 0.0f;
-        for (int s = gtid; s < S; s += gsize) {
-            const int4 a4 = __ldg(nbA + s);
-            const int4 b4 = __ldg(nbB + s);
-            const int2 c2 = __ldg(nbC + s);
-            const uint32_t c = __ldg(code + s);
-            const float4 lb = __ldg(lb4 + s), ub = __ldg(ub4 + s);
-            // the iterate is rewritten by other SMs every sweep: plain (coherent after grid.sync) loads
+        for (int s = s0; s < s_end; s += Threads) {
+            StripIds id;
+            if (Mode == 2) {
+                id = nxt;
+                int sn = s + Threads;
+                if (sn >= s_end) sn = s0;              // wrap: first strip of the next sweep
+                nxt = load_ids(sn);
+            } else {
+                id = load_ids(s);
+            }
+            uint32_t c;
+            float4 lb, ub, inv;
+            if (Mode == 2) { c = __ldcs(code + s); lb = ldcs4(lb4 + s); ub = ldcs4(ub4 + s); inv = ldcs4(inv4 + s); }
+            else { c = __ldg(code + s); lb = __ldg(lb4 + s); ub = __ldg(ub4 + s); inv = __ldg(inv4 + s); }
+            // the iterate is rewritten by other SMs every sweep: plain loads, ordered by the grid barrier
             const float4 xc = ld4(in + s);
-            const float4 xm2 = ld4(in + a4.x), xm1 = ld4(in + a4.y), ym2 = ld4(in + a4.z), ym1 = ld4(in + a4.w);
-            const float4 zlo = ld4(in + b4.x), zhi = ld4(in + b4.y), yp1 = ld4(in + b4.z), yp2 = ld4(in + b4.w);
-            const float4 xp1 = ld4(in + c2.x), xp2 = ld4(in + c2.y);
-            const bool t0 = c & 1u, t1 = c & 2u, t2 = c & 4u, t3 = c & 8u, tlo = c & 16u, thi = c & 32u;
+            const float4 xm2 = ld4(in + id.a.x), xm1 = ld4(in + id.a.y), ym2 = ld4(in + id.a.z), ym1 = ld4(in + id.a.w);
+            const float4 zlo = ld4(in + id.b.x), zhi = ld4(in + id.b.y), yp1 = ld4(in + id.b.z), yp2 = ld4(in + id.b.w);
+            const float4 xp1 = ld4(in + id.c.x), xp2 = ld4(in + id.c.y);
             float4 r;
-            r.x = qp_voxel(xc.x, xm2.x, xm1.x, ym2.x, ym1.x, zlo.z, zlo.w, xc.y, xc.z, yp1.x, yp2.x, xp1.x, xp2.x, t0,
-                           c & (1u << 6), c & (1u << 10), c & (1u << 14), c & (1u << 18), tlo, t1, lb.x, ub.x);
-            r.y = qp_voxel(xc.y, xm2.y, xm1.y, ym2.y, ym1.y, zlo.w, xc.x, xc.z, xc.w, yp1.y, yp2.y, xp1.y, xp2.y, t1,
-                           c & (1u << 7), c & (1u << 11), c & (1u << 15), c & (1u << 19), t0, t2, lb.y, ub.y);
-            r.z = qp_voxel(xc.z, xm2.z, xm1.z, ym2.z, ym1.z, xc.x, xc.y, xc.w, zhi.x, yp1.z, yp2.z, xp1.z, xp2.z, t2,
-                           c & (1u << 8), c & (1u << 12), c & (1u << 16), c & (1u << 20), t1, t3, lb.z, ub.z);
-            r.w = qp_voxel(xc.w, xm2.w, xm1.w, ym2.w, ym1.w, xc.y, xc.z, zhi.x, zhi.y, yp1.w, yp2.w, xp1.w, xp2.w, t3,
-                           c & (1u << 9), c & (1u << 13), c & (1u << 17), c & (1u << 21), t2, thi, lb.w, ub.w);
+            r.x = qp_voxel<1u << 0, 1u << 6, 1u << 10, 1u << 14, 1u << 18, 1u << 4, 1u << 1>(
+                c, xc.x, xm2.x, xm1.x, ym2.x, ym1.x, zlo.z, zlo.w, xc.y, xc.z, yp1.x, yp2.x, xp1.x, xp2.x, inv.x, lb.x, ub.x);
+            r.y = qp_voxel<1u << 1, 1u << 7, 1u << 11, 1u << 15, 1u << 19, 1u << 0, 1u << 2>(
+                c, xc.y, xm2.y, xm1.y, ym2.y, ym1.y, zlo.w, xc.x, xc.z, xc.w, yp1.y, yp2.y, xp1.y, xp2.y, inv.y, lb.y, ub.y);
+            r.z = qp_voxel<1u << 2, 1u << 8, 1u << 12, 1u << 16, 1u << 20, 1u << 1, 1u << 3>(
+                c, xc.z, xm2.z, xm1.z, ym2.z, ym1.z, xc.x, xc.y, xc.w, zhi.x, yp1.z, yp2.z, xp1.z, xp2.z, inv.z, lb.z, ub.z);
+            r.w = qp_voxel<1u << 3, 1u << 9, 1u << 13, 1u << 17, 1u << 21, 1u << 2, 1u << 5>(
+                c, xc.w, xm2.w, xm1.w, ym2.w, ym1.w, xc.y, xc.z, zhi.x, zhi.y, yp1.w, yp2.w, xp1.w, xp2.w, inv.w, lb.w, ub.w);
             out[s] = r;
             if (it == iters - 1)
                 dmax = fmaxf(fmaxf(dmax, fmaxf(fabsf(r.x - xc.x), fabsf(r.y - xc.y))), fmaxf(fabsf(r.z - xc.z), fabsf(r.w - xc.w)));
@@ -414,8 +493,15 @@ __global__ void __launch_bounds__(512) k_qp_strips(const uint32_t* __restrict__ 
             if ((threadIdx.x & 31) == 0) atomicMax(maxdelta_bits, __float_as_uint(dmax));
         }
         const float4* t = in; in = out; out = (float4*)t;
-        if (it + 1 < iters) grid.sync();
+        if (it + 1 < iters && !(dbg & 1)) grid_barrier(barrier_counter, (unsigned)(it + 1), gridDim.x);
     }
+}
+
+// Kernel variant (tuning knob): MRB_QP_VARIANT = "<mode>:<threads>", e.g. 0:1024, 1:512, 2:512, 2:1024
+static void qp_variant(int* mode, int* threads) {
+    *mode = 1; *threads = 512;       // measured best on B200 at 256^3 (see profiles/)
+    const char* e = getenv("MRB_QP_VARIANT");
+    if (e && e[0] >= '0' && e[0] <= '2' && e[1] == ':') { *mode = e[0] - '0'; *threads = atoi(e + 2) == 1024 ? 1024 : 512; }
 }
 
 static int solve_strips(mrb_ctx* ctx, const StripBand& sb, int iters, float4** result, float* last_delta_host) {
@@ -425,23 +511,44 @@ static int solve_strips(mrb_ctx* ctx, const StripBand& sb, int iters, float4** r
     if (S == 0 || iters == 0) return MRB_OK;
     unsigned* md = (unsigned*)(ctx->d_mail + 8);
     MRB_CUDA(cudaMemsetAsync(md, 0, sizeof(unsigned), ctx->stream));
-    int per_sm = 0;
-    const int block = 512;
-    MRB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_qp_strips, block, 0));
-    if (per_sm < 1) { set_error("k_qp_strips does not fit on an SM"); return MRB_ECUDA; }
+    int mode, block;
+    qp_variant(&mode, &block);
+    const size_t kSmemBudget = 200 * 1024;
+    if (mode == 0 && (size_t)((S + ctx->sm_count - 1) / ctx->sm_count) * 40 > kSmemBudget) mode = 2;
+    void* kern = nullptr;
+    if (mode == 0) kern = block == 1024 ? (void*)k_qp_strips<0, 1024> : (void*)k_qp_strips<0, 512>;
+    else if (mode == 1) kern = block == 1024 ? (void*)k_qp_strips<1, 1024> : (void*)k_qp_strips<1, 512>;
+    else kern = block == 1024 ? (void*)k_qp_strips<2, 1024> : (void*)k_qp_strips<2, 512>;
+    int per_sm = 2048 / block;                       // blocks per SM we want resident
+    if (mode == 0) per_sm = 1;
     int grid = per_sm * ctx->sm_count;
     int need = (S + block - 1) / block;
     if (grid > need) grid = need;
+    int cap = (S + grid - 1) / grid;
+    size_t smem = mode == 0 ? (size_t)cap * 40 : 0;
+    if (smem > 48 * 1024) MRB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int fit = 0;
+    MRB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessorWithFlags(&fit, kern, block, smem, 0));
+    if (fit < 1) { set_error("k_qp_strips does not fit on an SM"); return MRB_ECUDA; }
+    if (grid > fit * ctx->sm_count) {                // registers allow fewer blocks than wanted
+        grid = fit * ctx->sm_count;
+        cap = (S + grid - 1) / grid;
+        if (mode == 0) { smem = (size_t)cap * 40; if (smem > kSmemBudget) { set_error("k_qp_strips: ids do not fit in shared memory"); return MRB_ECUDA; } }
+        if (smem > 48 * 1024) MRB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    }
     const uint32_t* code = sb.code;
-    const float4 *lb4 = sb.lb4, *ub4 = sb.ub4;
+    const float4 *lb4 = sb.lb4, *ub4 = sb.ub4, *inv4 = sb.inv4;
+    unsigned* bar = (unsigned*)ctx->d_bar;
+    MRB_CUDA(cudaMemsetAsync(bar, 0, 64 * sizeof(unsigned), ctx->stream));
     const int4 *nbA = sb.nbA, *nbB = sb.nbB;
     const int2* nbC = sb.nbC;
     float4 *xa = sb.xa, *xb = sb.xb;
     int SS = S, its = iters;
-    void* args[] = {(void*)&code, (void*)&lb4, (void*)&ub4, (void*)&nbA, (void*)&nbB, (void*)&nbC,
-                    (void*)&xa, (void*)&xb, (void*)&SS, (void*)&its, (void*)&md};
+    int dbg = getenv("MRB_QP_DEBUG") ? atoi(getenv("MRB_QP_DEBUG")) : 0;   // 1: no barrier, 2: no work (timing aids; wrong results)
+    void* args[] = {(void*)&code, (void*)&lb4, (void*)&ub4, (void*)&inv4, (void*)&nbA, (void*)&nbB, (void*)&nbC,
+                    (void*)&xa, (void*)&xb, (void*)&SS, (void*)&its, (void*)&cap, (void*)&md, (void*)&bar, (void*)&dbg};
     MRB_CUDA(cudaEventRecord(ctx->ev[6], ctx->stream));
-    MRB_CUDA(cudaLaunchCooperativeKernel((void*)k_qp_strips, dim3(grid), dim3(block), args, 0, ctx->stream));
+    MRB_CUDA(cudaLaunchCooperativeKernel(kern, dim3(grid), dim3(block), args, smem, ctx->stream));
     MRB_CUDA(cudaEventRecord(ctx->ev[7], ctx->stream));
     ctx->launches++;
     *result = (iters % 2) ? sb.xb : sb.xa;
