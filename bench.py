@@ -272,10 +272,8 @@ def main():
     e2e_ms_total = sum(e2e_ms)
 
     # max over ranks
-    if world > 1:
-        t = torch.tensor([dev_ms_total, e2e_ms_total], dtype=torch.float64, device=vol_dev.device)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        dev_ms_total, e2e_ms_total = float(t[0]), float(t[1])
+    from mesh_reconstruction_b200.dist import max_over_ranks
+    dev_ms_total, e2e_ms_total = max_over_ranks([dev_ms_total, e2e_ms_total], device=vol_dev.device)
 
     B = stats[-1]["n_band"]
     updates_per_step = float(B) * args.iters * world
