@@ -1,0 +1,442 @@
+// mrb_bricks.cu -- stage 3 on 2x2x4 voxel bricks: the sweep kernel of mrb_optimize / mrb_reconstruct.
+//
+// Same arithmetic as the z-strip kernel in mrb_strips.cu (doStep, optimize/quadprog.cpp:45-61, on the
+// matrix-free operator of primeqp.cpp:7-112; see the header of mrb_strips.cu for the bit-exactness
+// argument), different data layout.  Profiling the strip kernel on B200 (profiles/r01_summary.md)
+// showed it bound by L1 data-pipe wavefronts, not by HBM or L2: every 4-voxel strip pulled 11 float4
+// of the iterate, 10 neighbour ids and 52 B of constants through the LSU.  A brick is 2(x) x 2(y) x
+// 4(z) voxels aligned to even x, even y and z % 4 == 0, stored as 4 consecutive float4 (64 B):
+//   * the radius-2 star of all 16 voxels reaches exactly ONE brick in each of the six directions, so
+//     a brick needs 6 neighbour ids (24 B) instead of 40 B per strip, and
+//   * the in-brick x/y neighbours are register values: 20 float4 + 8 float2 loads per 16 voxels
+//     instead of 44 float4 for four strips;
+//   * the per-voxel constants shrink to one 16-bit field (squared distance, diagonal d, volume==0,
+//     volume==1) decoded through two small constant-memory tables: margin = sqrtf(sq) and
+//     invdg = (float)(1.0/(double)d) -- the same values getsqrt (dfields.cpp:187) and primeQP
+//     (primeqp.cpp:196) compute.
+// Non-band voxels inside a brick have all tight bits 0, d = 0 (invdg 0), lb = -1000, ub = 1000 and
+// therefore stay exactly 0; they are never read with a non-zero coefficient.
+#include "mrb_internal.cuh"
+#include "mrb_compact.cuh"
+
+namespace mrb {
+
+#define MRB_VOXEL_LOOP(idx, n) \
+    for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < (n); idx += (size_t)gridDim.x * blockDim.x)
+
+static unsigned grid_for(mrb_ctx* ctx, size_t n, int block) {
+    size_t want = (n + block - 1) / block;
+    size_t cap = (size_t)ctx->sm_count * 16;
+    return (unsigned)(want < cap ? want : cap);
+}
+
+__constant__ float c_brick_sqrt[256];    // (float)sqrt((double)i): correctly rounded sqrtf(i)
+__constant__ float c_brick_invdg[32];    // (float)(1.0/(double)d), d = 1..18; 0 elsewhere
+
+static int upload_tables(int device) {
+    static bool ready[64] = {false};
+    if (ready[device & 63]) return MRB_OK;
+    float s[256], v[32];
+    for (int i = 0; i < 256; i++) s[i] = (float)sqrt((double)i);
+    for (int d = 0; d < 32; d++) v[d] = (d >= 1 && d <= 18) ? (float)(1.0 / (double)(float)d) : 0.0f;
+    MRB_CUDA(cudaMemcpyToSymbol(c_brick_sqrt, s, sizeof(s)));
+    MRB_CUDA(cudaMemcpyToSymbol(c_brick_invdg, v, sizeof(v)));
+    ready[device & 63] = true;
+    return MRB_OK;
+}
+
+struct BrickDims {
+    int nx, ny, nz;     // voxel grid
+    int bx, by, bz;     // brick grid = ceil(nx/2), ceil(ny/2), ceil(nz/4)
+    __host__ __device__ size_t count() const { return (size_t)bx * by * bz; }
+};
+
+struct ActiveBrickPred {
+    const uint8_t* flags;
+    BrickDims bd;
+    __device__ bool operator()(size_t p) const {
+        int Z = (int)(p % bd.bz);
+        size_t t = p / bd.bz;
+        int Y = (int)(t % bd.by);
+        int X = (int)(t / bd.by);
+        bool any = false;
+        for (int dx = 0; dx < 2; dx++)
+            for (int dy = 0; dy < 2; dy++) {
+                int x = 2 * X + dx, y = 2 * Y + dy;
+                if (x >= bd.nx || y >= bd.ny) continue;
+                const uint8_t* row = flags + ((size_t)x * bd.ny + y) * bd.nz;
+                for (int j = 0; j < 4; j++) {
+                    int z = 4 * Z + j;
+                    if (z < bd.nz) any = any || (row[z] & 1);
+                }
+            }
+        return any;
+    }
+};
+
+__global__ void k_fill_i32b(int* __restrict__ p, size_t n, int v) {
+    MRB_VOXEL_LOOP(idx, n) p[idx] = v;
+}
+__global__ void k_scatter_brick_ids(const int* __restrict__ bpos, int Q, int* __restrict__ bid) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < Q) bid[bpos[i]] = i;
+}
+
+// Voxel v = (dx*2+dy)*4 + j of brick (X,Y,Z) is (2X+dx, 2Y+dy, 4Z+j).
+// code.x: bits 0..15 T(v);  16..23 T(2X-1, y, z) [dy*4+j];  24..31 T(2X+2, y, z) [dy*4+j]
+// code.y: bits 0..7  T(x, 2Y-1, z) [dx*4+j];  8..15 T(x, 2Y+2, z) [dx*4+j];
+//         16..19 T(x, y, 4Z-1) [dx*2+dy];     20..23 T(x, y, 4Z+4) [dx*2+dy]
+// field (u16 per voxel): bits 0..7 squared distance, 8..12 d = 12 T(v) + six neighbour T,
+//         13 volume==0 (lb=-1000), 14 volume==1 (ub=1000), 15 in band
+__global__ void __launch_bounds__(128) k_brick_build(const float* __restrict__ vol, const uint8_t* __restrict__ sq,
+                                                     const uint8_t* __restrict__ flags, const int* __restrict__ bid,
+                                                     const int* __restrict__ bpos, int Q, BrickDims bd,
+                                                     uint2* __restrict__ code, uint4* __restrict__ fields,
+                                                     float4* __restrict__ x0, int4* __restrict__ nbA, int2* __restrict__ nbB,
+                                                     int* __restrict__ err) {
+    const size_t P = (size_t)Q + 1;      // plane stride of the SoA iterate: x[k][q], k = dx*2+dy
+    int q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= Q) return;
+    int p = bpos[q];
+    int Z = p % bd.bz;
+    int t = p / bd.bz;
+    int Y = t % bd.by;
+    int X = t / bd.by;
+    auto flag_at = [&](int x, int y, int z) -> uint32_t {
+        if (x < 0 || y < 0 || z < 0 || x >= bd.nx || y >= bd.ny || z >= bd.nz) return 0u;
+        return flags[((size_t)x * bd.ny + y) * bd.nz + z];
+    };
+    auto T = [&](int x, int y, int z) -> uint32_t { return (flag_at(x, y, z) >> 1) & 1u; };
+    uint32_t lo = 0, hi = 0;
+    uint32_t f16[16];
+    float xv[16];
+    bool bad = false;
+    for (int dx = 0; dx < 2; dx++)
+        for (int dy = 0; dy < 2; dy++)
+            for (int j = 0; j < 4; j++) {
+                const int k = dx * 2 + dy, v = k * 4 + j;
+                const int x = 2 * X + dx, y = 2 * Y + dy, z = 4 * Z + j;
+                const uint32_t fl = flag_at(x, y, z);
+                const uint32_t t0 = (fl >> 1) & 1u;
+                const uint32_t txm = T(x - 1, y, z), txp = T(x + 1, y, z), tym = T(x, y - 1, z), typ = T(x, y + 1, z);
+                const uint32_t tzm = T(x, y, z - 1), tzp = T(x, y, z + 1);
+                lo |= t0 << v;
+                if (dx == 0) lo |= txm << (16 + dy * 4 + j); else lo |= txp << (24 + dy * 4 + j);
+                if (dy == 0) hi |= tym << (dx * 4 + j); else hi |= typ << (8 + dx * 4 + j);
+                if (j == 0) hi |= tzm << (16 + k);
+                if (j == 3) hi |= tzp << (20 + k);
+                if (t0) {
+                    // a tight voxel needs its six neighbours inside the grid and in the band
+                    // (reference: grid.cpp:20-37 exit / indexMap -1 column, primeqp.cpp:40-75)
+                    bool in = x >= 1 && y >= 1 && z >= 1 && x <= bd.nx - 2 && y <= bd.ny - 2 && z <= bd.nz - 2;
+                    if (!in) bad = true;
+                    else bad = bad || !(flag_at(x - 1, y, z) & 1) || !(flag_at(x + 1, y, z) & 1) || !(flag_at(x, y - 1, z) & 1) ||
+                               !(flag_at(x, y + 1, z) & 1) || !(flag_at(x, y, z - 1) & 1) || !(flag_at(x, y, z + 1) & 1);
+                }
+                uint32_t f = (1u << 13) | (1u << 14);      // not in band: lb=-1000, ub=1000, d=0, margin 0
+                float xx = 0.0f;
+                if (fl & 1u) {
+                    const size_t a = ((size_t)x * bd.ny + y) * bd.nz + z;
+                    const uint32_t s = sq[a];
+                    const uint32_t dg = 12u * t0 + txm + txp + tym + typ + tzm + tzp;
+                    const float vv = vol[a];
+                    const float mg = c_brick_sqrt[s];
+                    f = s | (dg << 8) | (1u << 15);
+                    if (vv == 0.0f) f |= 1u << 13;          // getlb, primeqp.cpp:122-127
+                    if (vv == 1.0f) f |= 1u << 14;          // getub, primeqp.cpp:148-153
+                    const float l = (vv == 0.0f) ? -1000.0f : mg;
+                    const float u = (vv == 1.0f) ? 1000.0f : -mg;
+                    if (xx < l) xx = l;                     // x0 = clamp(0, lb, ub), primeqp.cpp:178-187
+                    if (xx > u) xx = u;
+                }
+                f16[v] = f;
+                xv[v] = xx;
+            }
+    if (bad) atomicExch(err, 1);
+    code[q] = make_uint2(lo, hi);
+    uint32_t w[8];
+    for (int i = 0; i < 8; i++) w[i] = f16[2 * i] | (f16[2 * i + 1] << 16);
+    fields[q] = make_uint4(w[0], w[1], w[2], w[3]);
+    fields[(size_t)Q + q] = make_uint4(w[4], w[5], w[6], w[7]);
+    for (int k = 0; k < 4; k++) x0[k * P + q] = make_float4(xv[4 * k], xv[4 * k + 1], xv[4 * k + 2], xv[4 * k + 3]);
+    auto nid = [&](bool ok, long long dp) {
+        int id = ok ? bid[p + dp] : -1;
+        return id >= 0 ? id : Q;             // slot Q = the all-zero dummy brick
+    };
+    const long long cx = (long long)bd.by * bd.bz, cy = bd.bz;
+    nbA[q] = make_int4(nid(X >= 1, -cx), nid(X <= bd.bx - 2, cx), nid(Y >= 1, -cy), nid(Y <= bd.by - 2, cy));
+    nbB[q] = make_int2(nid(Z >= 1, -1), nid(Z <= bd.bz - 2, 1));
+}
+
+// ---- sweep ---------------------------------------------------------------------------------------------------
+struct BrickRegs {
+    float own[4][4];      // [k = dx*2+dy][j]
+    float xm[4][4], xp[4][4], ym[4][4], yp[4][4];   // the four full neighbour bricks
+    float zl[4][2], zh[4][2];                       // last two z of brick Z-1, first two z of brick Z+1
+};
+
+__device__ __forceinline__ void put4(float (&d)[4], const float4 v) { d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w; }
+
+template <int DX, int DY, int J>
+__device__ __forceinline__ float brick_voxel(const BrickRegs& r, uint32_t lo, uint32_t hi, uint32_t field,
+                                             const float* __restrict__ s_sqrt, const float* __restrict__ s_inv) {
+    constexpr int K = DX * 2 + DY, V = K * 4 + J;
+    const bool a = lo & (1u << V);
+    const bool txm = DX == 0 ? (lo & (1u << (16 + DY * 4 + J))) : (lo & (1u << ((0 * 2 + DY) * 4 + J)));
+    const bool txp = DX == 0 ? (lo & (1u << ((1 * 2 + DY) * 4 + J))) : (lo & (1u << (24 + DY * 4 + J)));
+    const bool tym = DY == 0 ? (hi & (1u << (DX * 4 + J))) : (lo & (1u << ((DX * 2 + 0) * 4 + J)));
+    const bool typ = DY == 0 ? (lo & (1u << ((DX * 2 + 1) * 4 + J))) : (hi & (1u << (8 + DX * 4 + J)));
+    const bool tzm = J > 0 ? (lo & (1u << (V > 0 ? V - 1 : 0))) : (hi & (1u << (16 + K)));
+    const bool tzp = J < 3 ? (lo & (1u << (V + 1))) : (hi & (1u << (20 + K)));
+    const float xm2 = DX == 0 ? r.xm[0 * 2 + DY][J] : r.xm[1 * 2 + DY][J];
+    const float xm1 = DX == 0 ? r.xm[1 * 2 + DY][J] : r.own[0 * 2 + DY][J];
+    const float xp1 = DX == 0 ? r.own[1 * 2 + DY][J] : r.xp[0 * 2 + DY][J];
+    const float xp2 = DX == 0 ? r.xp[0 * 2 + DY][J] : r.xp[1 * 2 + DY][J];
+    const float ym2 = DY == 0 ? r.ym[DX * 2 + 0][J] : r.ym[DX * 2 + 1][J];
+    const float ym1 = DY == 0 ? r.ym[DX * 2 + 1][J] : r.own[DX * 2 + 0][J];
+    const float yp1 = DY == 0 ? r.own[DX * 2 + 1][J] : r.yp[DX * 2 + 0][J];
+    const float yp2 = DY == 0 ? r.yp[DX * 2 + 0][J] : r.yp[DX * 2 + 1][J];
+    const float zm2 = J >= 2 ? r.own[K][J >= 2 ? J - 2 : 0] : r.zl[K][J < 2 ? J : 0];
+    const float zm1 = J >= 1 ? r.own[K][J >= 1 ? J - 1 : 0] : r.zl[K][1];
+    const float zp1 = J <= 2 ? r.own[K][J <= 2 ? J + 1 : 0] : r.zh[K][0];
+    const float zp2 = J <= 1 ? r.own[K][J <= 1 ? J + 2 : 0] : r.zh[K][J >= 2 ? J - 2 : 0];
+    const float xc = r.own[K][J];
+    // c(+-e) = T(v) ? (t ? -4 : -2) : (t ? -2 : 0),  c(+-2e) = t ? 1 : 0; ascending band id order
+    const float cA = a ? -4.0f : -2.0f;
+    const float cB = a ? -2.0f : 0.0f;
+    float res = txm ? xm2 : 0.0f;
+    res = __fmaf_rn(txm ? cA : cB, xm1, res);
+    if (tym) res = __fadd_rn(res, ym2);
+    res = __fmaf_rn(tym ? cA : cB, ym1, res);
+    if (tzm) res = __fadd_rn(res, zm2);
+    res = __fmaf_rn(tzm ? cA : cB, zm1, res);
+    res = __fmaf_rn(tzp ? cA : cB, zp1, res);
+    if (tzp) res = __fadd_rn(res, zp2);
+    res = __fmaf_rn(typ ? cA : cB, yp1, res);
+    if (typ) res = __fadd_rn(res, yp2);
+    res = __fmaf_rn(txp ? cA : cB, xp1, res);
+    if (txp) res = __fadd_rn(res, xp2);
+    const float m = s_sqrt[field & 0xffu];
+    const float inv = s_inv[(field >> 8) & 31u];
+    const float lb = (field & (1u << 13)) ? -1000.0f : m;
+    const float ub = (field & (1u << 14)) ? 1000.0f : -m;
+    float t = __fsub_rn(xc, __fmul_rn(res, inv));
+    t = t * 0.5f;
+    if (t < lb) t = lb;
+    if (t > ub) t = ub;
+    return t;
+}
+
+template <int K>
+__device__ __forceinline__ float4 brick_strip(const BrickRegs& r, uint32_t lo, uint32_t hi, uint32_t w0, uint32_t w1,
+                                              const float* __restrict__ s_sqrt, const float* __restrict__ s_inv) {
+    constexpr int DX = K >> 1, DY = K & 1;
+    float4 o;
+    o.x = brick_voxel<DX, DY, 0>(r, lo, hi, w0 & 0xffffu, s_sqrt, s_inv);
+    o.y = brick_voxel<DX, DY, 1>(r, lo, hi, w0 >> 16, s_sqrt, s_inv);
+    o.z = brick_voxel<DX, DY, 2>(r, lo, hi, w1 & 0xffffu, s_sqrt, s_inv);
+    o.w = brick_voxel<DX, DY, 3>(r, lo, hi, w1 >> 16, s_sqrt, s_inv);
+    return o;
+}
+
+// Grid barrier: one arrival counter that only grows during a launch (see mrb_strips.cu).
+__device__ __forceinline__ void brick_grid_barrier(unsigned* bar, unsigned epoch, unsigned nblocks) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned target = epoch * nblocks;
+        asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(bar) : "memory");
+        unsigned v;
+        do {
+            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(bar) : "memory");
+        } while (v < target);
+    }
+    __syncthreads();
+}
+
+template <int Threads, int MinBlocks>
+__global__ void __launch_bounds__(Threads, MinBlocks) k_qp_bricks(const uint2* __restrict__ code, const uint4* __restrict__ fields,
+                                                                  const int4* __restrict__ nbA, const int2* __restrict__ nbB,
+                                                                  float4* xa, float4* xb, int Q, int iters,
+                                                                  unsigned* __restrict__ maxdelta_bits, unsigned* bar, int dbg) {
+    // contiguous range of bricks per block (bricks are ordered (X,Y,Z), Z fastest)
+    // margin / invdg tables in shared memory: conflict-free LDS (distinct entries sit in distinct banks)
+    __shared__ float s_sqrt[256];
+    __shared__ float s_inv[32];
+    for (int i = threadIdx.x; i < 256; i += Threads) s_sqrt[i] = c_brick_sqrt[i];
+    if (threadIdx.x < 32) s_inv[threadIdx.x] = c_brick_invdg[threadIdx.x];
+    __syncthreads();
+    const size_t P = (size_t)Q + 1;      // plane stride of the SoA iterate
+    const int q_begin = (int)((long long)Q * blockIdx.x / gridDim.x);
+    int q_end = (int)((long long)Q * (blockIdx.x + 1) / gridDim.x);
+    if (dbg & 2) q_end = q_begin;
+    const float4* in = xa;
+    float4* out = xb;
+    for (int it = 0; it < iters; it++) {
+        float dmax = 0.0f;
+        for (int q = q_begin + threadIdx.x; q < q_end; q += Threads) {
+            const int4 na = __ldg(nbA + q);
+            const int2 nz = __ldg(nbB + q);
+            const uint2 c = __ldg(code + q);
+            const uint4 f0 = __ldg(fields + q), f1 = __ldg(fields + (size_t)Q + q);
+            BrickRegs r;
+            // the iterate is rewritten by other SMs every sweep: plain loads, ordered by the grid barrier
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                const float4* pl = in + k * P;
+                put4(r.own[k], pl[q]);
+                put4(r.xm[k], pl[na.x]);
+                put4(r.xp[k], pl[na.y]);
+                put4(r.ym[k], pl[na.z]);
+                put4(r.yp[k], pl[na.w]);
+                const float2 l = *reinterpret_cast<const float2*>(reinterpret_cast<const float*>(pl + nz.x) + 2);
+                const float2 h = *reinterpret_cast<const float2*>(pl + nz.y);
+                r.zl[k][0] = l.x; r.zl[k][1] = l.y;
+                r.zh[k][0] = h.x; r.zh[k][1] = h.y;
+            }
+            const float4 o0 = brick_strip<0>(r, c.x, c.y, f0.x, f0.y, s_sqrt, s_inv);
+            const float4 o1 = brick_strip<1>(r, c.x, c.y, f0.z, f0.w, s_sqrt, s_inv);
+            const float4 o2 = brick_strip<2>(r, c.x, c.y, f1.x, f1.y, s_sqrt, s_inv);
+            const float4 o3 = brick_strip<3>(r, c.x, c.y, f1.z, f1.w, s_sqrt, s_inv);
+            out[q] = o0; out[P + q] = o1; out[2 * P + q] = o2; out[3 * P + q] = o3;
+            if (it == iters - 1) {
+                const float4 os[4] = {o0, o1, o2, o3};
+#pragma unroll
+                for (int k = 0; k < 4; k++)
+                    dmax = fmaxf(fmaxf(dmax, fmaxf(fabsf(os[k].x - r.own[k][0]), fabsf(os[k].y - r.own[k][1]))),
+                                 fmaxf(fabsf(os[k].z - r.own[k][2]), fabsf(os[k].w - r.own[k][3])));
+            }
+        }
+        if (it == iters - 1) {
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) dmax = fmaxf(dmax, __shfl_xor_sync(0xffffffffu, dmax, o));
+            if ((threadIdx.x & 31) == 0) atomicMax(maxdelta_bits, __float_as_uint(dmax));
+        }
+        const float4* t = in; in = out; out = (float4*)t;
+        if (it + 1 < iters && !(dbg & 1)) brick_grid_barrier(bar, (unsigned)(it + 1), gridDim.x);
+    }
+}
+
+// ---- feature reset + F assembly ---------------------------------------------------------------------------------
+__device__ __forceinline__ size_t brick_slot(const int* __restrict__ bid, const BrickDims& bd, size_t P, size_t idx) {
+    int z = (int)(idx % bd.nz);
+    size_t t = idx / bd.nz;
+    int y = (int)(t % bd.ny);
+    int x = (int)(t / bd.ny);
+    int q = bid[((size_t)(x >> 1) * bd.by + (y >> 1)) * bd.bz + (z >> 2)];
+    return ((size_t)((x & 1) * 2 + (y & 1)) * P + (size_t)q) * 4 + (size_t)(z & 3);
+}
+
+// getFeatureIndexes (primeqp.cpp:231-244) + the reset loop of runQP (quadprog.cpp:92-101): a single
+// feature voxel outside the band (-1 in the sorted id list) blocks every reset.
+__global__ void k_feat_check_b(const float* __restrict__ fmap, const uint8_t* __restrict__ flags, size_t n, int* __restrict__ any_off) {
+    MRB_VOXEL_LOOP(idx, n) if (fmap[idx] == 1.0f && !(flags[idx] & 1)) *any_off = 1;
+}
+__global__ void k_feat_apply_b(const float* __restrict__ fmap, const uint8_t* __restrict__ flags, const int* __restrict__ bid,
+                               BrickDims bd, size_t P, const int* __restrict__ any_off, float* __restrict__ x) {
+    if (*any_off) return;
+    MRB_VOXEL_LOOP(idx, (size_t)bd.nx * bd.ny * bd.nz)
+        if (fmap[idx] == 1.0f && (flags[idx] & 1)) x[brick_slot(bid, bd, P, idx)] = 0.2f;
+}
+
+// F = (2 volume - 1)(band_size + 1) off the band, the QP solution on it (quadprog.cpp:131-145)
+__global__ void __launch_bounds__(256) k_assemble_F_b(const float* __restrict__ vol, const uint8_t* __restrict__ flags,
+                                                      const int* __restrict__ bid, const float* __restrict__ x, BrickDims bd,
+                                                      size_t P, double scale, float* __restrict__ F) {
+    MRB_VOXEL_LOOP(idx, (size_t)bd.nx * bd.ny * bd.nz) {
+        float f;
+        if (flags[idx] & 1) f = x[brick_slot(bid, bd, P, idx)];
+        else f = (float)__dmul_rn(__dsub_rn(__dmul_rn(2.0, (double)vol[idx]), 1.0), scale);
+        F[idx] = f;
+    }
+}
+
+// Builds the bricks from the stage-2 byte grids, runs `iters` sweeps, applies the feature reset and writes F.
+// *n_bricks / *closure_err_host are outputs; ev[6], ev[7] bracket the sweep kernel.
+int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_t* flags, const uint8_t* sq, Dims d,
+                 int band_size, int iters, int using_features, float* F_dev, float* last_delta_host, int* n_bricks,
+                 int* closure_err_host) {
+    MRB_TRY(upload_tables(ctx->device));
+    BrickDims bd{d.nx, d.ny, d.nz, (d.nx + 1) / 2, (d.ny + 1) / 2, (d.nz + 3) / 4};
+    const size_t nb = bd.count();
+    int* bpos = nullptr;
+    int Q = 0;
+    MRB_TRY(compact(ctx, ActiveBrickPred{flags, bd}, nb, &bpos, &Q));
+    *n_bricks = Q;
+    *closure_err_host = 0;
+    if (last_delta_host) *last_delta_host = 0.0f;
+    int* bid = nullptr;
+    MRB_TRY(arena_alloc(ctx, nb, &bid));
+    MRB_LAUNCH(ctx, k_fill_i32b, grid_for(ctx, nb, 256), 256, 0, bid, nb, -1);
+    const size_t Qn = (size_t)(Q > 0 ? Q : 1);
+    uint2* code = nullptr;
+    uint4* fields = nullptr;
+    float4 *xa = nullptr, *xb = nullptr;
+    int4* nbA = nullptr;
+    int2* nbB = nullptr;
+    MRB_TRY(arena_alloc(ctx, Qn, &code));
+    MRB_TRY(arena_alloc(ctx, 2 * Qn, &fields));
+    MRB_TRY(arena_alloc(ctx, 4 * (Qn + 1), &xa));
+    MRB_TRY(arena_alloc(ctx, 4 * (Qn + 1), &xb));
+    MRB_TRY(arena_alloc(ctx, Qn, &nbA));
+    MRB_TRY(arena_alloc(ctx, Qn, &nbB));
+    const float* xres = (const float*)xa;
+    if (Q > 0) {
+        MRB_LAUNCH(ctx, k_scatter_brick_ids, cdiv(Q, 256), 256, 0, bpos, Q, bid);
+        int* err = ctx->d_mail + 24;
+        MRB_CUDA(cudaMemsetAsync(err, 0, sizeof(int), ctx->stream));
+        for (int k = 0; k < 4; k++) MRB_CUDA(cudaMemsetAsync(xa + (size_t)k * (Q + 1) + Q, 0, sizeof(float4), ctx->stream));
+        MRB_CUDA(cudaMemsetAsync(xb, 0, 4 * (Qn + 1) * sizeof(float4), ctx->stream));
+        MRB_LAUNCH(ctx, k_brick_build, cdiv(Q, 128), 128, 0, vol, sq, flags, bid, bpos, Q, bd, code, fields, xa, nbA, nbB, err);
+        MRB_CUDA(cudaMemcpyAsync(ctx->h_mail + 24, err, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+        MRB_CUDA(cudaStreamSynchronize(ctx->stream));
+        *closure_err_host = ctx->h_mail[24];
+        if (*closure_err_host) return MRB_OK;      // caller reports MRB_EBORDER
+        if (iters > 0) {
+            unsigned* md = (unsigned*)(ctx->d_mail + 8);
+            unsigned* bar = (unsigned*)ctx->d_bar;
+            MRB_CUDA(cudaMemsetAsync(md, 0, sizeof(unsigned), ctx->stream));
+            MRB_CUDA(cudaMemsetAsync(bar, 0, 64 * sizeof(unsigned), ctx->stream));
+            int threads = 256;
+            const char* e = getenv("MRB_QP_BRICK_THREADS");
+            if (e) threads = atoi(e);
+            void* kern = nullptr;
+            if (threads == 128) kern = (void*)k_qp_bricks<128, 4>;
+            else if (threads == 512) kern = (void*)k_qp_bricks<512, 1>;
+            else { threads = 256; kern = (void*)k_qp_bricks<256, 2>; }
+            int fit = 0;
+            MRB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&fit, kern, threads, 0));
+            if (fit < 1) { set_error("k_qp_bricks does not fit on an SM"); return MRB_ECUDA; }
+            int grid = fit * ctx->sm_count;
+            int need = (Q + threads - 1) / threads;
+            if (grid > need) grid = need;
+            int its = iters, QQ = Q;
+            int dbg = getenv("MRB_QP_DEBUG") ? atoi(getenv("MRB_QP_DEBUG")) : 0;   // timing aids (wrong results): 1 no barrier, 2 no work
+            void* args[] = {(void*)&code, (void*)&fields, (void*)&nbA, (void*)&nbB, (void*)&xa, (void*)&xb, (void*)&QQ,
+                            (void*)&its, (void*)&md, (void*)&bar, (void*)&dbg};
+            MRB_CUDA(cudaEventRecord(ctx->ev[6], ctx->stream));
+            MRB_CUDA(cudaLaunchCooperativeKernel(kern, dim3(grid), dim3(threads), args, 0, ctx->stream));
+            MRB_CUDA(cudaEventRecord(ctx->ev[7], ctx->stream));
+            ctx->launches++;
+            xres = (iters % 2) ? (const float*)xb : (const float*)xa;
+            if (last_delta_host) {
+                MRB_CUDA(cudaMemcpyAsync(ctx->h_mail + 8, md, sizeof(unsigned), cudaMemcpyDeviceToHost, ctx->stream));
+                MRB_CUDA(cudaStreamSynchronize(ctx->stream));
+                unsigned bits = (unsigned)ctx->h_mail[8];
+                memcpy(last_delta_host, &bits, sizeof(float));
+            }
+        }
+    }
+    const size_t n = d.count();
+    if (using_features && fmap && Q > 0) {
+        int* flag = ctx->d_mail + 16;
+        MRB_CUDA(cudaMemsetAsync(flag, 0, sizeof(int), ctx->stream));
+        const unsigned g = grid_for(ctx, n, 256);
+        MRB_LAUNCH(ctx, k_feat_check_b, g, 256, 0, fmap, flags, n, flag);
+        MRB_LAUNCH(ctx, k_feat_apply_b, g, 256, 0, fmap, flags, bid, bd, (size_t)Q + 1, flag, (float*)xres);
+    }
+    MRB_LAUNCH(ctx, k_assemble_F_b, grid_for(ctx, n, 256), 256, 0, vol, flags, bid, xres, bd, (size_t)Q + 1, (double)band_size + 1.0,
+               F_dev);
+    return MRB_OK;
+}
+
+}  // namespace mrb

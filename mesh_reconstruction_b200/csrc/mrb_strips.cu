@@ -468,7 +468,14 @@ __global__ void __launch_bounds__(Threads) k_qp_strips(const uint32_t* __restric
             uint32_t c;
             float4 lb, ub, inv;
             if (Mode == 2) { c = __ldcs(code + s); lb = ldcs4(lb4 + s); ub = ldcs4(ub4 + s); inv = ldcs4(inv4 + s); }
+            else if (dbg & 4) {     // tuning aid: no lb/ub/inv traffic (wrong results)
+                c = __ldg(code + s);
+                lb = make_float4(-1000.f, -1000.f, -1000.f, -1000.f); ub = make_float4(1000.f, 1000.f, 1000.f, 1000.f);
+                inv = make_float4(0.055f, 0.055f, 0.055f, 0.055f);
+            }
             else { c = __ldg(code + s); lb = __ldg(lb4 + s); ub = __ldg(ub4 + s); inv = __ldg(inv4 + s); }
+            if (dbg & 8) { id.a.x = s; id.a.z = s; id.b.w = s; id.c.y = s; }   // tuning aid: +-2 rows alias the own row
+            if (dbg & 16) { id.a.y = s; id.a.w = s; id.b.z = s; id.c.x = s; }  // tuning aid: +-1 rows alias the own row
             // the iterate is rewritten by other SMs every sweep: plain loads, ordered by the grid barrier
             const float4 xc = ld4(in + s);
             const float4 xm2 = ld4(in + id.a.x), xm1 = ld4(in + id.a.y), ym2 = ld4(in + id.a.z), ym1 = ld4(in + id.a.w);
@@ -596,6 +603,10 @@ __global__ void __launch_bounds__(256) k_assemble_F_s(const float* __restrict__ 
     }
 }
 
+int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_t* flags, const uint8_t* sq, Dims d,
+                 int band_size, int iters, int using_features, float* F_dev, float* last_delta_host, int* n_bricks,
+                 int* closure_err_host);
+
 // Stages 1-3 on device pointers.  F_dev: N^3 floats.  Records events ev[0..3] (+ ev[6..7] around the sweeps).
 int optimize_strips(mrb_ctx* ctx, const float* vol, const float* fmap, Dims d, int using_features, int band_size,
                     int iters, float* F_dev, mrb_qp_stats* stats) {
@@ -619,6 +630,40 @@ int optimize_strips(mrb_ctx* ctx, const float* vol, const float* fmap, Dims d, i
         MRB_CUDA(cudaEventRecord(ctx->ev[1], ctx->stream));
         MRB_LAUNCH(ctx, k_tight, g, 256, 0, sq, d, b1);
         MRB_LAUNCH(ctx, k_band_flags, g, 256, 0, b1, d, flags, counts);
+        const char* layout = getenv("MRB_QP_LAYOUT");          // tuning knob: "strips" selects the z-strip kernel
+        if (!(layout && strcmp(layout, "strips") == 0)) {
+            // default: 2x2x4 bricks (mrb_bricks.cu)
+            MRB_CUDA(cudaMemcpyAsync(ctx->h_mail + 32, counts, 4 * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+            int Q = 0, closure_err = 0;
+            float last_delta = 0.0f;
+            MRB_TRY(bricks_solve(ctx, vol, fmap, flags, sq, d, band_size, iters, using_features, F_dev,
+                                 stats ? &last_delta : nullptr, &Q, &closure_err));
+            MRB_CUDA(cudaEventRecord(ctx->ev[3], ctx->stream));
+            MRB_CUDA(cudaStreamSynchronize(ctx->stream));
+            if (ctx->h_mail[34] || closure_err) {
+                set_error("narrow band touches the grid border (tight-band voxel on the border or with a neighbour outside "
+                          "the band); the reference exits here (grid.cpp:20-37 via primeqp.cpp:40-75)");
+                return MRB_EBORDER;
+            }
+            if (stats) {
+                stats->n_band = ctx->h_mail[32];
+                stats->n_tight = ctx->h_mail[33];
+                stats->iters = iters;
+                stats->last_max_delta = last_delta;
+                cudaEventElapsedTime(&stats->ms_dfield, ctx->ev[0], ctx->ev[1]);
+                stats->ms_mc = 0.0f;
+                stats->ms_qp_kernel = 0.0f;
+                stats->ms_band = 0.0f;
+                if (iters > 0 && Q > 0) {
+                    cudaEventElapsedTime(&stats->ms_qp_kernel, ctx->ev[6], ctx->ev[7]);
+                    cudaEventElapsedTime(&stats->ms_band, ctx->ev[1], ctx->ev[6]);
+                    cudaEventElapsedTime(&stats->ms_qp, ctx->ev[6], ctx->ev[3]);
+                } else {
+                    cudaEventElapsedTime(&stats->ms_qp, ctx->ev[1], ctx->ev[3]);
+                }
+            }
+            return MRB_OK;
+        }
         MRB_TRY(build_strips(ctx, vol, MarginSq{sq}, flags, d, &sb));
     } else {
         // wide bands: full exact EDT + float morphology, then the same strip machinery
