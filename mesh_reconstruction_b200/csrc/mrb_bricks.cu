@@ -222,9 +222,10 @@ __device__ __forceinline__ float brick_voxel(const BrickRegs& r, uint32_t lo, ui
     const float ub = (field & (1u << 14)) ? 1000.0f : -m;
     float t = __fsub_rn(xc, __fmul_rn(res, inv));
     t = t * 0.5f;
-    if (t < lb) t = lb;
-    if (t > ub) t = ub;
-    return t;
+    // "if (t < lb) t = lb; if (t > ub) t = ub;" (quadprog.cpp:58-59) == min(max(t, lb), ub) for lb <= ub and no
+    // NaN; the two forms can only differ in the sign of a zero result, which no later stage can observe
+    // (see mrb_strips.cu header: res never becomes -0, val < iso and the interpolation treat +-0 alike).
+    return fminf(fmaxf(t, lb), ub);
 }
 
 template <int K>
@@ -253,11 +254,63 @@ __device__ __forceinline__ void brick_grid_barrier(unsigned* bar, unsigned epoch
     __syncthreads();
 }
 
+// ---- neighbour-only synchronisation --------------------------------------------------------------------------
+// Block b owns bricks [Q*b/G, Q*(b+1)/G).  Its sweep k+1 reads bricks owned by a few other blocks only
+// (bricks are ordered (X,Y,Z): the X+-1 neighbours sit about one x-plane of bricks away), so instead of
+// a grid-wide barrier every block publishes "sweep k done" in its own progress word and waits for the
+// progress words of exactly the blocks [lo_b, hi_b] that own one of its neighbour bricks.  The same
+// condition covers the write-after-read hazard of the ping-pong buffers (a neighbour that finished
+// sweep k no longer reads the buffer sweep k+1 overwrites).  All blocks are co-resident (cooperative
+// launch), so the waits cannot deadlock.
+__host__ __device__ __forceinline__ int brick_owner(int q, int Q, int G) {
+    int b = (int)(((long long)q * G) / Q);
+    while (b + 1 < G && (int)(((long long)Q * (b + 1)) / G) <= q) b++;
+    while (b > 0 && (int)(((long long)Q * b) / G) > q) b--;
+    return b;
+}
+
+__global__ void k_block_ranges_init(int* __restrict__ lo, int* __restrict__ hi, int G) {
+    int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b < G) { lo[b] = b; hi[b] = b; }
+}
+__global__ void k_block_ranges(const int4* __restrict__ nbA, const int2* __restrict__ nbB, int Q, int G,
+                               int* __restrict__ lo, int* __restrict__ hi) {
+    int q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= Q) return;
+    const int b = brick_owner(q, Q, G);
+    const int4 a = nbA[q];
+    const int2 z = nbB[q];
+    const int n[6] = {a.x, a.y, a.z, a.w, z.x, z.y};
+    int mn = b, mx = b;
+    for (int i = 0; i < 6; i++)
+        if (n[i] < Q) { int o = brick_owner(n[i], Q, G); mn = min(mn, o); mx = max(mx, o); }
+    if (mn < b) atomicMin(&lo[b], mn);
+    if (mx > b) atomicMax(&hi[b], mx);
+}
+
+static const int kProgressStride = 32;     // one 128-byte line per block
+
+__device__ __forceinline__ void neighbour_sync(unsigned* progress, unsigned epoch, int lo, int hi) {
+    __syncthreads();                                   // the block's stores of this sweep are issued
+    if (threadIdx.x == 0)
+        asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(progress + (size_t)blockIdx.x * kProgressStride), "r"(epoch) : "memory");
+    for (int c = lo + (int)threadIdx.x; c <= hi; c += blockDim.x) {
+        if (c == (int)blockIdx.x) continue;
+        unsigned v;
+        do {
+            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(progress + (size_t)c * kProgressStride) : "memory");
+        } while (v < epoch);
+    }
+    __syncthreads();
+}
+
 template <int Threads, int MinBlocks>
 __global__ void __launch_bounds__(Threads, MinBlocks) k_qp_bricks(const uint2* __restrict__ code, const uint4* __restrict__ fields,
                                                                   const int4* __restrict__ nbA, const int2* __restrict__ nbB,
                                                                   float4* xa, float4* xb, int Q, int iters,
-                                                                  unsigned* __restrict__ maxdelta_bits, unsigned* bar, int dbg) {
+                                                                  unsigned* __restrict__ maxdelta_bits, unsigned* bar, int dbg,
+                                                                  const int* __restrict__ blk_lo, const int* __restrict__ blk_hi,
+                                                                  unsigned* progress) {
     // contiguous range of bricks per block (bricks are ordered (X,Y,Z), Z fastest)
     // margin / invdg tables in shared memory: conflict-free LDS (distinct entries sit in distinct banks)
     __shared__ float s_sqrt[256];
@@ -269,6 +322,7 @@ __global__ void __launch_bounds__(Threads, MinBlocks) k_qp_bricks(const uint2* _
     const int q_begin = (int)((long long)Q * blockIdx.x / gridDim.x);
     int q_end = (int)((long long)Q * (blockIdx.x + 1) / gridDim.x);
     if (dbg & 2) q_end = q_begin;
+    const int nlo = blk_lo[blockIdx.x], nhi = blk_hi[blockIdx.x];
     const float4* in = xa;
     float4* out = xb;
     for (int it = 0; it < iters; it++) {
@@ -312,7 +366,10 @@ __global__ void __launch_bounds__(Threads, MinBlocks) k_qp_bricks(const uint2* _
             if ((threadIdx.x & 31) == 0) atomicMax(maxdelta_bits, __float_as_uint(dmax));
         }
         const float4* t = in; in = out; out = (float4*)t;
-        if (it + 1 < iters && !(dbg & 1)) brick_grid_barrier(bar, (unsigned)(it + 1), gridDim.x);
+        if (it + 1 < iters && !(dbg & 1)) {
+            if (dbg & 4) brick_grid_barrier(bar, (unsigned)(it + 1), gridDim.x);     // tuning aid: global barrier
+            else neighbour_sync(progress, (unsigned)(it + 1), nlo, nhi);
+        }
     }
 }
 
@@ -402,6 +459,9 @@ int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_
             void* kern = nullptr;
             if (threads == 128) kern = (void*)k_qp_bricks<128, 4>;
             else if (threads == 512) kern = (void*)k_qp_bricks<512, 1>;
+            else if (threads == 1285) { threads = 128; kern = (void*)k_qp_bricks<128, 5>; }   // tuning: <=102 registers
+            else if (threads == 1286) { threads = 128; kern = (void*)k_qp_bricks<128, 6>; }   // tuning: <=85 registers
+            else if (threads == 2563) { threads = 256; kern = (void*)k_qp_bricks<256, 3>; }   // tuning: <=85 registers
             else { threads = 256; kern = (void*)k_qp_bricks<256, 2>; }
             int fit = 0;
             MRB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&fit, kern, threads, 0));
@@ -409,10 +469,19 @@ int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_
             int grid = fit * ctx->sm_count;
             int need = (Q + threads - 1) / threads;
             if (grid > need) grid = need;
+            // neighbour block ranges + progress words for the point-to-point synchronisation
+            int *blk_lo = nullptr, *blk_hi = nullptr;
+            unsigned* progress = nullptr;
+            MRB_TRY(arena_alloc(ctx, (size_t)grid, &blk_lo));
+            MRB_TRY(arena_alloc(ctx, (size_t)grid, &blk_hi));
+            MRB_TRY(arena_alloc(ctx, (size_t)grid * kProgressStride, &progress));
+            MRB_CUDA(cudaMemsetAsync(progress, 0, (size_t)grid * kProgressStride * sizeof(unsigned), ctx->stream));
+            MRB_LAUNCH(ctx, k_block_ranges_init, cdiv(grid, 256), 256, 0, blk_lo, blk_hi, grid);
+            MRB_LAUNCH(ctx, k_block_ranges, cdiv(Q, 256), 256, 0, nbA, nbB, Q, grid, blk_lo, blk_hi);
             int its = iters, QQ = Q;
             int dbg = getenv("MRB_QP_DEBUG") ? atoi(getenv("MRB_QP_DEBUG")) : 0;   // timing aids (wrong results): 1 no barrier, 2 no work
             void* args[] = {(void*)&code, (void*)&fields, (void*)&nbA, (void*)&nbB, (void*)&xa, (void*)&xb, (void*)&QQ,
-                            (void*)&its, (void*)&md, (void*)&bar, (void*)&dbg};
+                            (void*)&its, (void*)&md, (void*)&bar, (void*)&dbg, (void*)&blk_lo, (void*)&blk_hi, (void*)&progress};
             MRB_CUDA(cudaEventRecord(ctx->ev[6], ctx->stream));
             MRB_CUDA(cudaLaunchCooperativeKernel(kern, dim3(grid), dim3(threads), args, 0, ctx->stream));
             MRB_CUDA(cudaEventRecord(ctx->ev[7], ctx->stream));
