@@ -310,7 +310,7 @@ __global__ void __launch_bounds__(Threads, MinBlocks) k_qp_bricks(const uint2* _
                                                                   float4* xa, float4* xb, int Q, int iters,
                                                                   unsigned* __restrict__ maxdelta_bits, unsigned* bar, int dbg,
                                                                   const int* __restrict__ blk_lo, const int* __restrict__ blk_hi,
-                                                                  unsigned* progress) {
+                                                                  unsigned* progress, int cap) {
     // contiguous range of bricks per block (bricks are ordered (X,Y,Z), Z fastest)
     // margin / invdg tables in shared memory: conflict-free LDS (distinct entries sit in distinct banks)
     __shared__ float s_sqrt[256];
@@ -323,15 +323,37 @@ __global__ void __launch_bounds__(Threads, MinBlocks) k_qp_bricks(const uint2* _
     int q_end = (int)((long long)Q * (blockIdx.x + 1) / gridDim.x);
     if (dbg & 2) q_end = q_begin;
     const int nlo = blk_lo[blockIdx.x], nhi = blk_hi[blockIdx.x];
+    // The per-brick constants (6 neighbour ids, code, fields: 64 B) never change: when a block's share
+    // fits they are copied to shared memory once, which takes the ids -> iterate dependent L2 round
+    // trip out of every sweep.
+    extern __shared__ uint4 s_dyn[];
+    uint4* s_f0 = s_dyn;
+    uint4* s_f1 = s_dyn + cap;
+    int4* s_na = (int4*)(s_dyn + 2 * cap);
+    int2* s_nz = (int2*)(s_dyn + 3 * cap);
+    uint2* s_code = (uint2*)(s_nz + cap);
+    const bool smem_consts = cap > 0;
+    if (smem_consts) {
+        for (int q = q_begin + threadIdx.x; q < q_end; q += Threads) {
+            const int l = q - q_begin;
+            s_na[l] = __ldg(nbA + q); s_nz[l] = __ldg(nbB + q); s_code[l] = __ldg(code + q);
+            s_f0[l] = __ldg(fields + q); s_f1[l] = __ldg(fields + (size_t)Q + q);
+        }
+        __syncthreads();
+    }
     const float4* in = xa;
     float4* out = xb;
     for (int it = 0; it < iters; it++) {
         float dmax = 0.0f;
         for (int q = q_begin + threadIdx.x; q < q_end; q += Threads) {
-            const int4 na = __ldg(nbA + q);
-            const int2 nz = __ldg(nbB + q);
-            const uint2 c = __ldg(code + q);
-            const uint4 f0 = __ldg(fields + q), f1 = __ldg(fields + (size_t)Q + q);
+            int4 na; int2 nz; uint2 c; uint4 f0, f1;
+            if (smem_consts) {            // brick constants resident in shared memory (copied once)
+                const int l = q - q_begin;
+                na = s_na[l]; nz = s_nz[l]; c = s_code[l]; f0 = s_f0[l]; f1 = s_f1[l];
+            } else {
+                na = __ldg(nbA + q); nz = __ldg(nbB + q); c = __ldg(code + q);
+                f0 = __ldg(fields + q); f1 = __ldg(fields + (size_t)Q + q);
+            }
             BrickRegs r;
             // the iterate is rewritten by other SMs every sweep: plain loads, ordered by the grid barrier
 #pragma unroll
@@ -478,12 +500,16 @@ int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_
             MRB_CUDA(cudaMemsetAsync(progress, 0, (size_t)grid * kProgressStride * sizeof(unsigned), ctx->stream));
             MRB_LAUNCH(ctx, k_block_ranges_init, cdiv(grid, 256), 256, 0, blk_lo, blk_hi, grid);
             MRB_LAUNCH(ctx, k_block_ranges, cdiv(Q, 256), 256, 0, nbA, nbB, Q, grid, blk_lo, blk_hi);
+            int cap = (Q + grid - 1) / grid + 1;
+            size_t smem = (size_t)cap * 64;
+            if (getenv("MRB_QP_BRICK_NOSMEM") || smem > 96 * 1024 / (size_t)fit) { cap = 0; smem = 0; }
+            if (smem > 48 * 1024) MRB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
             int its = iters, QQ = Q;
             int dbg = getenv("MRB_QP_DEBUG") ? atoi(getenv("MRB_QP_DEBUG")) : 0;   // timing aids (wrong results): 1 no barrier, 2 no work
             void* args[] = {(void*)&code, (void*)&fields, (void*)&nbA, (void*)&nbB, (void*)&xa, (void*)&xb, (void*)&QQ,
-                            (void*)&its, (void*)&md, (void*)&bar, (void*)&dbg, (void*)&blk_lo, (void*)&blk_hi, (void*)&progress};
+                            (void*)&its, (void*)&md, (void*)&bar, (void*)&dbg, (void*)&blk_lo, (void*)&blk_hi, (void*)&progress, (void*)&cap};
             MRB_CUDA(cudaEventRecord(ctx->ev[6], ctx->stream));
-            MRB_CUDA(cudaLaunchCooperativeKernel(kern, dim3(grid), dim3(threads), args, 0, ctx->stream));
+            MRB_CUDA(cudaLaunchCooperativeKernel(kern, dim3(grid), dim3(threads), args, smem, ctx->stream));
             MRB_CUDA(cudaEventRecord(ctx->ev[7], ctx->stream));
             ctx->launches++;
             xres = (iters % 2) ? (const float*)xb : (const float*)xa;
