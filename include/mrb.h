@@ -186,6 +186,15 @@ void mrb_options_default(mrb_options* o);
 int mrb_reconstruct(mrb_ctx* ctx, const float* volume, const int dims[3], const mrb_options* opt,
                     int device_out, mrb_mesh* out, mrb_qp_stats* stats);
 
+/* Object-parallel batch (BASELINE config 5: many independent small objects): the fused path on `nobj`
+ * grids of identical dims stored back to back ([nobj][nx][ny][nz], host or device memory).  The meshes are
+ * returned concatenated (host memory, release with mrb_mesh_free): object o owns vertices
+ * [vert_off[o], vert_off[o+1]) and faces [face_off[o], face_off[o+1]); face entries are vertex ids local
+ * to their object, exactly what mcubes (mcubes.cpp:592-662) would write for that object alone.
+ * vert_off / face_off: nobj+1 ints each (host). */
+int mrb_reconstruct_batch(mrb_ctx* ctx, const float* volumes, const int dims[3], int nobj,
+                          const mrb_options* opt, mrb_mesh* out, int* vert_off, int* face_off);
+
 #ifdef __cplusplus
 }
 #endif

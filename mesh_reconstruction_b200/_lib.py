@@ -61,6 +61,8 @@ SYMBOLS = {
     "mrb_options_default": (None, [C.POINTER(Options)]),
     "mrb_reconstruct": (C.c_int, [_VP, _VP, c_int_p, C.POINTER(Options), C.c_int, C.POINTER(Mesh),
                                   C.POINTER(QPStats)]),
+    "mrb_reconstruct_batch": (C.c_int, [_VP, _VP, c_int_p, C.c_int, C.POINTER(Options), C.POINTER(Mesh), c_int_p,
+                                        c_int_p]),
 }
 
 _lib = None

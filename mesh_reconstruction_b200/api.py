@@ -260,6 +260,28 @@ class Context:
         return verts, faces
 
 
+def _batch(self, volumes, band_size=4, iters=500, isolevel=0.0):
+    """Object-parallel batch: volumes [nobj, nx, ny, nz] -> list of (verts, faces) per object."""
+    kv, pv, shape, like = self._in(volumes)
+    if len(shape) != 4:
+        raise ValueError("volumes must be [nobj, nx, ny, nz]")
+    nobj = int(shape[0])
+    opt = L.Options()
+    self.lib.mrb_options_default(C.byref(opt))
+    opt.band_size, opt.iters, opt.isolevel = int(band_size), int(iters), float(isolevel)
+    m = L.Mesh()
+    voff = (C.c_int * (nobj + 1))()
+    foff = (C.c_int * (nobj + 1))()
+    self._check(self.lib.mrb_reconstruct_batch(self.h, pv, self._dims(shape[1:]), nobj, C.byref(opt), C.byref(m), voff, foff))
+    verts = np.ctypeslib.as_array(m.verts, shape=(max(m.nverts, 1), 3))[:m.nverts].copy()
+    faces = np.ctypeslib.as_array(m.faces, shape=(max(m.nfaces, 1), 3))[:m.nfaces].copy()
+    self.lib.mrb_mesh_free(C.byref(m))
+    return [(verts[voff[o]:voff[o + 1]], faces[foff[o]:foff[o + 1]]) for o in range(nobj)]
+
+
+Context.reconstruct_batch = _batch
+
+
 def _stats(st):
     return {k: getattr(st, k) for k, _ in L.QPStats._fields_}
 

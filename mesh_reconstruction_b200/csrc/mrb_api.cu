@@ -9,6 +9,7 @@
 #include <stdlib.h>
 #include <string.h>
 #include <string>
+#include <vector>
 
 namespace mrb {
 
@@ -77,6 +78,52 @@ int mrb_reconstruct(mrb_ctx* ctx, const float* volume, const int dims[3], const 
     MRB_CUDA(cudaEventRecord(ctx->ev[5], ctx->stream));
     MRB_TRY(export_mesh(ctx, verts, faces, nv, nf, device_out, out));
     if (stats) cudaEventElapsedTime(&stats->ms_mc, ctx->ev[4], ctx->ev[5]);
+    return MRB_OK;
+}
+
+int mrb_reconstruct_batch(mrb_ctx* ctx, const float* volumes, const int dims[3], int nobj, const mrb_options* opt,
+                          mrb_mesh* out, int* vert_off, int* face_off) {
+    MRB_REQUIRE(ctx && volumes && dims && out && vert_off && face_off && nobj >= 0, "bad argument");
+    mrb_options o;
+    if (opt) o = *opt; else mrb_options_default(&o);
+    MRB_REQUIRE(o.band_size >= 1 && o.band_size <= 64 && o.iters >= 0, "bad band_size / iters");
+    MRB_REQUIRE(!o.using_features, "the --feature-detection path is not implemented on the GPU yet");
+    MRB_CUDA(cudaSetDevice(ctx->device));
+    memset(out, 0, sizeof(*out));
+    Dims d = mkdims(dims);
+    MRB_REQUIRE(d.count() <= (size_t)0x7fffffff, "grid too large");
+    std::vector<float> verts;
+    std::vector<int> faces;
+    vert_off[0] = 0; face_off[0] = 0;
+    for (int ob = 0; ob < nobj; ob++) {
+        MRB_TRY(ctx->arena.reset());
+        const float* dv = nullptr;
+        MRB_TRY(stage_in(ctx, volumes + (size_t)ob * d.count(), d.count(), &dv));
+        float* F = nullptr;
+        MRB_TRY(arena_alloc(ctx, d.count(), &F));
+        int rc = optimize_dev(ctx, dv, nullptr, d, 0, o.band_size, o.iters, F, nullptr);
+        if (rc != MRB_OK) { std::string m = mrb_last_error(); set_error("object %d: %s", ob, m.c_str()); return rc; }
+        float* dverts = nullptr;
+        int* dfaces = nullptr;
+        int nv = 0, nf = 0;
+        MRB_TRY(dev_mcubes(ctx, F, d, o.isolevel, &dverts, &dfaces, &nv, &nf));
+        size_t v0 = verts.size(), f0 = faces.size();
+        verts.resize(v0 + (size_t)nv * 3);
+        faces.resize(f0 + (size_t)nf * 3);
+        if (nv) MRB_CUDA(cudaMemcpyAsync(verts.data() + v0, dverts, sizeof(float) * 3 * (size_t)nv, cudaMemcpyDeviceToHost, ctx->stream));
+        if (nf) MRB_CUDA(cudaMemcpyAsync(faces.data() + f0, dfaces, sizeof(int) * 3 * (size_t)nf, cudaMemcpyDeviceToHost, ctx->stream));
+        MRB_TRY(sync(ctx));
+        vert_off[ob + 1] = vert_off[ob] + nv;
+        face_off[ob + 1] = face_off[ob] + nf;
+    }
+    out->nverts = (int)(verts.size() / 3);
+    out->nfaces = (int)(faces.size() / 3);
+    out->on_device = 0;
+    out->verts = (float*)malloc(sizeof(float) * (verts.size() ? verts.size() : 1));
+    out->faces = (int*)malloc(sizeof(int) * (faces.size() ? faces.size() : 1));
+    if (!out->verts || !out->faces) { set_error("mrb_reconstruct_batch: host malloc failed"); return MRB_ENOMEM; }
+    if (!verts.empty()) memcpy(out->verts, verts.data(), sizeof(float) * verts.size());
+    if (!faces.empty()) memcpy(out->faces, faces.data(), sizeof(int) * faces.size());
     return MRB_OK;
 }
 
