@@ -78,6 +78,20 @@ int mrb_sqrt(mrb_ctx* ctx, const float* in, const int dims[3], float* out);
 /* dfield_gpu (dfields.cu:161-200) == getsqrt(getsqdist(fastPerim(volume))). */
 int mrb_dfield(mrb_ctx* ctx, const float* volume, const int dims[3], float* margin);
 
+/* ---- feature pre-pass (distance_fields/, only consumed with --feature-detection) --------- */
+/* The normals come from Eigen::SelfAdjointEigenSolver in the reference; here from the deterministic
+ * Jacobi solver of include/mrb_eig3.h (parity unpinned against the reference, exact against our oracle). */
+/* getSurface (dfields.cpp:322-338): x-fastest linear indexes of occupied voxels (== 1) with an empty (== 0)
+ * voxel in their 3x3x3 window, in (x,y,z) order.  idx_out may be NULL (count only). */
+int mrb_get_surface(mrb_ctx* ctx, const float* volume, const int dims[3], int* idx_out, int capacity, int* n_out);
+/* getSurfaceNormals (dfields.cpp:341-349): one unit normal (3 floats) per surface voxel. */
+int mrb_surface_normals(mrb_ctx* ctx, const float* volume, const int dims[3], const int* surface, int n,
+                        float* normals_out);
+/* getFeatureMap (dfields.cpp:447-555): 1 on the surface voxels of every boundary cell whose minimum pairwise
+ * normal dot product is below `threshold`, else 0.  surface_map = getIndexMap(volume, surface). */
+int mrb_feature_map(mrb_ctx* ctx, const float* volume, const float* surface_map, const float* normals, int nnormals,
+                    const int dims[3], float threshold, float* feature_map_out);
+
 /* ---- stage 2: narrow band (narrow_band/, grid/) ------------------------ */
 /* erode_grid / dilate_grid (narrowBand.cpp:10-79): 6-neighbour, interior voxels only. */
 int mrb_erode(mrb_ctx* ctx, const float* in, const int dims[3], float* out);

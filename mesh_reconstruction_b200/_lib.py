@@ -44,6 +44,9 @@ SYMBOLS = {
     "mrb_sqdist": (C.c_int, [_VP, _VP, c_int_p, _VP]),
     "mrb_sqrt": (C.c_int, [_VP, _VP, c_int_p, _VP]),
     "mrb_dfield": (C.c_int, [_VP, _VP, c_int_p, _VP]),
+    "mrb_get_surface": (C.c_int, [_VP, _VP, c_int_p, _VP, C.c_int, c_int_p]),
+    "mrb_surface_normals": (C.c_int, [_VP, _VP, c_int_p, _VP, C.c_int, _VP]),
+    "mrb_feature_map": (C.c_int, [_VP, _VP, _VP, _VP, C.c_int, c_int_p, C.c_float, _VP]),
     "mrb_erode": (C.c_int, [_VP, _VP, c_int_p, _VP]),
     "mrb_dilate": (C.c_int, [_VP, _VP, c_int_p, _VP]),
     "mrb_create_bands": (C.c_int, [_VP, _VP, c_int_p, C.c_float, _VP, _VP]),

@@ -111,6 +111,32 @@ class Context:
     def dfield_gpu(self, volume):
         return self._grid_op(self.lib.mrb_dfield, volume)
 
+    # ---- feature pre-pass (dfields.h:49-67) -------------------------------------------------------
+    def getSurface(self, volume):
+        keep, p, shape, like = self._in(volume)
+        n = C.c_int(0)
+        self._check(self.lib.mrb_get_surface(self.h, p, self._dims(shape), None, 0, C.byref(n)))
+        out, op = self._out((max(n.value, 1),), like, np.int32)
+        if n.value:
+            self._check(self.lib.mrb_get_surface(self.h, p, self._dims(shape), op, n.value, C.byref(n)))
+        return out[:n.value]
+
+    def getSurfaceNormals(self, volume, surface):
+        kv, pv, shape, like = self._in(volume)
+        ks, ps, sshape, _ = self._in(surface, np.int32)
+        n = int(sshape[0])
+        out, op = self._out((max(n, 1), 3), like)
+        self._check(self.lib.mrb_surface_normals(self.h, pv, self._dims(shape), ps, n, op))
+        return out[:n]
+
+    def getFeatureMap(self, volume, surfaceMap, normals, threshold):
+        kv, pv, shape, like = self._in(volume)
+        km, pm, _, _ = self._in(surfaceMap)
+        kn, pn, nshape, _ = self._in(normals)
+        out, op = self._out(shape, like)
+        self._check(self.lib.mrb_feature_map(self.h, pv, pm, pn, int(nshape[0]), self._dims(shape), float(threshold), op))
+        return out
+
     # ---- stage 2 (narrowBand.h:18-24, grid.h:95-104) -------------------------------------------
     def erode_grid(self, g):
         return self._grid_op(self.lib.mrb_erode, g)

@@ -163,6 +163,27 @@ MRB_GRID_OP(fastPerim, mrb_fast_perim)
 MRB_GRID_OP(getsqdist, mrb_sqdist)
 MRB_GRID_OP(getsqrt, mrb_sqrt)
 MRB_GRID_OP(dfield_gpu, mrb_dfield)
+// feature pre-pass (dfields.h:49-67)
+inline std::vector<int> getSurface(gridPtr volume) {
+    int n = 0;
+    mrbcompat::check(mrb_get_surface(mrbcompat::ctx(), volume->data(), &volume->dims[0], nullptr, 0, &n));
+    std::vector<int> idx((size_t)n, 0);
+    if (n) mrbcompat::check(mrb_get_surface(mrbcompat::ctx(), volume->data(), &volume->dims[0], idx.data(), n, &n));
+    return idx;
+}
+inline std::vector<Eigen::Vector3f> getSurfaceNormals(gridPtr volume, const std::vector<int>& surface) {
+    std::vector<Eigen::Vector3f> normals(surface.size());
+    static_assert(sizeof(Eigen::Vector3f) == 3 * sizeof(float), "Vector3f stand-in must be 3 packed floats");
+    mrbcompat::check(mrb_surface_normals(mrbcompat::ctx(), volume->data(), &volume->dims[0], surface.data(), (int)surface.size(),
+                                         surface.empty() ? nullptr : &normals[0][0]));
+    return normals;
+}
+inline gridPtr getFeatureMap(gridPtr volume, gridPtr surfaceMap, const std::vector<Eigen::Vector3f>& normals, float threshold) {
+    gridPtr fm = mrb_like(volume);
+    mrbcompat::check(mrb_feature_map(mrbcompat::ctx(), volume->data(), surfaceMap->data(), normals.empty() ? nullptr : &normals[0][0],
+                                     (int)normals.size(), &volume->dims[0], threshold, fm->data()));
+    return fm;
+}
 // ---- narrowBand (narrowBand.h:11-24) ---------------------------------------------------------------------
 MRB_GRID_OP(erode_grid, mrb_erode)
 MRB_GRID_OP(dilate_grid, mrb_dilate)

@@ -48,8 +48,15 @@ int main(int argc, char** argv) {
     for (size_t i = 0; i < F->size(); i++)
         if (F->data()[i] != F2->data()[i]) { cerr << "optimize() != module-level composition at " << i << endl; return 3; }
 
-    vector<Eigen::Vector3f> normals;
-    mcubes(F, gridPtr(), normals, 0.0, 0.75f, 0.8f, out, false);
+    // feature pre-pass exactly as mesh_reconstruction.cpp:125-128 (always computed there)
+    vector<int> surface = getSurface(volume);
+    gridPtr surfaceMap = getIndexMap(volume, surface);
+    vector<Eigen::Vector3f> normals = getSurfaceNormals(volume, surface);
+    gridPtr featureMap = getFeatureMap(volume, surfaceMap, normals, 0.75f);
+    double nfeat = 0;
+    for (size_t i = 0; i < featureMap->size(); i++) nfeat += featureMap->data()[i];
+    cout << "surface " << surface.size() << " features " << nfeat << endl;
+    mcubes(F, surfaceMap, normals, 0.0, 0.75f, 0.8f, out, false);
     cout << "band " << indexes.size() << " nnz " << args->R->nonZeros() << " idmap0 " << (*indexMap)(indexes[0]) << endl;
     return 0;
 }

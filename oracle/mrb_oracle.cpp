@@ -650,3 +650,132 @@ int mrbo_optimize(const float* volume, const float* feature_map, const int* dims
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+// Feature pre-pass (dfields.cpp:199-349, 447-555).  PARITY UNPINNED against the reference: the
+// normals come from Eigen::SelfAdjointEigenSolver there; here from the deterministic Jacobi solver
+// of include/mrb_eig3.h (the definition both the oracle and the CUDA kernels use).
+// ---------------------------------------------------------------------------------------------
+#include "../include/mrb_eig3.h"
+
+namespace {
+
+// isSurface, dfields.cpp:216-232.  Returns -1 if the 3x3x3 window leaves the grid (reference: exit(1)).
+inline int is_surface(const float* g, const Dims& d, int i, int j, int k) {
+    if (g[at(d, i, j, k)] != 1.0f) return 0;
+    if (i < 1 || j < 1 || k < 1 || i > d.nx - 2 || j > d.ny - 2 || k > d.nz - 2) return -1;
+    for (int a = i - 1; a <= i + 1; a++)
+        for (int b = j - 1; b <= j + 1; b++)
+            for (int c = k - 1; c <= k + 1; c++)
+                if (g[at(d, a, b, c)] == 0.0f) return 1;
+    return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+// getSurface, dfields.cpp:322-338: x-fastest linear indexes of the surface voxels in (i,j,k) order.
+int mrbo_get_surface(const float* vol, const int* dims, int* out, int capacity, int* n_out) {
+    Dims d = mk(dims);
+    int n = 0;
+    for (int i = 0; i < d.nx; i++)
+        for (int j = 0; j < d.ny; j++)
+            for (int k = 0; k < d.nz; k++) {
+                int s = is_surface(vol, d, i, j, k);
+                if (s < 0) { g_err = "get_surface: occupied voxel on the grid border (reference exits, grid.cpp:20-37)"; return -4; }
+                if (s) {
+                    if (out) { if (n >= capacity) return -5; out[n] = sub2ind(d, i, j, k); }
+                    n++;
+                }
+            }
+    *n_out = n;
+    return 0;
+}
+
+// getSurfaceNormals, dfields.cpp:341-349 with getCovariance (:270-290), getSurfaceNeighbors (:235-251),
+// getCentroid (:254-267), getNormalVector (:293-309), orientNormal (:312-319), getNeighbors (:199-213).
+int mrbo_surface_normals(const float* vol, const int* dims, const int* surface, int n, float* normals) {
+    Dims d = mk(dims);
+    int bad = 0;
+#pragma omp parallel for schedule(static)
+    for (int s = 0; s < n; s++) {
+        int x, y, z;
+        ind2sub(d, surface[s], x, y, z);
+        if (x < 2 || y < 2 || z < 2 || x > d.nx - 3 || y > d.ny - 3 || z > d.nz - 3) { bad = 1; continue; }
+        // surface neighbours in (i,j,k) order
+        int px[27], py[27], pz[27], cnt = 0;
+        for (int i = x - 1; i <= x + 1; i++)
+            for (int j = y - 1; j <= y + 1; j++)
+                for (int k = z - 1; k <= z + 1; k++)
+                    if (vol[at(d, i, j, k)] > 0 && is_surface(vol, d, i, j, k) == 1) { px[cnt] = i; py[cnt] = j; pz[cnt] = k; cnt++; }
+        float c[3] = {0.0f, 0.0f, 0.0f};
+        for (int q = 0; q < cnt; q++) { c[0] += (float)px[q]; c[1] += (float)py[q]; c[2] += (float)pz[q]; }
+        c[0] = c[0] / (float)cnt; c[1] = c[1] / (float)cnt; c[2] = c[2] / (float)cnt;
+        float cov[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+        for (int q = 0; q < cnt; q++) {
+            float v[3] = {(float)px[q] - c[0], (float)py[q] - c[1], (float)pz[q] - c[2]};
+            for (int r = 0; r < 3; r++)
+                for (int cc = 0; cc < 3; cc++) cov[r * 3 + cc] = cov[r * 3 + cc] + v[r] * v[cc];
+        }
+        for (int e = 0; e < 9; e++) cov[e] = cov[e] / (float)cnt;
+        float nrm[3];
+        mrb_normal_from_covariance(cov, nrm);
+        // orientNormal: centroid of all occupied (>0) voxels of the 3x3x3 window, relative to the voxel
+        float oc[3] = {0.0f, 0.0f, 0.0f};
+        int on = 0;
+        for (int i = x - 1; i <= x + 1; i++)
+            for (int j = y - 1; j <= y + 1; j++)
+                for (int k = z - 1; k <= z + 1; k++)
+                    if (vol[at(d, i, j, k)] > 0) { oc[0] += (float)i; oc[1] += (float)j; oc[2] += (float)k; on++; }
+        oc[0] = oc[0] / (float)on; oc[1] = oc[1] / (float)on; oc[2] = oc[2] / (float)on;
+        oc[0] -= (float)x; oc[1] -= (float)y; oc[2] -= (float)z;
+        float prod = nrm[0] * oc[0] + nrm[1] * oc[1] + nrm[2] * oc[2];
+        if (prod > 0.0f) { nrm[0] = -nrm[0]; nrm[1] = -nrm[1]; nrm[2] = -nrm[2]; }
+        normals[3 * s] = nrm[0]; normals[3 * s + 1] = nrm[1]; normals[3 * s + 2] = nrm[2];
+    }
+    if (bad) { g_err = "surface_normals: surface voxel within 2 voxels of the border (reference exits)"; return -4; }
+    return 0;
+}
+
+// getFeatureMap, dfields.cpp:447-555.
+int mrbo_feature_map(const float* vol, const float* surface_map, const float* normals, int nnormals, const int* dims,
+                     float threshold, float* out) {
+    Dims d = mk(dims);
+    size_t tot = count(d);
+    for (size_t i = 0; i < tot; i++) out[i] = 0.0f;
+    for (int i = 0; i < d.nx - 1; i++)
+        for (int j = 0; j < d.ny - 1; j++)
+            for (int k = 0; k < d.nz - 1; k++) {
+                int cubeindex = 0;
+                int cx[8], cy[8], cz[8];
+                for (int n = 0; n < 8; n++) {
+                    cx[n] = i + (((n % 4) == 1 || (n % 4) == 2) ? 1 : 0);
+                    cy[n] = j + (n % 4) / 2;
+                    cz[n] = k + n / 4;
+                    int gv = (int)vol[at(d, cx[n], cy[n], cz[n])];
+                    if (gv < 1) cubeindex |= (1 << n);
+                }
+                if (cubeindex == 0 || cubeindex == 255) continue;      // edgeTable[cubeindex] == 0
+                float mn = 5.0f;
+                for (int n = 0; n < 7; n++)
+                    for (int m = n + 1; m < 8; m++) {
+                        int i1 = (int)surface_map[at(d, cx[n], cy[n], cz[n])];
+                        int i2 = (int)surface_map[at(d, cx[m], cy[m], cz[m])];
+                        if (i1 == -1 || i2 == -1) continue;
+                        if (i1 < 0 || i2 < 0 || i1 >= nnormals || i2 >= nnormals) { g_err = "feature_map: normal index out of range"; return -1; }
+                        const float* a = normals + 3 * i1;
+                        const float* b = normals + 3 * i2;
+                        float angle = a[0] * b[0] + a[1] * b[1] + a[2] * b[2];
+                        if (angle < mn) mn = angle;
+                    }
+                if (mn >= threshold) continue;
+                for (int a = 0; a < 2; a++)
+                    for (int b = 0; b < 2; b++)
+                        for (int c = 0; c < 2; c++)
+                            if (surface_map[at(d, i + a, j + b, k + c)] > -1.0f) out[at(d, i + a, j + b, k + c)] = 1.0f;
+            }
+    return 0;
+}
+
+}  // extern "C"

@@ -197,3 +197,30 @@ def write_ply(path, verts, faces, scale=(1, 1, 1), shift=(0, 0, 0), pad=6):
     sc = (C.c_float * 3)(*scale)
     sh = (C.c_float * 3)(*shift)
     _check(lib().mrbo_write_ply(path.encode(), vp, len(v), fpp, len(f), sc, sh, pad), "write_ply")
+
+
+def get_surface(vol):
+    v, vp = _f(vol)
+    n = C.c_int(0)
+    _check(lib().mrbo_get_surface(vp, _dims(v.shape), None, 0, C.byref(n)), "get_surface")
+    out = np.empty(max(n.value, 1), np.int32)
+    _check(lib().mrbo_get_surface(vp, _dims(v.shape), out.ctypes.data_as(C.POINTER(C.c_int)), n.value, C.byref(n)), "get_surface")
+    return out[:n.value].copy()
+
+
+def surface_normals(vol, surface):
+    v, vp = _f(vol)
+    s, sp = _i(surface)
+    out = np.empty((max(len(s), 1), 3), np.float32)
+    _check(lib().mrbo_surface_normals(vp, _dims(v.shape), sp, len(s), out.ctypes.data_as(C.POINTER(C.c_float))), "surface_normals")
+    return out[:len(s)].copy()
+
+
+def feature_map(vol, surface_map, normals, threshold):
+    v, vp = _f(vol)
+    m, mp = _f(surface_map)
+    nr, nrp = _f(np.asarray(normals).reshape(-1, 3))
+    out = np.empty_like(v)
+    _check(lib().mrbo_feature_map(vp, mp, nrp, len(nr), _dims(v.shape), C.c_float(threshold),
+                                  out.ctypes.data_as(C.POINTER(C.c_float))), "feature_map")
+    return out

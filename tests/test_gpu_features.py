@@ -1,0 +1,52 @@
+"""Feature pre-pass (--feature-detection): surface, normals, feature map and the QP feature reset, GPU vs oracle.
+The eigen-solve is our own deterministic definition (include/mrb_eig3.h): bit-exact GPU == oracle is required;
+against the reference (Eigen) this sub-path is parity-unpinned."""
+import numpy as np
+import pytest
+
+from conftest import random_blobs
+
+pytestmark = pytest.mark.gpu
+
+
+def shapes(synth):
+    yield "box", synth.box(48, (12, 9, 7), None, 0.0, 0.0)
+    yield "box_rot", synth.box(56, (13, 10, 8), None, 20.0, 35.0)
+    yield "blobs", random_blobs((44, 48, 52), seed=9)
+    yield "cfg2_small", synth.union(synth.box(64, (18, 14, 10), None, 20.0, 35.0), synth.sphere(64, 14.0))
+
+
+def test_surface_normals_feature_map(ctx, O, synth):
+    for name, v in shapes(synth):
+        s_ref = O.get_surface(v)
+        s = ctx.getSurface(v)
+        assert np.array_equal(s, s_ref), name
+        n_ref = O.surface_normals(v, s_ref)
+        n = ctx.getSurfaceNormals(v, s)
+        assert np.array_equal(n, n_ref), name
+        assert np.allclose(np.linalg.norm(n, axis=1), 1.0, atol=1e-6)
+        smap = O.index_map(v.shape, s_ref)
+        assert np.array_equal(ctx.getIndexMap(v.shape, s), smap), name
+        for thr in (0.75, 0.9):
+            assert np.array_equal(ctx.getFeatureMap(v, smap, n, thr), O.feature_map(v, smap, n_ref, thr)), (name, thr)
+
+
+def test_optimize_with_feature_reset(ctx, O, synth):
+    """optimize(..., USING_FEATURES=true): band voxels on the feature map are reset to 0.2 (quadprog.cpp:92-101)."""
+    for name, v in shapes(synth):
+        s = O.get_surface(v)
+        n = O.surface_normals(v, s)
+        fm = O.feature_map(v, O.index_map(v.shape, s), n, 0.75)
+        F_ref = O.optimize(v, fm, using_features=True, iters=40)
+        F = ctx.optimize(v, fm, True, iters=40)
+        assert np.array_equal(F, F_ref), name
+        if fm.sum() > 0:
+            assert np.all(F[fm == 1] == np.float32(0.2)), name     # all feature voxels lie in the band here
+
+
+def test_border_volume_is_an_error(ctx):
+    import mesh_reconstruction_b200 as mrb
+    v = np.zeros((10, 10, 10), np.float32)
+    v[0:4, 3:7, 3:7] = 1.0
+    with pytest.raises(mrb.MrbError):
+        ctx.getSurface(v)
