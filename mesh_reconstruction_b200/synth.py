@@ -115,3 +115,55 @@ def config_volume(cfg):
             v = np.maximum(v, sphere(512, r, c))
         return v
     raise ValueError(cfg)
+
+
+def write_binvox(path, occ, translate=(0.0, 0.0, 0.0), scale=1.0):
+    """Writes a binvox file (RLE) for occupancy occ[x][y][z]; voxel order x*wxh + z*width + y
+    (binvoxToPcl.cpp:9-13)."""
+    occ = np.asarray(occ) != 0
+    d, w, h = occ.shape[0], occ.shape[1], occ.shape[2]          # depth(x), width(y), height(z)
+    flat = np.ascontiguousarray(occ.transpose(0, 2, 1)).reshape(-1).astype(np.uint8)
+    with open(path, "wb") as f:
+        f.write(b"#binvox 1\n")
+        f.write(("dim %d %d %d\n" % (d, h, w)).encode())
+        f.write(("translate %g %g %g\n" % tuple(translate)).encode())
+        f.write(("scale %g\n" % scale).encode())
+        f.write(b"data\n")
+        i, n = 0, len(flat)
+        out = bytearray()
+        while i < n:
+            v = flat[i]
+            j = i
+            while j < n and flat[j] == v and j - i < 255:
+                j += 1
+            out += bytes([int(v), j - i])
+            i = j
+        f.write(bytes(out))
+
+
+def write_pcd_ascii(path, pts):
+    pts = np.asarray(pts, np.float32)
+    with open(path, "w") as f:
+        f.write("# .PCD v0.7 - Point Cloud Data file format\nVERSION 0.7\nFIELDS x y z\nSIZE 4 4 4\nTYPE F F F\n"
+                "COUNT 1 1 1\nWIDTH %d\nHEIGHT 1\nVIEWPOINT 0 0 0 1 0 0 0\nPOINTS %d\nDATA ascii\n" % (len(pts), len(pts)))
+        for p in pts:
+            f.write("%.7g %.7g %.7g\n" % (p[0], p[1], p[2]))
+
+
+def cli_inputs(dirpath, n=40, radius=12.0):
+    """Config 1 at CLI level: a synthetic 40^3 binvox completion of a sphere (world frame [0,1]^3) and an
+    ASCII PCD of its +z-facing hemisphere sampled at 4x the voxel density.  Returns (binvox, pcd) paths."""
+    import os
+    occ = sphere(n, radius)
+    bv = os.path.join(dirpath, "completion.binvox")
+    pcd = os.path.join(dirpath, "partial.pcd")
+    write_binvox(bv, occ)
+    c = n / 2.0
+    step = 1.0 / (4.0 * n)
+    g = np.arange(-radius / n, radius / n + step, step)
+    xx, yy = np.meshgrid(g, g, indexing="ij")
+    rr = (radius / n) ** 2 - xx ** 2 - yy ** 2
+    m = rr > 0
+    pts = np.stack([xx[m] + c / n, yy[m] + c / n, np.sqrt(rr[m]) + c / n], 1)
+    write_pcd_ascii(pcd, pts)
+    return bv, pcd
