@@ -288,7 +288,64 @@ __global__ void k_block_ranges(const int4* __restrict__ nbA, const int2* __restr
     if (mx > b) atomicMax(&hi[b], mx);
 }
 
-static const int kProgressStride = 32;     // one 128-byte line per block
+static const int kProgressStride = 32;     // one 128-byte line per block / per chunk
+
+// ---- warp-level dataflow synchronisation ------------------------------------------------------------------------
+// Finer than the block-level progress words: every warp owns a contiguous chunk of its block's bricks and
+// publishes its own "sweeps completed" word; before sweep k it waits only for the chunks that own one of
+// its neighbour bricks (typically 6-12 warps).  There is no block-wide barrier inside the sweep loop, so
+// while one warp pays the release/poll latency the other warps of the SM keep computing.  Producer and
+// consumer sets coincide (the neighbour relation is symmetric), so the one wait also covers the
+// write-after-read hazard of the ping-pong buffers.
+static const int kChunkListCap = 64;
+
+__host__ __device__ __forceinline__ void chunk_range(int b, int w, int Q, int G, int W, int* c0, int* c1) {
+    const int qb = (int)(((long long)Q * b) / G), qe = (int)(((long long)Q * (b + 1)) / G);
+    const int cw = (qe - qb + W - 1) / W;
+    int a = qb + w * cw, e = a + cw;
+    if (a > qe) a = qe;
+    if (e > qe) e = qe;
+    *c0 = a; *c1 = e;
+}
+__host__ __device__ __forceinline__ int chunk_of(int q, int Q, int G, int W) {
+    const int b = brick_owner(q, Q, G);
+    const int qb = (int)(((long long)Q * b) / G), qe = (int)(((long long)Q * (b + 1)) / G);
+    const int cw = (qe - qb + W - 1) / W;
+    return b * W + (q - qb) / (cw > 0 ? cw : 1);
+}
+
+__global__ void k_chunk_bitmap(const int4* __restrict__ nbA, const int2* __restrict__ nbB, int Q, int G, int W, int NW,
+                               unsigned* __restrict__ bitmap) {
+    int q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= Q) return;
+    const int g = chunk_of(q, Q, G, W);
+    const int4 a = nbA[q];
+    const int2 z = nbB[q];
+    const int n[6] = {a.x, a.y, a.z, a.w, z.x, z.y};
+    for (int i = 0; i < 6; i++)
+        if (n[i] < Q) {
+            int o = chunk_of(n[i], Q, G, W);
+            if (o != g) atomicOr(&bitmap[(size_t)g * NW + (o >> 5)], 1u << (o & 31));
+        }
+}
+// one warp per chunk: bitmap row -> producer list (order irrelevant)
+__global__ void k_chunk_lists(const unsigned* __restrict__ bitmap, int NC, int NW, int* __restrict__ plist,
+                              int* __restrict__ pcount, int* __restrict__ overflow) {
+    const int g = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (g >= NC) return;
+    for (int wi = lane; wi < NW; wi += 32) {
+        unsigned m = bitmap[(size_t)g * NW + wi];
+        while (m) {
+            int bit = __ffs(m) - 1;
+            m &= m - 1;
+            int slot = atomicAdd(&pcount[g], 1);
+            if (slot < kChunkListCap) plist[(size_t)g * kChunkListCap + slot] = wi * 32 + bit;
+            else *overflow = 1;
+        }
+    }
+}
+
 
 __device__ __forceinline__ void neighbour_sync(unsigned* progress, unsigned epoch, int lo, int hi) {
     __syncthreads();                                   // the block's stores of this sweep are issued
@@ -304,13 +361,14 @@ __device__ __forceinline__ void neighbour_sync(unsigned* progress, unsigned epoc
     __syncthreads();
 }
 
-template <int Threads, int MinBlocks>
+template <int Threads, int MinBlocks, bool WarpFlow>
 __global__ void __launch_bounds__(Threads, MinBlocks) k_qp_bricks(const uint2* __restrict__ code, const uint4* __restrict__ fields,
                                                                   const int4* __restrict__ nbA, const int2* __restrict__ nbB,
                                                                   float4* xa, float4* xb, int Q, int iters,
                                                                   unsigned* __restrict__ maxdelta_bits, unsigned* bar, int dbg,
                                                                   const int* __restrict__ blk_lo, const int* __restrict__ blk_hi,
-                                                                  unsigned* progress, int cap) {
+                                                                  unsigned* progress, int cap, const int* __restrict__ plist,
+                                                                  const int* __restrict__ pcount) {
     // contiguous range of bricks per block (bricks are ordered (X,Y,Z), Z fastest)
     // margin / invdg tables in shared memory: conflict-free LDS (distinct entries sit in distinct banks)
     __shared__ float s_sqrt[256];
@@ -343,9 +401,44 @@ __global__ void __launch_bounds__(Threads, MinBlocks) k_qp_bricks(const uint2* _
     }
     const float4* in = xa;
     float4* out = xb;
+    // work assignment: block-strided (block-level sync) or one contiguous chunk per warp (warp dataflow)
+    constexpr int W = Threads / 32;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    int q_first = q_begin + threadIdx.x, q_last = q_end, q_step = Threads;
+    int np = 0, p0 = 0, p1 = 0;
+    const int chunk = blockIdx.x * W + wid;
+    if (WarpFlow) {
+        int c0, c1;
+        chunk_range(blockIdx.x, wid, Q, gridDim.x, W, &c0, &c1);
+        if (dbg & 2) c1 = c0;
+        q_first = c0 + lane; q_last = c1; q_step = 32;
+        np = min(pcount[chunk], kChunkListCap);
+        if (lane < np) p0 = plist[(size_t)chunk * kChunkListCap + lane];
+        if (lane + 32 < np) p1 = plist[(size_t)chunk * kChunkListCap + lane + 32];
+    }
     for (int it = 0; it < iters; it++) {
         float dmax = 0.0f;
-        for (int q = q_begin + threadIdx.x; q < q_end; q += Threads) {
+        if (WarpFlow && it > 0 && !(dbg & 1)) {
+            // wait until every producer chunk has completed sweep it-1
+            unsigned spins = 0;
+            if (lane < np) {
+                unsigned v;
+                do {
+                    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(progress + (size_t)p0 * kProgressStride) : "memory");
+                    if (++spins == (1u << 28)) __trap();       // a lost producer must not hang the GPU
+                } while (v < (unsigned)it);
+            }
+            if (lane + 32 < np) {
+                unsigned v;
+                do {
+                    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(progress + (size_t)p1 * kProgressStride) : "memory");
+                    if (++spins == (1u << 28)) __trap();
+                } while (v < (unsigned)it);
+            }
+            asm volatile("fence.acq_rel.gpu;" ::: "memory");
+            __syncwarp();
+        }
+        for (int q = q_first; q < q_last; q += q_step) {
             int4 na; int2 nz; uint2 c; uint4 f0, f1;
             if (smem_consts) {            // brick constants resident in shared memory (copied once)
                 const int l = q - q_begin;
@@ -388,7 +481,11 @@ __global__ void __launch_bounds__(Threads, MinBlocks) k_qp_bricks(const uint2* _
             if ((threadIdx.x & 31) == 0) atomicMax(maxdelta_bits, __float_as_uint(dmax));
         }
         const float4* t = in; in = out; out = (float4*)t;
-        if (it + 1 < iters && !(dbg & 1)) {
+        if (WarpFlow) {
+            __syncwarp();
+            if (lane == 0)
+                asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(progress + (size_t)chunk * kProgressStride), "r"((unsigned)(it + 1)) : "memory");
+        } else if (it + 1 < iters && !(dbg & 1)) {
             if (dbg & 4) brick_grid_barrier(bar, (unsigned)(it + 1), gridDim.x);     // tuning aid: global barrier
             else neighbour_sync(progress, (unsigned)(it + 1), nlo, nhi);
         }
@@ -479,12 +576,14 @@ int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_
             const char* e = getenv("MRB_QP_BRICK_THREADS");
             if (e) threads = atoi(e);
             void* kern = nullptr;
-            if (threads == 128) kern = (void*)k_qp_bricks<128, 4>;
-            else if (threads == 512) kern = (void*)k_qp_bricks<512, 1>;
-            else if (threads == 1285) { threads = 128; kern = (void*)k_qp_bricks<128, 5>; }   // tuning: <=102 registers
-            else if (threads == 1286) { threads = 128; kern = (void*)k_qp_bricks<128, 6>; }   // tuning: <=85 registers
-            else if (threads == 2563) { threads = 256; kern = (void*)k_qp_bricks<256, 3>; }   // tuning: <=85 registers
-            else { threads = 256; kern = (void*)k_qp_bricks<256, 2>; }
+            // tuning knob: MRB_QP_SYNC=flow selects the warp-dataflow synchronisation (measured slower on B200:
+            // 3.9-4.4 ms vs 3.5 ms -- one fence per warp and sweep costs more than the overlap wins)
+            bool flow = getenv("MRB_QP_SYNC") && strcmp(getenv("MRB_QP_SYNC"), "flow") == 0;
+            void* kern_block = nullptr;
+            if (threads == 128) { kern = (void*)k_qp_bricks<128, 4, true>; kern_block = (void*)k_qp_bricks<128, 4, false>; }
+            else if (threads == 512) { kern = (void*)k_qp_bricks<512, 1, true>; kern_block = (void*)k_qp_bricks<512, 1, false>; }
+            else { threads = 256; kern = (void*)k_qp_bricks<256, 2, true>; kern_block = (void*)k_qp_bricks<256, 2, false>; }
+            if (!flow) kern = kern_block;
             int fit = 0;
             MRB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&fit, kern, threads, 0));
             if (fit < 1) { set_error("k_qp_bricks does not fit on an SM"); return MRB_ECUDA; }
@@ -503,11 +602,35 @@ int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_
             int cap = (Q + grid - 1) / grid + 1;
             size_t smem = (size_t)cap * 64;
             if (getenv("MRB_QP_BRICK_NOSMEM") || smem > 96 * 1024 / (size_t)fit) { cap = 0; smem = 0; }
-            if (smem > 48 * 1024) MRB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            if (smem > 48 * 1024) {
+                MRB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+                MRB_CUDA(cudaFuncSetAttribute(kern_block, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            }
+            // producer lists of the warp chunks (warp-dataflow synchronisation)
+            int *plist = nullptr, *pcount = nullptr;
+            const int W = threads / 32, NC = grid * W, NW = (NC + 31) / 32;
+            MRB_TRY(arena_alloc(ctx, (size_t)NC * kChunkListCap, &plist));
+            MRB_TRY(arena_alloc(ctx, (size_t)NC, &pcount));
+            if (flow) {
+                unsigned* bitmap = nullptr;
+                MRB_TRY(arena_alloc(ctx, (size_t)NC * NW, &bitmap));
+                int* ovf = ctx->d_mail + 50;
+                MRB_CUDA(cudaMemsetAsync(bitmap, 0, (size_t)NC * NW * sizeof(unsigned), ctx->stream));
+                MRB_CUDA(cudaMemsetAsync(pcount, 0, (size_t)NC * sizeof(int), ctx->stream));
+                MRB_CUDA(cudaMemsetAsync(ovf, 0, sizeof(int), ctx->stream));
+                MRB_LAUNCH(ctx, k_chunk_bitmap, cdiv(Q, 256), 256, 0, nbA, nbB, Q, grid, W, NW, bitmap);
+                MRB_LAUNCH(ctx, k_chunk_lists, cdiv((size_t)NC * 32, 256), 256, 0, bitmap, NC, NW, plist, pcount, ovf);
+                int overflow = 0;
+                MRB_TRY(read_int(ctx, ovf, &overflow));
+                if (overflow) { flow = false; kern = kern_block; }      // a chunk with > 64 producers: block-level sync
+                // progress words: one line per chunk
+                MRB_TRY(arena_alloc(ctx, (size_t)NC * kProgressStride, &progress));
+                MRB_CUDA(cudaMemsetAsync(progress, 0, (size_t)NC * kProgressStride * sizeof(unsigned), ctx->stream));
+            }
             int its = iters, QQ = Q;
             int dbg = getenv("MRB_QP_DEBUG") ? atoi(getenv("MRB_QP_DEBUG")) : 0;   // timing aids (wrong results): 1 no barrier, 2 no work
             void* args[] = {(void*)&code, (void*)&fields, (void*)&nbA, (void*)&nbB, (void*)&xa, (void*)&xb, (void*)&QQ,
-                            (void*)&its, (void*)&md, (void*)&bar, (void*)&dbg, (void*)&blk_lo, (void*)&blk_hi, (void*)&progress, (void*)&cap};
+                            (void*)&its, (void*)&md, (void*)&bar, (void*)&dbg, (void*)&blk_lo, (void*)&blk_hi, (void*)&progress, (void*)&cap, (void*)&plist, (void*)&pcount};
             MRB_CUDA(cudaEventRecord(ctx->ev[6], ctx->stream));
             MRB_CUDA(cudaLaunchCooperativeKernel(kern, dim3(grid), dim3(threads), args, smem, ctx->stream));
             MRB_CUDA(cudaEventRecord(ctx->ev[7], ctx->stream));

@@ -137,6 +137,20 @@ def test_optimize_matrix_free(ctx, O, synth):
             assert np.array_equal(F, F_ref), (name, iters)
 
 
+def test_optimize_sync_and_layout_variants(ctx, O, synth, monkeypatch):
+    """Every selectable stage-3 variant (tuning knobs) must give the same bits as the default."""
+    v = synth.torus(56, 14.0, 5.0)
+    F_ref = O.optimize(v, iters=60)
+    for env in ({"MRB_QP_SYNC": "flow"}, {"MRB_QP_LAYOUT": "strips"}, {"MRB_QP_BRICK_THREADS": "512"},
+                {"MRB_QP_BRICK_THREADS": "128"}, {"MRB_QP_BRICK_NOSMEM": "1"},
+                {"MRB_QP_LAYOUT": "strips", "MRB_QP_VARIANT": "0:1024"}, {"MRB_QP_LAYOUT": "strips", "MRB_QP_VARIANT": "2:512"}):
+        for k, val in env.items():
+            monkeypatch.setenv(k, val)
+        assert np.array_equal(ctx.optimize(v, iters=60), F_ref), env
+        for k in env:
+            monkeypatch.delenv(k)
+
+
 def test_optimize_band_sizes(ctx, O, synth):
     v = synth.sphere(64, 20.0)
     for bs in (2, 8):
