@@ -79,6 +79,19 @@ void Arena::release() {
     blocks.clear();
 }
 
+int pinned_reserve(mrb_ctx* ctx, size_t bytes, char** out) {
+    if (bytes > ctx->h_pinned_cap) {
+        if (ctx->h_pinned) cudaFreeHost(ctx->h_pinned);
+        ctx->h_pinned = nullptr;
+        size_t cap = bytes + (bytes >> 2) + (1u << 20);
+        cudaError_t e = cudaMallocHost((void**)&ctx->h_pinned, cap);
+        if (e != cudaSuccess) { cudaGetLastError(); ctx->h_pinned_cap = 0; set_error("pinned staging: cudaMallocHost(%zu) failed", cap); return MRB_ENOMEM; }
+        ctx->h_pinned_cap = cap;
+    }
+    *out = ctx->h_pinned;
+    return MRB_OK;
+}
+
 int read_int(mrb_ctx* ctx, const int* dev, int* host) {
     MRB_CUDA(cudaMemcpyAsync(ctx->h_mail, dev, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
     MRB_CUDA(cudaStreamSynchronize(ctx->stream));
@@ -235,6 +248,7 @@ void mrb_ctx_destroy(mrb_ctx* ctx) {
     if (ctx->h_mail) cudaFreeHost(ctx->h_mail);
     if (ctx->d_mail) cudaFree(ctx->d_mail);
     if (ctx->d_bar) cudaFree(ctx->d_bar);
+    if (ctx->h_pinned) cudaFreeHost(ctx->h_pinned);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }

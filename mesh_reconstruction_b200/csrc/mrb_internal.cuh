@@ -66,9 +66,14 @@ struct mrb_ctx {
     int* h_mail = nullptr;      // 64 ints, pinned
     int* d_mail = nullptr;      // 64 ints, device
     int* d_bar = nullptr;       // 64 ints, device: grid-barrier words (two 128-byte lines)
+    char* h_pinned = nullptr;   // grow-only pinned staging buffer for device->host results
+    size_t h_pinned_cap = 0;
 };
 
 namespace mrb {
+
+// Pinned host staging of at least `bytes` (grow-only; contents valid until the next reserve).
+int pinned_reserve(mrb_ctx* ctx, size_t bytes, char** out);
 
 // True when p is device-accessible memory (device or managed).
 bool is_device_ptr(const void* p);

@@ -304,9 +304,16 @@ int export_mesh(mrb_ctx* ctx, float* verts_dev, int* faces_dev, int nverts, int 
     out->verts = (float*)malloc(sizeof(float) * 3 * (size_t)(nverts > 0 ? nverts : 1));
     out->faces = (int*)malloc(sizeof(int) * 3 * (size_t)(nfaces > 0 ? nfaces : 1));
     if (!out->verts || !out->faces) { set_error("export_mesh: host malloc failed"); return MRB_ENOMEM; }
-    if (nverts > 0) MRB_CUDA(cudaMemcpyAsync(out->verts, verts_dev, sizeof(float) * 3 * (size_t)nverts, cudaMemcpyDeviceToHost, ctx->stream));
-    if (nfaces > 0) MRB_CUDA(cudaMemcpyAsync(out->faces, faces_dev, sizeof(int) * 3 * (size_t)nfaces, cudaMemcpyDeviceToHost, ctx->stream));
-    return sync(ctx);
+    // device -> pinned staging (full PCIe rate) -> the caller's malloc'd arrays
+    const size_t vb = sizeof(float) * 3 * (size_t)nverts, fb = sizeof(int) * 3 * (size_t)nfaces;
+    char* pin = nullptr;
+    MRB_TRY(pinned_reserve(ctx, vb + fb, &pin));
+    if (nverts > 0) MRB_CUDA(cudaMemcpyAsync(pin, verts_dev, vb, cudaMemcpyDeviceToHost, ctx->stream));
+    if (nfaces > 0) MRB_CUDA(cudaMemcpyAsync(pin + vb, faces_dev, fb, cudaMemcpyDeviceToHost, ctx->stream));
+    MRB_TRY(sync(ctx));
+    if (nverts > 0) memcpy(out->verts, pin, vb);
+    if (nfaces > 0) memcpy(out->faces, pin + vb, fb);
+    return MRB_OK;
 }
 
 }  // namespace mrb

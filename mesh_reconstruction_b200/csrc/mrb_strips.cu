@@ -603,6 +603,7 @@ __global__ void __launch_bounds__(256) k_assemble_F_s(const float* __restrict__ 
     }
 }
 
+int stage12_binary(mrb_ctx* ctx, const float* vol, Dims d, int W, uint8_t* sq, uint8_t* flags, int* counts, int* binary_out);
 int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_t* flags, const uint8_t* sq, Dims d,
                  int band_size, int iters, int using_features, float* F_dev, float* last_delta_host, int* n_bricks,
                  int* closure_err_host);
@@ -623,13 +624,22 @@ int optimize_strips(mrb_ctx* ctx, const float* vol, const float* fmap, Dims d, i
         MRB_TRY(arena_alloc(ctx, n, &b1));
         MRB_TRY(arena_alloc(ctx, n, &sq));
         const unsigned g = grid_for(ctx, n, 256);
-        MRB_LAUNCH(ctx, k_site, g, 256, 0, vol, d, b0);
-        MRB_LAUNCH(ctx, k_tedt_x, g, 256, 0, b0, d, band_size, b1);
-        MRB_LAUNCH(ctx, k_tedt_y, g, 256, 0, b1, d, band_size, b0);
-        MRB_LAUNCH(ctx, k_tedt_z, g, 256, 0, b0, d, band_size, sq);
-        MRB_CUDA(cudaEventRecord(ctx->ev[1], ctx->stream));
-        MRB_LAUNCH(ctx, k_tight, g, 256, 0, sq, d, b1);
-        MRB_LAUNCH(ctx, k_band_flags, g, 256, 0, b1, d, flags, counts);
+        // binary occupancy grids (the normal case): bit-packed perimeter + tile-sparse passes (mrb_stage12.cu);
+        // any other value in the grid -> the general byte-grid kernels below
+        int binary = 0;
+        if (!getenv("MRB_STAGE12_GENERAL")) MRB_TRY(stage12_binary(ctx, vol, d, band_size, sq, flags, counts, &binary));
+        if (binary) {
+            MRB_CUDA(cudaEventRecord(ctx->ev[1], ctx->stream));
+        } else {
+            MRB_CUDA(cudaMemsetAsync(counts, 0, 4 * sizeof(int), ctx->stream));
+            MRB_LAUNCH(ctx, k_site, g, 256, 0, vol, d, b0);
+            MRB_LAUNCH(ctx, k_tedt_x, g, 256, 0, b0, d, band_size, b1);
+            MRB_LAUNCH(ctx, k_tedt_y, g, 256, 0, b1, d, band_size, b0);
+            MRB_LAUNCH(ctx, k_tedt_z, g, 256, 0, b0, d, band_size, sq);
+            MRB_CUDA(cudaEventRecord(ctx->ev[1], ctx->stream));
+            MRB_LAUNCH(ctx, k_tight, g, 256, 0, sq, d, b1);
+            MRB_LAUNCH(ctx, k_band_flags, g, 256, 0, b1, d, flags, counts);
+        }
         const char* layout = getenv("MRB_QP_LAYOUT");          // tuning knob: "strips" selects the z-strip kernel
         if (!(layout && strcmp(layout, "strips") == 0)) {
             // default: 2x2x4 bricks (mrb_bricks.cu)
