@@ -254,6 +254,93 @@ int dev_dedup(mrb_ctx* ctx, const float* soup, const unsigned long long* keys, i
     return MRB_OK;
 }
 
+// ---- bit-plane classification -------------------------------------------------------------------------------
+// "val < isolevel" (mcubes.cpp:199-207) is one bit per voxel; a cell is surface-crossing iff its 8 corner bits
+// are not all equal (edgeTable[cubeindex] != 0).  F is read once to pack the bits (32 z per word); the cell
+// test then runs on words: OR and AND over the 2x2 (x,y) rows and the z / z+1 bit pair, 32 cells at a time.
+// popc of the active-cell words + exclusive scan gives the (i,j,k)-ordered list of crossing cells.
+__global__ void __launch_bounds__(256) k_sign_bits(const float* __restrict__ F, Dims d, int nzw, float iso,
+                                                   uint32_t* __restrict__ sb) {
+    const int lane = threadIdx.x & 31;
+    const size_t rows = (size_t)d.nx * d.ny;
+    for (size_t row = (size_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); row < rows; row += (size_t)gridDim.x * (blockDim.x >> 5)) {
+        const float* p = F + row * d.nz;
+        for (int w = 0; w < nzw; w++) {
+            int z = w * 32 + lane;
+            bool below = z < d.nz && __ldg(p + z) < iso;
+            unsigned m = __ballot_sync(0xffffffffu, below);
+            if (lane == 0) sb[row * nzw + w] = m;
+        }
+    }
+}
+
+// one thread per (i, j, zw): active-cell word for cells k = 32 zw .. 32 zw + 31 and its popcount
+__global__ void __launch_bounds__(256) k_cell_words(const uint32_t* __restrict__ sb, CellDims cd, int nzw,
+                                                    uint32_t* __restrict__ aw, int* __restrict__ cnt) {
+    const size_t n = (size_t)cd.cx * cd.cy * nzw;
+    for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < n; idx += (size_t)gridDim.x * blockDim.x) {
+        const int w = (int)(idx % nzw);
+        const size_t t = idx / nzw;
+        const int j = (int)(t % cd.cy), i = (int)(t / cd.cy);
+        uint32_t any = 0, all = 0xffffffffu;
+        for (int a = 0; a < 2; a++)
+            for (int b = 0; b < 2; b++) {
+                const uint32_t* row = sb + ((size_t)(i + a) * cd.ny + (j + b)) * nzw;
+                const uint32_t lo = __ldg(row + w);
+                const uint32_t nx = w + 1 < nzw ? __ldg(row + w + 1) : 0u;
+                const uint32_t hi = (lo >> 1) | (nx << 31);          // bit k+1
+                any |= lo | hi;
+                all &= lo & hi;
+            }
+        const int nvalid = min(32, cd.cz - 32 * w);                   // cells k <= nz - 2
+        const uint32_t valid = nvalid >= 32 ? 0xffffffffu : (nvalid > 0 ? ((1u << nvalid) - 1u) : 0u);
+        const uint32_t m = any & ~all & valid;
+        aw[idx] = m;
+        cnt[idx] = __popc(m);
+    }
+}
+
+__global__ void __launch_bounds__(256) k_cell_list(const uint32_t* __restrict__ aw, const int* __restrict__ off, CellDims cd,
+                                                   int nzw, int* __restrict__ cells) {
+    const size_t n = (size_t)cd.cx * cd.cy * nzw;
+    for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < n; idx += (size_t)gridDim.x * blockDim.x) {
+        uint32_t m = aw[idx];
+        if (!m) continue;
+        const int w = (int)(idx % nzw);
+        const size_t col = idx / nzw;                                  // i * cy + j
+        int o = off[idx];
+        while (m) {
+            int bit = __ffs(m) - 1;
+            m &= m - 1;
+            cells[o++] = (int)(col * cd.cz + (size_t)(32 * w + bit));
+        }
+    }
+}
+
+static int classify_cells(mrb_ctx* ctx, const float* F, Dims d, const CellDims& cd, float iso, int** cells_out, int* ncells_out) {
+    const int nzw = (d.nz + 31) / 32;
+    const size_t nwords = (size_t)d.nx * d.ny * nzw, ncw = (size_t)cd.cx * cd.cy * nzw;
+    uint32_t *sb = nullptr, *aw = nullptr;
+    int* cnt = nullptr;
+    MRB_TRY(arena_alloc(ctx, nwords, &sb));
+    MRB_TRY(arena_alloc(ctx, ncw, &aw));
+    MRB_TRY(arena_alloc(ctx, ncw, &cnt));
+    const size_t cap = (size_t)ctx->sm_count * 32;
+    size_t want = ((size_t)d.nx * d.ny + 7) / 8;
+    MRB_LAUNCH(ctx, k_sign_bits, (unsigned)(want < cap ? want : cap), 256, 0, F, d, nzw, iso, sb);
+    want = (ncw + 255) / 256;
+    MRB_LAUNCH(ctx, k_cell_words, (unsigned)(want < cap ? want : cap), 256, 0, sb, cd, nzw, aw, cnt);
+    MRB_TRY(scan_exclusive(ctx, cnt, cnt, ncw, ctx->d_mail));
+    int total = 0;
+    MRB_TRY(read_int(ctx, ctx->d_mail, &total));
+    int* cells = nullptr;
+    MRB_TRY(arena_alloc(ctx, (size_t)(total > 0 ? total : 1), &cells));
+    if (total > 0) MRB_LAUNCH(ctx, k_cell_list, (unsigned)(want < cap ? want : cap), 256, 0, aw, cnt, cd, nzw, cells);
+    *cells_out = cells;
+    *ncells_out = total;
+    return MRB_OK;
+}
+
 int dev_mcubes(mrb_ctx* ctx, const float* F, Dims d, float isolevel, float** verts_dev, int** faces_dev, int* nverts,
                int* nfaces) {
     *verts_dev = nullptr; *faces_dev = nullptr; *nverts = 0; *nfaces = 0;
@@ -262,7 +349,8 @@ int dev_mcubes(mrb_ctx* ctx, const float* F, Dims d, float isolevel, float** ver
     size_t ncell_total = (size_t)cd.cx * cd.cy * cd.cz;
     int* cells = nullptr;
     int ncells = 0;
-    MRB_TRY(compact(ctx, ActiveCellPred{F, cd, isolevel}, ncell_total, &cells, &ncells));
+    (void)ncell_total;
+    MRB_TRY(classify_cells(ctx, F, d, cd, isolevel, &cells, &ncells));
     if (ncells == 0) return MRB_OK;
     int* tri_off = nullptr;
     MRB_TRY(arena_alloc(ctx, (size_t)ncells, &tri_off));
