@@ -209,6 +209,23 @@ int mrb_reconstruct(mrb_ctx* ctx, const float* volume, const int dims[3], const 
 int mrb_reconstruct_batch(mrb_ctx* ctx, const float* volumes, const int dims[3], int nobj,
                           const mrb_options* opt, mrb_mesh* out, int* vert_off, int* face_off);
 
+/* ---- stepwise stage 3 for slab-sharded multi-GPU runs ---------------------------------------
+ * No counterpart in the reference (it is single-GPU).  A plan holds stages 1-2 and the 2x2x4 bricks of one binary
+ * occupancy grid; bricks are numbered with x slowest, so an x-slab is a contiguous brick range and its halo is
+ * the neighbouring brick plane.  The iterate lives in caller-owned device buffers of 16*(Q+1) floats (four SoA
+ * planes of Q+1 float4; slot Q of every plane must stay 0).  One sweep over [q_begin, q_end) is exactly one
+ * doStep (quadprog.cpp:45-61) for every voxel of those bricks; running all bricks for `iters` sweeps with
+ * alternating buffers and assembling gives the same F as mrb_optimize, bit for bit. */
+typedef struct mrb_qp_plan mrb_qp_plan;
+int  mrb_qp_plan_create(mrb_ctx* ctx, const float* volume, const int dims[3], int band_size, mrb_qp_plan** out);
+void mrb_qp_plan_destroy(mrb_qp_plan* plan);
+int  mrb_qp_plan_info(mrb_qp_plan* plan, int* n_bricks, int* n_band, int* n_tight, int* n_brick_planes);
+/* off[X] = first brick id of brick plane X (voxel planes 2X, 2X+1); n_brick_planes + 1 entries. */
+int  mrb_qp_plan_plane_offsets(mrb_qp_plan* plan, int* off);
+int  mrb_qp_plan_init_x(mrb_qp_plan* plan, float* x_dev);
+int  mrb_qp_plan_sweep(mrb_qp_plan* plan, const float* x_in_dev, float* x_out_dev, int q_begin, int q_end);
+int  mrb_qp_plan_assemble(mrb_qp_plan* plan, const float* x_dev, float* F_out);
+
 #ifdef __cplusplus
 }
 #endif

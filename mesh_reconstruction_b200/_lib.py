@@ -64,6 +64,13 @@ SYMBOLS = {
     "mrb_options_default": (None, [C.POINTER(Options)]),
     "mrb_reconstruct": (C.c_int, [_VP, _VP, c_int_p, C.POINTER(Options), C.c_int, C.POINTER(Mesh),
                                   C.POINTER(QPStats)]),
+    "mrb_qp_plan_create": (C.c_int, [_VP, _VP, c_int_p, C.c_int, C.POINTER(_VP)]),
+    "mrb_qp_plan_destroy": (None, [_VP]),
+    "mrb_qp_plan_info": (C.c_int, [_VP, c_int_p, c_int_p, c_int_p, c_int_p]),
+    "mrb_qp_plan_plane_offsets": (C.c_int, [_VP, c_int_p]),
+    "mrb_qp_plan_init_x": (C.c_int, [_VP, _VP]),
+    "mrb_qp_plan_sweep": (C.c_int, [_VP, _VP, _VP, C.c_int, C.c_int]),
+    "mrb_qp_plan_assemble": (C.c_int, [_VP, _VP, _VP]),
     "mrb_reconstruct_batch": (C.c_int, [_VP, _VP, c_int_p, C.c_int, C.POINTER(Options), C.POINTER(Mesh), c_int_p,
                                         c_int_p]),
 }

@@ -254,6 +254,41 @@ __device__ __forceinline__ void brick_grid_barrier(unsigned* bar, unsigned epoch
     __syncthreads();
 }
 
+// One Jacobi update of brick q: reads the iterate planes `in` (stride P), writes `out`.  Returns max |delta|.
+__device__ __forceinline__ float brick_update(int q, size_t P, const int4 na, const int2 nz, const uint2 c, const uint4 f0,
+                                              const uint4 f1, const float4* in, float4* out, const float* __restrict__ s_sqrt,
+                                              const float* __restrict__ s_inv, bool want_delta) {
+    BrickRegs r;
+    // the iterate is rewritten by other SMs every sweep: plain loads, ordered by the sweep synchronisation
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const float4* pl = in + k * P;
+        put4(r.own[k], pl[q]);
+        put4(r.xm[k], pl[na.x]);
+        put4(r.xp[k], pl[na.y]);
+        put4(r.ym[k], pl[na.z]);
+        put4(r.yp[k], pl[na.w]);
+        const float2 l = *reinterpret_cast<const float2*>(reinterpret_cast<const float*>(pl + nz.x) + 2);
+        const float2 h = *reinterpret_cast<const float2*>(pl + nz.y);
+        r.zl[k][0] = l.x; r.zl[k][1] = l.y;
+        r.zh[k][0] = h.x; r.zh[k][1] = h.y;
+    }
+    const float4 o0 = brick_strip<0>(r, c.x, c.y, f0.x, f0.y, s_sqrt, s_inv);
+    const float4 o1 = brick_strip<1>(r, c.x, c.y, f0.z, f0.w, s_sqrt, s_inv);
+    const float4 o2 = brick_strip<2>(r, c.x, c.y, f1.x, f1.y, s_sqrt, s_inv);
+    const float4 o3 = brick_strip<3>(r, c.x, c.y, f1.z, f1.w, s_sqrt, s_inv);
+    out[q] = o0; out[P + q] = o1; out[2 * P + q] = o2; out[3 * P + q] = o3;
+    float dmax = 0.0f;
+    if (want_delta) {
+        const float4 os[4] = {o0, o1, o2, o3};
+#pragma unroll
+        for (int k = 0; k < 4; k++)
+            dmax = fmaxf(fmaxf(dmax, fmaxf(fabsf(os[k].x - r.own[k][0]), fabsf(os[k].y - r.own[k][1]))),
+                         fmaxf(fabsf(os[k].z - r.own[k][2]), fabsf(os[k].w - r.own[k][3])));
+    }
+    return dmax;
+}
+
 // ---- neighbour-only synchronisation --------------------------------------------------------------------------
 // Block b owns bricks [Q*b/G, Q*(b+1)/G).  Its sweep k+1 reads bricks owned by a few other blocks only
 // (bricks are ordered (X,Y,Z): the X+-1 neighbours sit about one x-plane of bricks away), so instead of
@@ -447,33 +482,7 @@ __global__ void __launch_bounds__(Threads, MinBlocks) k_qp_bricks(const uint2* _
                 na = __ldg(nbA + q); nz = __ldg(nbB + q); c = __ldg(code + q);
                 f0 = __ldg(fields + q); f1 = __ldg(fields + (size_t)Q + q);
             }
-            BrickRegs r;
-            // the iterate is rewritten by other SMs every sweep: plain loads, ordered by the grid barrier
-#pragma unroll
-            for (int k = 0; k < 4; k++) {
-                const float4* pl = in + k * P;
-                put4(r.own[k], pl[q]);
-                put4(r.xm[k], pl[na.x]);
-                put4(r.xp[k], pl[na.y]);
-                put4(r.ym[k], pl[na.z]);
-                put4(r.yp[k], pl[na.w]);
-                const float2 l = *reinterpret_cast<const float2*>(reinterpret_cast<const float*>(pl + nz.x) + 2);
-                const float2 h = *reinterpret_cast<const float2*>(pl + nz.y);
-                r.zl[k][0] = l.x; r.zl[k][1] = l.y;
-                r.zh[k][0] = h.x; r.zh[k][1] = h.y;
-            }
-            const float4 o0 = brick_strip<0>(r, c.x, c.y, f0.x, f0.y, s_sqrt, s_inv);
-            const float4 o1 = brick_strip<1>(r, c.x, c.y, f0.z, f0.w, s_sqrt, s_inv);
-            const float4 o2 = brick_strip<2>(r, c.x, c.y, f1.x, f1.y, s_sqrt, s_inv);
-            const float4 o3 = brick_strip<3>(r, c.x, c.y, f1.z, f1.w, s_sqrt, s_inv);
-            out[q] = o0; out[P + q] = o1; out[2 * P + q] = o2; out[3 * P + q] = o3;
-            if (it == iters - 1) {
-                const float4 os[4] = {o0, o1, o2, o3};
-#pragma unroll
-                for (int k = 0; k < 4; k++)
-                    dmax = fmaxf(fmaxf(dmax, fmaxf(fabsf(os[k].x - r.own[k][0]), fabsf(os[k].y - r.own[k][1]))),
-                                 fmaxf(fabsf(os[k].z - r.own[k][2]), fabsf(os[k].w - r.own[k][3])));
-            }
+            dmax = fmaxf(dmax, brick_update(q, P, na, nz, c, f0, f1, in, out, s_sqrt, s_inv, it == iters - 1));
         }
         if (it == iters - 1) {
 #pragma unroll
@@ -657,4 +666,181 @@ int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_
     return MRB_OK;
 }
 
+// ---- stepwise solver ("plan") for slab-sharded multi-GPU runs -----------------------------------------------
+// The same bricks and the same per-brick update, but driven one sweep at a time over a caller-chosen brick
+// range, with the iterate in caller-owned device buffers.  Bricks are numbered (X,Y,Z) with X slowest, so an
+// x-slab of the grid is a contiguous brick range and its one-brick-plane halo is the contiguous range of the
+// neighbouring X plane: ranks that built the plan from the same volume share the numbering and exchange
+// plain sub-ranges of the four SoA planes between sweeps (mesh_reconstruction_b200/slab.py).
+int stage12_binary(mrb_ctx* ctx, const float* vol, Dims d, int W, uint8_t* sq, uint8_t* flags, int* counts, int* binary_out);
+
+__global__ void __launch_bounds__(256) k_qp_bricks_range(const uint2* __restrict__ code, const uint4* __restrict__ fields,
+                                                         const int4* __restrict__ nbA, const int2* __restrict__ nbB,
+                                                         const float4* in, float4* out, int Q, int q0, int q1) {
+    __shared__ float s_sqrt[256];
+    __shared__ float s_inv[32];
+    s_sqrt[threadIdx.x] = c_brick_sqrt[threadIdx.x];
+    if (threadIdx.x < 32) s_inv[threadIdx.x] = c_brick_invdg[threadIdx.x];
+    __syncthreads();
+    const int q = q0 + blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= q1) return;
+    brick_update(q, (size_t)Q + 1, __ldg(nbA + q), __ldg(nbB + q), __ldg(code + q), __ldg(fields + q),
+                 __ldg(fields + (size_t)Q + q), in, out, s_sqrt, s_inv, false);
+}
+
 }  // namespace mrb
+
+struct mrb_qp_plan {
+    mrb_ctx* ctx = nullptr;
+    mrb::Arena arena;                 // owns every device buffer of the plan
+    mrb::Dims d{};
+    mrb::BrickDims bd{};
+    int band_size = 0, Q = 0, n_band = 0, n_tight = 0;
+    const float* vol = nullptr;
+    uint8_t *flags = nullptr, *sq = nullptr;
+    int* bid = nullptr;
+    uint2* code = nullptr;
+    uint4* fields = nullptr;
+    int4* nbA = nullptr;
+    int2* nbB = nullptr;
+    float4* x0 = nullptr;
+    std::vector<int> plane_off;       // bx + 1 entries: first brick id of every X plane
+};
+
+using namespace mrb;
+
+extern "C" {
+
+void mrb_qp_plan_destroy(mrb_qp_plan* plan) {
+    if (!plan) return;
+    if (plan->ctx) { cudaSetDevice(plan->ctx->device); cudaStreamSynchronize(plan->ctx->stream); }
+    plan->arena.release();
+    delete plan;
+}
+
+int mrb_qp_plan_create(mrb_ctx* ctx, const float* volume, const int dims[3], int band_size, mrb_qp_plan** out) {
+    MRB_REQUIRE(ctx && volume && dims && out, "NULL argument");
+    MRB_REQUIRE(band_size >= 1 && band_size <= 15, "plans support band_size 1..15");
+    *out = nullptr;
+    MRB_CUDA(cudaSetDevice(ctx->device));
+    MRB_TRY(upload_tables(ctx->device));
+    mrb_qp_plan* p = new mrb_qp_plan();
+    p->ctx = ctx;
+    p->d = mkdims(dims);
+    p->band_size = band_size;
+    const Dims d = p->d;
+    const size_t n = d.count();
+    // every allocation below (scratch included) lands in the plan's own arena and lives as long as the plan
+    std::swap(ctx->arena, p->arena);
+    auto build = [&]() -> int {
+        const float* dv = nullptr;
+        if (is_device_ptr(volume)) {
+            float* copy = nullptr;
+            MRB_TRY(arena_alloc(ctx, n, &copy));
+            MRB_CUDA(cudaMemcpyAsync(copy, volume, n * sizeof(float), cudaMemcpyDeviceToDevice, ctx->stream));
+            dv = copy;
+        } else {
+            MRB_TRY(stage_in(ctx, volume, n, &dv));
+        }
+        p->vol = dv;
+        MRB_TRY(arena_alloc(ctx, n, &p->flags));
+        MRB_TRY(arena_alloc(ctx, n, &p->sq));
+        int* counts = ctx->d_mail + 32;
+        MRB_CUDA(cudaMemsetAsync(counts, 0, 4 * sizeof(int), ctx->stream));
+        int binary = 0;
+        MRB_TRY(stage12_binary(ctx, dv, d, band_size, p->sq, p->flags, counts, &binary));
+        if (!binary) { set_error("mrb_qp_plan_create: the volume must contain only 0 and 1"); return MRB_EINVAL; }
+        MRB_CUDA(cudaMemcpyAsync(ctx->h_mail + 32, counts, 4 * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+        p->bd = BrickDims{d.nx, d.ny, d.nz, (d.nx + 1) / 2, (d.ny + 1) / 2, (d.nz + 3) / 4};
+        const size_t nb = p->bd.count();
+        int* bpos = nullptr;
+        MRB_TRY(compact(ctx, ActiveBrickPred{p->flags, p->bd}, nb, &bpos, &p->Q));
+        p->n_band = ctx->h_mail[32];
+        p->n_tight = ctx->h_mail[33];
+        if (ctx->h_mail[34]) { set_error("narrow band touches the grid border (reference exits, grid.cpp:20-37)"); return MRB_EBORDER; }
+        const int Q = p->Q;
+        const size_t Qn = (size_t)(Q > 0 ? Q : 1);
+        MRB_TRY(arena_alloc(ctx, nb, &p->bid));
+        MRB_LAUNCH(ctx, k_fill_i32b, grid_for(ctx, nb, 256), 256, 0, p->bid, nb, -1);
+        MRB_TRY(arena_alloc(ctx, Qn, &p->code));
+        MRB_TRY(arena_alloc(ctx, 2 * Qn, &p->fields));
+        MRB_TRY(arena_alloc(ctx, 4 * (Qn + 1), &p->x0));
+        MRB_TRY(arena_alloc(ctx, Qn, &p->nbA));
+        MRB_TRY(arena_alloc(ctx, Qn, &p->nbB));
+        p->plane_off.assign((size_t)p->bd.bx + 1, Q);
+        if (Q == 0) return MRB_OK;
+        MRB_LAUNCH(ctx, k_scatter_brick_ids, cdiv(Q, 256), 256, 0, bpos, Q, p->bid);
+        int* err = ctx->d_mail + 24;
+        MRB_CUDA(cudaMemsetAsync(err, 0, sizeof(int), ctx->stream));
+        MRB_CUDA(cudaMemsetAsync(p->x0, 0, 4 * (Qn + 1) * sizeof(float4), ctx->stream));
+        MRB_LAUNCH(ctx, k_brick_build, cdiv(Q, 128), 128, 0, dv, p->sq, p->flags, p->bid, bpos, Q, p->bd, p->code, p->fields,
+                   p->x0, p->nbA, p->nbB, err);
+        std::vector<int> hpos((size_t)Q);
+        MRB_CUDA(cudaMemcpyAsync(hpos.data(), bpos, (size_t)Q * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+        MRB_CUDA(cudaMemcpyAsync(ctx->h_mail + 24, err, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+        MRB_CUDA(cudaStreamSynchronize(ctx->stream));
+        if (ctx->h_mail[24]) { set_error("narrow band touches the grid border (reference exits, grid.cpp:20-37)"); return MRB_EBORDER; }
+        const int per_plane = p->bd.by * p->bd.bz;
+        int q = 0;
+        for (int X = 0; X <= p->bd.bx; X++) {          // bricks are sorted by position: first id with plane >= X
+            while (q < Q && hpos[q] / per_plane < X) q++;
+            p->plane_off[X] = q;
+        }
+        return MRB_OK;
+    };
+    int rc = build();
+    std::swap(ctx->arena, p->arena);
+    if (rc != MRB_OK) { p->arena.release(); delete p; return rc; }
+    *out = p;
+    return MRB_OK;
+}
+
+int mrb_qp_plan_info(mrb_qp_plan* plan, int* n_bricks, int* n_band, int* n_tight, int* n_brick_planes) {
+    MRB_REQUIRE(plan, "NULL plan");
+    if (n_bricks) *n_bricks = plan->Q;
+    if (n_band) *n_band = plan->n_band;
+    if (n_tight) *n_tight = plan->n_tight;
+    if (n_brick_planes) *n_brick_planes = plan->bd.bx;
+    return MRB_OK;
+}
+
+int mrb_qp_plan_plane_offsets(mrb_qp_plan* plan, int* off) {
+    MRB_REQUIRE(plan && off, "NULL argument");
+    for (size_t i = 0; i < plan->plane_off.size(); i++) off[i] = plan->plane_off[i];
+    return MRB_OK;
+}
+
+int mrb_qp_plan_init_x(mrb_qp_plan* plan, float* x_dev) {
+    MRB_REQUIRE(plan && x_dev && is_device_ptr(x_dev), "x must be a device buffer of 16*(Q+1) floats");
+    mrb_ctx* ctx = plan->ctx;
+    MRB_CUDA(cudaSetDevice(ctx->device));
+    MRB_CUDA(cudaMemcpyAsync(x_dev, plan->x0, 4 * ((size_t)plan->Q + 1) * sizeof(float4), cudaMemcpyDeviceToDevice, ctx->stream));
+    return sync(ctx);
+}
+
+int mrb_qp_plan_sweep(mrb_qp_plan* plan, const float* x_in_dev, float* x_out_dev, int q_begin, int q_end) {
+    MRB_REQUIRE(plan && x_in_dev && x_out_dev && x_in_dev != x_out_dev, "bad buffers");
+    MRB_REQUIRE(q_begin >= 0 && q_end <= plan->Q && q_begin <= q_end, "bad brick range");
+    mrb_ctx* ctx = plan->ctx;
+    MRB_CUDA(cudaSetDevice(ctx->device));
+    if (q_end > q_begin)
+        MRB_LAUNCH(ctx, k_qp_bricks_range, cdiv((size_t)(q_end - q_begin), 256), 256, 0, plan->code, plan->fields, plan->nbA,
+                   plan->nbB, (const float4*)x_in_dev, (float4*)x_out_dev, plan->Q, q_begin, q_end);
+    return sync(ctx);
+}
+
+int mrb_qp_plan_assemble(mrb_qp_plan* plan, const float* x_dev, float* F_out) {
+    MRB_REQUIRE(plan && x_dev && F_out, "NULL argument");
+    mrb_ctx* ctx = plan->ctx;
+    MRB_CUDA(cudaSetDevice(ctx->device));
+    MRB_TRY(ctx->arena.reset());
+    const size_t n = plan->d.count();
+    Out<float> o;
+    MRB_TRY(o.init(ctx, F_out, n));
+    MRB_LAUNCH(ctx, k_assemble_F_b, grid_for(ctx, n, 256), 256, 0, plan->vol, plan->flags, plan->bid, x_dev, plan->bd,
+               (size_t)plan->Q + 1, (double)plan->band_size + 1.0, o.dev);
+    MRB_TRY(o.commit(ctx));
+    return sync(ctx);
+}
+
+}  // extern "C"
