@@ -71,6 +71,9 @@ SYMBOLS = {
     "mrb_qp_plan_init_x": (C.c_int, [_VP, _VP]),
     "mrb_qp_plan_sweep": (C.c_int, [_VP, _VP, _VP, C.c_int, C.c_int]),
     "mrb_qp_plan_assemble": (C.c_int, [_VP, _VP, _VP]),
+    "mrb_qp_plan_solve_sharded": (C.c_int, [_VP, C.c_int, C.c_int, C.POINTER(_VP), C.POINTER(_VP), C.POINTER(_VP), c_int_p,
+                                            C.c_int]),
+    "mrb_qp_plan_last_kernel_ms": (C.c_float, [_VP]),
     "mrb_reconstruct_batch": (C.c_int, [_VP, _VP, c_int_p, C.c_int, C.POINTER(Options), C.POINTER(Mesh), c_int_p,
                                         c_int_p]),
 }

@@ -688,6 +688,118 @@ __global__ void __launch_bounds__(256) k_qp_bricks_range(const uint2* __restrict
                  __ldg(fields + (size_t)Q + q), in, out, s_sqrt, s_inv, false);
 }
 
+// ---- slab-sharded persistent kernel: sweep + halo exchange over NVLink peer memory in ONE kernel ---------------
+// Rank r owns the brick range [qa, qb) (its x-slab).  The iterate buffers of all ranks are peer-mapped (symmetric
+// memory); the bricks of the first / last owned brick plane are stored into the neighbour rank's buffer as well,
+// so the halo travels with the sweep's own stores, tile by tile, instead of in a separate exchange step.
+// Synchronisation per sweep: the local neighbour-only progress words (as in k_qp_bricks) plus, for the blocks
+// that own boundary-plane bricks, one flag per direction in the neighbour's memory: each such block fences at
+// system scope and bumps a local counter; the last one stores the sweep number into the neighbour's flag; the
+// same blocks wait for the neighbour's flag before the next sweep (which also protects the ping-pong buffers:
+// a neighbour only starts writing sweep k+1 halos after it has seen our sweep-k flag).
+struct ShardArgs {
+    int qa, qb;               // owned brick range
+    int lo0, lo1, hi0, hi1;   // first / last owned plane: [lo0,lo1) is sent down, [hi0,hi1) is sent up (empty if no neighbour)
+    float4* peer_lo[2];       // lower neighbour's iterate buffers (A, B), nullptr if none
+    float4* peer_hi[2];
+    unsigned* flag_lo_remote; // lower neighbour's "from_upper" slots (one per boundary block of this rank)
+    unsigned* flag_hi_remote; // upper neighbour's "from_lower" slots
+    unsigned* flags_local;    // [0, 128) from_lower slots, [128, 256) from_upper slots
+    int first_lo, first_hi;   // first block of this rank that owns lo / hi plane bricks (slot = block - first)
+    int nrem_lo, nrem_hi;     // boundary blocks of the lower / upper neighbour (slots to wait for)
+};
+static const int kShardSlots = 128;
+
+__device__ __forceinline__ void spin_until(const unsigned* p, unsigned target) {
+    unsigned v, spins = 0;
+    do {
+        asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+        if (++spins == (1u << 27)) __trap();          // a lost neighbour must not hang the GPU
+    } while (v < target);
+}
+
+template <int Threads, int MinBlocks>
+__global__ void __launch_bounds__(Threads, MinBlocks) k_qp_bricks_sharded(const uint2* __restrict__ code, const uint4* __restrict__ fields,
+                                                                          const int4* __restrict__ nbA, const int2* __restrict__ nbB,
+                                                                          float4* xa, float4* xb, int Q, int iters, ShardArgs sh,
+                                                                          const int* __restrict__ blk_lo, const int* __restrict__ blk_hi,
+                                                                          unsigned* progress) {
+    __shared__ float s_sqrt[256];
+    __shared__ float s_inv[32];
+    for (int i = threadIdx.x; i < 256; i += Threads) s_sqrt[i] = c_brick_sqrt[i];
+    if (threadIdx.x < 32) s_inv[threadIdx.x] = c_brick_invdg[threadIdx.x];
+    __syncthreads();
+    const size_t P = (size_t)Q + 1;
+    const int Ql = sh.qb - sh.qa;
+    const int q_begin = sh.qa + (int)((long long)Ql * blockIdx.x / gridDim.x);
+    const int q_end = sh.qa + (int)((long long)Ql * (blockIdx.x + 1) / gridDim.x);
+    const int nlo = blk_lo[blockIdx.x], nhi = blk_hi[blockIdx.x];
+    const bool has_lo = sh.peer_lo[0] != nullptr && q_begin < sh.lo1 && q_end > sh.lo0;
+    const bool has_hi = sh.peer_hi[0] != nullptr && q_begin < sh.hi1 && q_end > sh.hi0;
+    float4* in = xa;
+    float4* out = xb;
+    for (int it = 0; it < iters; it++) {
+        float4* plo = sh.peer_lo[(it + 1) & 1];       // sweep `it` writes buffer B when it is even
+        float4* phi = sh.peer_hi[(it + 1) & 1];
+        for (int q = q_begin + threadIdx.x; q < q_end; q += Threads) {
+            const int4 na = __ldg(nbA + q);
+            const int2 nz = __ldg(nbB + q);
+            brick_update(q, P, na, nz, __ldg(code + q), __ldg(fields + q), __ldg(fields + (size_t)Q + q), in, out, s_sqrt, s_inv, false);
+            // boundary planes: the same values go into the neighbour's halo over NVLink
+            if (plo && q >= sh.lo0 && q < sh.lo1) {
+#pragma unroll
+                for (int k = 0; k < 4; k++) plo[k * P + q] = out[k * P + q];
+            }
+            if (phi && q >= sh.hi0 && q < sh.hi1) {
+#pragma unroll
+                for (int k = 0; k < 4; k++) phi[k * P + q] = out[k * P + q];
+            }
+        }
+        float4* t = in; in = out; out = t;
+        if (it + 1 == iters) break;
+        const unsigned epoch = (unsigned)(it + 1);
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(progress + (size_t)blockIdx.x * kProgressStride), "r"(epoch) : "memory");
+            // every boundary block owns one slot in the neighbour's memory: release at system scope orders this
+            // block's peer stores (bar.sync above makes them cumulative) before the sweep number becomes visible
+            if (has_lo)
+                asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(sh.flag_lo_remote + (blockIdx.x - sh.first_lo)), "r"(epoch) : "memory");
+            if (has_hi)
+                asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(sh.flag_hi_remote + (blockIdx.x - sh.first_hi)), "r"(epoch) : "memory");
+        }
+        // local neighbours (block-level progress words)
+        for (int c = nlo + (int)threadIdx.x; c <= nhi; c += Threads) {
+            if (c == (int)blockIdx.x) continue;
+            unsigned v;
+            do {
+                asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(progress + (size_t)c * kProgressStride) : "memory");
+            } while (v < epoch);
+        }
+        // remote neighbours (halo planes written by the other GPU)
+        if (has_lo && (int)threadIdx.x < sh.nrem_lo) { spin_until(sh.flags_local + threadIdx.x, epoch); __threadfence_system(); }
+        if (has_hi && (int)threadIdx.x < sh.nrem_hi) { spin_until(sh.flags_local + kShardSlots + threadIdx.x, epoch); __threadfence_system(); }
+        __syncthreads();
+    }
+}
+
+// block -> [lo, hi] neighbour blocks for a local range [qa, qb) split over G blocks
+__global__ void k_block_ranges_local(const int4* __restrict__ nbA, const int2* __restrict__ nbB, int qa, int qb, int G,
+                                     int* __restrict__ lo, int* __restrict__ hi) {
+    int q = qa + blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= qb) return;
+    const int Ql = qb - qa;
+    const int b = brick_owner(q - qa, Ql, G);
+    const int4 a = nbA[q];
+    const int2 z = nbB[q];
+    const int n[6] = {a.x, a.y, a.z, a.w, z.x, z.y};
+    int mn = b, mx = b;
+    for (int i = 0; i < 6; i++)
+        if (n[i] >= qa && n[i] < qb) { int o = brick_owner(n[i] - qa, Ql, G); mn = min(mn, o); mx = max(mx, o); }
+    if (mn < b) atomicMin(&lo[b], mn);
+    if (mx > b) atomicMax(&hi[b], mx);
+}
+
 }  // namespace mrb
 
 struct mrb_qp_plan {
@@ -827,6 +939,100 @@ int mrb_qp_plan_sweep(mrb_qp_plan* plan, const float* x_in_dev, float* x_out_dev
         MRB_LAUNCH(ctx, k_qp_bricks_range, cdiv((size_t)(q_end - q_begin), 256), 256, 0, plan->code, plan->fields, plan->nbA,
                    plan->nbB, (const float4*)x_in_dev, (float4*)x_out_dev, plan->Q, q_begin, q_end);
     return sync(ctx);
+}
+
+// Blocks of a G-block split of [qa, qb) whose range intersects [p0, p1): count and first block.
+static int blocks_touching(int qa, int qb, int G, int p0, int p1, int* first) {
+    *first = 0;
+    if (p1 <= p0) return 0;
+    int n = 0;
+    const long long Ql = qb - qa;
+    for (int b = 0; b < G; b++) {
+        int s = qa + (int)(Ql * b / G), e = qa + (int)(Ql * (b + 1) / G);
+        if (s < p1 && e > p0) { if (n == 0) *first = b; n++; }
+    }
+    return n;
+}
+// Grid size every rank uses for a range of Ql bricks (all ranks run the same GPU model and kernel).
+static int shard_grid(int fit, int sm_count, int Ql, int threads) {
+    int grid = fit * sm_count, need = (Ql + threads - 1) / threads;
+    return grid > need ? need : grid;
+}
+
+int mrb_qp_plan_solve_sharded(mrb_qp_plan* plan, int rank, int world, void* const* xa_ptrs, void* const* xb_ptrs,
+                              void* const* flag_ptrs, const int* plane_cuts, int iters) {
+    MRB_REQUIRE(plan && xa_ptrs && xb_ptrs && flag_ptrs && plane_cuts && world >= 1 && rank >= 0 && rank < world && iters >= 0,
+                "bad argument");
+    mrb_ctx* ctx = plan->ctx;
+    MRB_CUDA(cudaSetDevice(ctx->device));
+    MRB_TRY(ctx->arena.reset());
+    const std::vector<int>& po = plan->plane_off;
+    for (int r = 0; r < world; r++)
+        MRB_REQUIRE(plane_cuts[r] < plane_cuts[r + 1] && po[plane_cuts[r]] < po[plane_cuts[r + 1]], "every rank must own at least one brick");
+    MRB_REQUIRE(plane_cuts[0] == 0 && plane_cuts[world] == plan->bd.bx, "plane cuts must cover the grid");
+    const int Xa = plane_cuts[rank], Xb = plane_cuts[rank + 1];
+    ShardArgs sh;
+    memset(&sh, 0, sizeof(sh));
+    sh.qa = po[Xa]; sh.qb = po[Xb];
+    if (rank > 0) {
+        sh.lo0 = po[Xa]; sh.lo1 = po[Xa + 1];
+        sh.peer_lo[0] = (float4*)xa_ptrs[rank - 1]; sh.peer_lo[1] = (float4*)xb_ptrs[rank - 1];
+        sh.flag_lo_remote = (unsigned*)flag_ptrs[rank - 1] + kShardSlots;   // the lower rank's "from_upper" slots
+    }
+    if (rank < world - 1) {
+        sh.hi0 = po[Xb - 1]; sh.hi1 = po[Xb];
+        sh.peer_hi[0] = (float4*)xa_ptrs[rank + 1]; sh.peer_hi[1] = (float4*)xb_ptrs[rank + 1];
+        sh.flag_hi_remote = (unsigned*)flag_ptrs[rank + 1] + 0;             // the upper rank's "from_lower" slots
+    }
+    sh.flags_local = (unsigned*)flag_ptrs[rank];
+    if (iters == 0 || sh.qb == sh.qa) return sync(ctx);
+    const int threads = 256;
+    void* kern = (void*)k_qp_bricks_sharded<256, 2>;
+    int fit = 0;
+    MRB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&fit, kern, threads, 0));
+    if (fit < 1) { set_error("k_qp_bricks_sharded does not fit on an SM"); return MRB_ECUDA; }
+    const int Ql = sh.qb - sh.qa;
+    const int grid = shard_grid(fit, ctx->sm_count, Ql, threads);
+    int dummy = 0;
+    const int nlo_mine = blocks_touching(sh.qa, sh.qb, grid, sh.lo0, sh.lo1, &sh.first_lo);
+    const int nhi_mine = blocks_touching(sh.qa, sh.qb, grid, sh.hi0, sh.hi1, &sh.first_hi);
+    if (rank > 0) {            // the lower neighbour's blocks that own its LAST plane (they fill my from_lower slots)
+        const int a = po[plane_cuts[rank - 1]], b = po[plane_cuts[rank]];
+        sh.nrem_lo = blocks_touching(a, b, shard_grid(fit, ctx->sm_count, b - a, threads), po[plane_cuts[rank] - 1], b, &dummy);
+    }
+    if (rank < world - 1) {    // the upper neighbour's blocks that own its FIRST plane
+        const int a = po[plane_cuts[rank + 1]], b = po[plane_cuts[rank + 2]];
+        sh.nrem_hi = blocks_touching(a, b, shard_grid(fit, ctx->sm_count, b - a, threads), a, po[plane_cuts[rank + 1] + 1], &dummy);
+    }
+    if (nlo_mine > kShardSlots || nhi_mine > kShardSlots || sh.nrem_lo > kShardSlots || sh.nrem_hi > kShardSlots) {
+        set_error("mrb_qp_plan_solve_sharded: more than %d boundary blocks per side", kShardSlots);
+        return MRB_EINVAL;
+    }
+    int *blk_lo = nullptr, *blk_hi = nullptr;
+    unsigned* progress = nullptr;
+    MRB_TRY(arena_alloc(ctx, (size_t)grid, &blk_lo));
+    MRB_TRY(arena_alloc(ctx, (size_t)grid, &blk_hi));
+    MRB_TRY(arena_alloc(ctx, (size_t)grid * kProgressStride, &progress));
+    MRB_CUDA(cudaMemsetAsync(progress, 0, (size_t)grid * kProgressStride * sizeof(unsigned), ctx->stream));
+    MRB_LAUNCH(ctx, k_block_ranges_init, cdiv(grid, 256), 256, 0, blk_lo, blk_hi, grid);
+    MRB_LAUNCH(ctx, k_block_ranges_local, cdiv((size_t)Ql, 256), 256, 0, plan->nbA, plan->nbB, sh.qa, sh.qb, grid, blk_lo, blk_hi);
+    float4* xa = (float4*)xa_ptrs[rank];
+    float4* xb = (float4*)xb_ptrs[rank];
+    int Q = plan->Q, its = iters;
+    void* args[] = {(void*)&plan->code, (void*)&plan->fields, (void*)&plan->nbA, (void*)&plan->nbB, (void*)&xa, (void*)&xb,
+                    (void*)&Q, (void*)&its, (void*)&sh, (void*)&blk_lo, (void*)&blk_hi, (void*)&progress};
+    MRB_CUDA(cudaEventRecord(ctx->ev[6], ctx->stream));
+    MRB_CUDA(cudaLaunchCooperativeKernel(kern, dim3(grid), dim3(threads), args, 0, ctx->stream));
+    MRB_CUDA(cudaEventRecord(ctx->ev[7], ctx->stream));
+    ctx->launches++;
+    return sync(ctx);
+}
+
+/* Device time (ms) of the last persistent sweep kernel launched on this plan's context. */
+float mrb_qp_plan_last_kernel_ms(mrb_qp_plan* plan) {
+    float ms = 0.0f;
+    if (plan) cudaEventElapsedTime(&ms, plan->ctx->ev[6], plan->ctx->ev[7]);
+    return ms;
 }
 
 int mrb_qp_plan_assemble(mrb_qp_plan* plan, const float* x_dev, float* F_out) {

@@ -121,6 +121,7 @@ def solve_emulated(ctx, volume, nranks, iters=500, band_size=4):
     x = torch.zeros_like(xin[0])
     for r in range(nranks):
         x[:, owned[r][0]:owned[r][1], :] = xin[r][:, owned[r][0]:owned[r][1], :]
+    torch.cuda.synchronize()
     F = plan.assemble(x)
     plan.close()
     return F
@@ -168,6 +169,75 @@ def solve_distributed(ctx, volume, iters=500, band_size=4, timings=None):
     x = torch.zeros_like(xin)
     x[:, owned[rank][0]:owned[rank][1], :] = xin[:, owned[rank][0]:owned[rank][1], :]
     dist.all_reduce(x)                               # disjoint supports: x + 0 is exact
+    torch.cuda.synchronize()
+    F = plan.assemble(x)
+    plan.close()
+    return F
+
+
+def balanced_cuts(plane_off, world):
+    """world+1 brick-plane boundaries with balanced brick counts and at least one occupied plane per rank."""
+    groups = slab_planes(plane_off, world)
+    cuts = [g[0] for g in groups] + [groups[-1][1]]
+    occupied = [X for X in range(len(plane_off) - 1) if plane_off[X + 1] > plane_off[X]]
+    if len(occupied) < world:
+        raise ValueError("fewer occupied brick planes (%d) than ranks (%d)" % (len(occupied), world))
+    # repair empty groups by moving cuts onto occupied planes
+    for r in range(1, world):
+        lo = occupied[r - 1] + 1
+        hi = occupied[len(occupied) - (world - r)]
+        cuts[r] = min(max(cuts[r], lo, cuts[r - 1] + 1), hi)
+    return cuts
+
+
+def solve_fused(ctx, volume, iters=500, band_size=4, timings=None):
+    """Slab-sharded solve with the halo exchange INSIDE the persistent kernel: every rank's iterate buffers and a
+    small flag block live in torch symmetric memory (peer-mapped over NVLink); mrb_qp_plan_solve_sharded stores the
+    boundary brick planes straight into the neighbours' buffers and synchronises with per-sweep flags.
+    Works with world size 1 (no process group needed).  Every rank returns the full F."""
+    import torch
+    import torch.distributed as dist
+    distributed = dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
+    world = dist.get_world_size() if distributed else 1
+    rank = dist.get_rank() if distributed else 0
+    plan = Plan(ctx, volume, band_size)
+    cuts = balanced_cuts(plan.plane_off, world)
+    nfloat = 16 * (plan.Q + 1)
+    if distributed:
+        import torch.distributed._symmetric_memory as symm_mem
+        group = dist.group.WORLD.group_name
+        xa = symm_mem.empty(nfloat, dtype=torch.float32, device=plan.device)
+        xb = symm_mem.empty(nfloat, dtype=torch.float32, device=plan.device)
+        flags = symm_mem.empty(256, dtype=torch.int32, device=plan.device)
+        ha, hb, hf = (symm_mem.rendezvous(t, group) for t in (xa, xb, flags))
+        pa, pb, pf = list(ha.buffer_ptrs), list(hb.buffer_ptrs), list(hf.buffer_ptrs)
+    else:
+        xa = torch.empty(nfloat, dtype=torch.float32, device=plan.device)
+        xb = torch.empty(nfloat, dtype=torch.float32, device=plan.device)
+        flags = torch.empty(256, dtype=torch.int32, device=plan.device)
+        pa, pb, pf = [xa.data_ptr()], [xb.data_ptr()], [flags.data_ptr()]
+    flags.zero_()
+    plan._check(plan.lib.mrb_qp_plan_init_x(plan.h, C.c_void_p(xa.data_ptr())))
+    plan._check(plan.lib.mrb_qp_plan_init_x(plan.h, C.c_void_p(xb.data_ptr())))
+    torch.cuda.synchronize()
+    if distributed:
+        dist.barrier()
+        torch.cuda.synchronize()
+    VP = C.c_void_p * world
+    ccuts = (C.c_int * (world + 1))(*cuts)
+    plan._check(plan.lib.mrb_qp_plan_solve_sharded(plan.h, rank, world, VP(*pa), VP(*pb), VP(*pf), ccuts, int(iters)))
+    if timings is not None:
+        timings["kernel_ms"] = float(plan.lib.mrb_qp_plan_last_kernel_ms(plan.h))
+        timings["n_band"] = plan.n_band
+        timings["cuts"] = cuts
+    res = (xb if iters % 2 else xa).view(4, plan.Q + 1, 4)
+    q0, q1 = int(plan.plane_off[cuts[rank]]), int(plan.plane_off[cuts[rank + 1]])
+    x = torch.zeros((4, plan.Q + 1, 4), dtype=torch.float32, device=plan.device)
+    x[:, q0:q1, :] = res[:, q0:q1, :]
+    if distributed:
+        dist.barrier()                               # nobody frees peer-mapped buffers while a neighbour still runs
+        dist.all_reduce(x)
+    torch.cuda.synchronize()                         # the library works on its own stream: x must be complete
     F = plan.assemble(x)
     plan.close()
     return F

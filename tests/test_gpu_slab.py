@@ -37,3 +37,12 @@ def test_slab_planes_partition():
         g = slab.slab_planes(off, w)
         assert g[0][0] == 0 and g[-1][1] == 6
         assert all(g[i][1] == g[i + 1][0] for i in range(w - 1))
+
+
+def test_fused_sharded_kernel_world1(ctx, synth):
+    """The slab-sharded persistent kernel with a single rank (no peers) == mrb_optimize."""
+    from mesh_reconstruction_b200 import slab
+    v = synth.union(synth.sphere(64, 20.0), synth.box(64, (24, 8, 8), None, 0.0, 0.0))
+    for iters in (1, 40, 41):
+        F = slab.solve_fused(ctx, v, iters=iters).cpu().numpy()
+        assert np.array_equal(F, ctx.optimize(v, iters=iters)), iters

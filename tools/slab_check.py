@@ -18,14 +18,24 @@ ctx = mrb.Context(local)
 v = synth.sphere(size, size / 2.0 - 18.0)
 vt = torch.from_numpy(v).cuda(local)
 F_ref, st = ctx.optimize(vt, iters=iters, return_stats=True)
+mode = sys.argv[3] if len(sys.argv) > 3 else "fused"
 t = {}
-F = slab.solve_distributed(ctx, vt, iters=iters, timings=t)
+if mode == "nccl":
+    F = slab.solve_distributed(ctx, vt, iters=iters, timings=t)
+else:
+    slab.solve_fused(ctx, vt, iters=min(iters, 20))        # warm-up (module load, symmetric-memory setup)
+    F = slab.solve_fused(ctx, vt, iters=iters, timings=t)
+    t["solve_ms"] = t["kernel_ms"]
 ok = bool(torch.equal(F, F_ref))
+if not ok and dist.get_rank() == 0:
+    bad = (F != F_ref).nonzero()
+    print("mismatch voxels", len(bad), "x range", int(bad[:, 0].min()), int(bad[:, 0].max()), "cuts", t.get("cuts"),
+          "max abs diff", float((F - F_ref).abs().max()), flush=True)
 flag = torch.tensor([1 if ok else 0], device=vt.device)
 dist.all_reduce(flag, op=dist.ReduceOp.MIN)
 if dist.get_rank() == 0:
     print(json.dumps({"slab_check": "ok" if int(flag) else "MISMATCH", "world": dist.get_world_size(), "size": size, "iters": iters,
-                      "n_band": st["n_band"], "single_gpu_kernel_ms": st["ms_qp_kernel"], "slab_solve_ms": t["solve_ms"],
+                      "n_band": st["n_band"], "single_gpu_kernel_ms": st["ms_qp_kernel"], "mode": mode, "slab_solve_ms": t["solve_ms"],
                       "us_per_sweep_slab": 1000.0 * t["solve_ms"] / iters}))
 dist.destroy_process_group()
 sys.exit(0 if int(flag) else 1)
