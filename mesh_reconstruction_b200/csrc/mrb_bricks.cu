@@ -760,13 +760,16 @@ __global__ void __launch_bounds__(Threads, MinBlocks) k_qp_bricks_sharded(const 
         const unsigned epoch = (unsigned)(it + 1);
         __syncthreads();
         if (threadIdx.x == 0) {
-            asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(progress + (size_t)blockIdx.x * kProgressStride), "r"(epoch) : "memory");
-            // every boundary block owns one slot in the neighbour's memory: release at system scope orders this
-            // block's peer stores (bar.sync above makes them cumulative) before the sweep number becomes visible
+            // ONE fence (system scope for boundary blocks: it also covers the stores into the neighbour GPU, which
+            // the bar.sync above made cumulative), then relaxed stores of the sweep number: the block's own progress
+            // word and, for boundary blocks, its slot in the neighbour's memory
+            if (has_lo || has_hi) asm volatile("fence.acq_rel.sys;" ::: "memory");
+            else asm volatile("fence.acq_rel.gpu;" ::: "memory");
+            asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(progress + (size_t)blockIdx.x * kProgressStride), "r"(epoch) : "memory");
             if (has_lo)
-                asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(sh.flag_lo_remote + (blockIdx.x - sh.first_lo)), "r"(epoch) : "memory");
+                asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(sh.flag_lo_remote + (blockIdx.x - sh.first_lo)), "r"(epoch) : "memory");
             if (has_hi)
-                asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(sh.flag_hi_remote + (blockIdx.x - sh.first_hi)), "r"(epoch) : "memory");
+                asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(sh.flag_hi_remote + (blockIdx.x - sh.first_hi)), "r"(epoch) : "memory");
         }
         // local neighbours (block-level progress words)
         for (int c = nlo + (int)threadIdx.x; c <= nhi; c += Threads) {
