@@ -180,6 +180,14 @@ typedef struct mrb_mesh {
 int  mrb_mcubes(mrb_ctx* ctx, const float* F, const int dims[3], float isolevel,
                 int device_out, mrb_mesh* out);
 void mrb_mesh_free(mrb_mesh* mesh);
+/* mcubes with USING_FEATURES (mcubes.cpp:592-662): isFeature per cell, least-squares feature points with triangle
+ * fans, flipEdges between neighbouring feature cells, then the same hash de-duplication.  surface_map / normals are
+ * getIndexMap(volume, getSurface(volume)) and getSurfaceNormals.  The feature point solve is our own definition
+ * (include/mrb_eig3.h, include/mrb_feature_mc.h) in place of Eigen::JacobiSVD: parity unpinned against the
+ * reference, bit-exact against our oracle. */
+int  mrb_mcubes_features(mrb_ctx* ctx, const float* F, const float* surface_map, const float* normals, int nnormals,
+                         const int dims[3], float isolevel, float feat_thresh, float corner_thresh,
+                         int device_out, mrb_mesh* out);
 /* hashXYZ (hasher.h:99-104) for n points (xyz interleaved); keys_out: n uint64. */
 int  mrb_hash_points(mrb_ctx* ctx, const float* xyz, int n, const int dims[3], uint64_t* keys_out);
 /* ASCII PLY exactly as mcubes.cpp:626-660 (vertices through grid::getCloudPoint, grid.cpp:204-210). */

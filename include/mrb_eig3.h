@@ -84,4 +84,35 @@ MRB_HD void mrb_normal_from_covariance(const float cov[9], float n[3]) {
     n[0] = n[0] / len; n[1] = n[1] / len; n[2] = n[2] / len;
 }
 
+/* computePoint (mcubes.cpp:142-152): least-squares solution of  M p = vec  (M: n x 3 rows of unit normals) plus
+ * the centroid shift.  The reference uses Eigen::JacobiSVD (+ setThreshold for edge features); our DEFINITION (shared
+ * by oracle and GPU, parity unpinned against Eigen) goes through the 3x3 normal equations and the Jacobi solver above:
+ *   A = M^T M = V diag(w) V^T,  sigma_i = sqrt(max(w_i, 0)),  p = sum_{kept i} v_i (v_i . M^T vec) / w_i,
+ * keeping sigma_i > thr * sigma_max with thr = sigma_min / (sigma_max - 0.0001) for edges (this always drops the
+ * smallest singular value: the solution is constrained to the edge line's normal plane) and
+ * thr = 3 * FLT_EPSILON for corners (Eigen's default rank threshold for a 3-column matrix). */
+MRB_HD void mrb_feature_point(const float* M, const float* vec, int n, const float shift[3], int is_edge, float out[3]) {
+    float a[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0}, b[3] = {0, 0, 0}, w[3], v[9], sg[3];
+    float smax, smin, thr, p[3] = {0, 0, 0};
+    int i, r, c;
+    for (i = 0; i < n; i++)
+        for (r = 0; r < 3; r++) {
+            for (c = 0; c < 3; c++) a[r * 3 + c] = a[r * 3 + c] + M[i * 3 + r] * M[i * 3 + c];
+            b[r] = b[r] + M[i * 3 + r] * vec[i];
+        }
+    mrb_eig3_jacobi(a, w, v);
+    for (i = 0; i < 3; i++) sg[i] = sqrtf(w[i] > 0.0f ? w[i] : 0.0f);
+    smax = sg[0]; smin = sg[0];
+    for (i = 1; i < 3; i++) { if (sg[i] > smax) smax = sg[i]; if (sg[i] < smin) smin = sg[i]; }
+    thr = is_edge ? smin / (smax - 0.0001f) : 3.0f * 1.1920929e-7f;
+    for (i = 0; i < 3; i++) {
+        if (sg[i] > thr * smax) {
+            float proj = v[0 * 3 + i] * b[0] + v[1 * 3 + i] * b[1] + v[2 * 3 + i] * b[2];
+            float coef = proj / w[i];
+            p[0] = p[0] + v[0 * 3 + i] * coef; p[1] = p[1] + v[1 * 3 + i] * coef; p[2] = p[2] + v[2 * 3 + i] * coef;
+        }
+    }
+    out[0] = p[0] + shift[0]; out[1] = p[1] + shift[1]; out[2] = p[2] + shift[2];
+}
+
 #endif /* MRB_EIG3_H */

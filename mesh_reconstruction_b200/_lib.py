@@ -59,6 +59,8 @@ SYMBOLS = {
     "mrb_optimize": (C.c_int, [_VP, _VP, _VP, c_int_p, C.c_int, C.c_int, C.c_int, _VP, C.POINTER(QPStats)]),
     "mrb_mcubes": (C.c_int, [_VP, _VP, c_int_p, C.c_float, C.c_int, C.POINTER(Mesh)]),
     "mrb_mesh_free": (None, [C.POINTER(Mesh)]),
+    "mrb_mcubes_features": (C.c_int, [_VP, _VP, _VP, _VP, C.c_int, c_int_p, C.c_float, C.c_float, C.c_float, C.c_int,
+                                      C.POINTER(Mesh)]),
     "mrb_hash_points": (C.c_int, [_VP, _VP, C.c_int, c_int_p, _VP]),
     "mrb_write_ply": (C.c_int, [C.c_char_p, _VP, C.c_int, _VP, C.c_int, c_float_p, c_float_p, C.c_int]),
     "mrb_options_default": (None, [C.POINTER(Options)]),

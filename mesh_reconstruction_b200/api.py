@@ -252,6 +252,17 @@ class Context:
             self.write_ply(filename, verts, faces, scale, shift, pad)
         return verts, faces
 
+    def mcubes_features(self, F, surfaceMap, normals, isolevel=0.0, feat_thresh=0.75, corner_thresh=0.8):
+        """mcubes(..., USING_FEATURES=true) (mcubes.h:354): feature points, triangle fans and edge flips."""
+        kF, pF, shape, like = self._in(F)
+        km, pm, _, _ = self._in(surfaceMap)
+        kn, pn, nshape, _ = self._in(normals)
+        m = L.Mesh()
+        self._check(self.lib.mrb_mcubes_features(self.h, pF, pm, pn, int(nshape[0]), self._dims(shape), float(isolevel),
+                                                 float(feat_thresh), float(corner_thresh), 1 if like is not None else 0,
+                                                 C.byref(m)))
+        return self._take_mesh(m, like)
+
     def hashXYZ(self, xyz, shape):
         kx, px, s, like = self._in(np.asarray(xyz, np.float32).reshape(-1, 3))
         keys = np.empty(s[0], np.uint64)
@@ -270,12 +281,15 @@ class Context:
                                            C.c_void_p(f.ctypes.data), len(f), sc, sh, int(pad)))
 
     # ---- fused ---------------------------------------------------------------------------------
-    def reconstruct(self, volume, band_size=4, iters=500, isolevel=0.0, return_stats=False):
+    def reconstruct(self, volume, band_size=4, iters=500, isolevel=0.0, return_stats=False, using_features=False,
+                    feature_threshold=0.75, corner_threshold=0.8):
         """optimize + mcubes, device-resident between the stages (mesh_reconstruction.cpp:131-134)."""
         kv, pv, shape, like = self._in(volume)
         opt = L.Options()
         self.lib.mrb_options_default(C.byref(opt))
         opt.band_size, opt.iters, opt.isolevel = int(band_size), int(iters), float(isolevel)
+        opt.using_features = 1 if using_features else 0
+        opt.feature_threshold, opt.corner_threshold = float(feature_threshold), float(corner_threshold)
         m = L.Mesh()
         st = L.QPStats()
         self._check(self.lib.mrb_reconstruct(self.h, pv, self._dims(shape), C.byref(opt),

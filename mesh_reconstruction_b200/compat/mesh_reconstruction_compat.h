@@ -325,16 +325,15 @@ class pointHashmap {      // vertex ids in first-appearance order, keyed by hash
     }
 };
 
-// surfaceMap / normals / thresholds are only consumed when USING_FEATURES (mcubes.cpp:176-183, 234-311).
+// surfaceMap / normals / thresholds are only consumed when USING_FEATURES (mcubes.cpp:176-183, 234-311, 396-588).
 inline void mcubes(gridPtr in, gridPtr surfaceMap, const std::vector<Eigen::Vector3f>& normals, float isolevel,
                    float feat_thresh, float corner_thresh, const char* filename, const bool USING_FEATURES) {
-    (void)surfaceMap; (void)normals; (void)feat_thresh; (void)corner_thresh;
-    if (USING_FEATURES) {
-        std::cerr << "mcubes: the --feature-detection path is not available in libmrb yet" << std::endl;
-        std::exit(1);
-    }
     mrb_mesh mesh;
-    mrbcompat::check(mrb_mcubes(mrbcompat::ctx(), in->data(), &in->dims[0], isolevel, 0, &mesh));
+    if (USING_FEATURES)
+        mrbcompat::check(mrb_mcubes_features(mrbcompat::ctx(), in->data(), surfaceMap->data(), normals.empty() ? nullptr : &normals[0][0],
+                                             (int)normals.size(), &in->dims[0], isolevel, feat_thresh, corner_thresh, 0, &mesh));
+    else
+        mrbcompat::check(mrb_mcubes(mrbcompat::ctx(), in->data(), &in->dims[0], isolevel, 0, &mesh));
     mrbcompat::check(mrb_write_ply(filename, mesh.verts, mesh.nverts, mesh.faces, mesh.nfaces, &in->scale[0], &in->shift[0], in->pad));
     mrb_mesh_free(&mesh);
 }

@@ -49,17 +49,47 @@ int mrb_optimize(mrb_ctx* ctx, const float* volume, const float* feature_map, co
     return sync(ctx);
 }
 
+// --feature-detection end to end (mesh_reconstruction.cpp:123-134): getSurface, getIndexMap, getSurfaceNormals,
+// getFeatureMap, optimize(USING_FEATURES), mcubes(USING_FEATURES).  Composed from the module-level entry points on
+// device buffers that live outside the per-call arena (each entry point resets the arena).
+static int reconstruct_with_features(mrb_ctx* ctx, const float* volume, const int dims[3], const mrb_options& o, int device_out,
+                                     mrb_mesh* out, mrb_qp_stats* stats) {
+    MRB_CUDA(cudaSetDevice(ctx->device));
+    memset(out, 0, sizeof(*out));
+    const size_t n = (size_t)dims[0] * dims[1] * dims[2];
+    float *vol = nullptr, *smap = nullptr, *fmap = nullptr, *F = nullptr, *normals = nullptr;
+    int* surf = nullptr;
+    int rc = MRB_OK, ns = 0;
+    auto fail = [&](int code) { cudaFree(vol); cudaFree(smap); cudaFree(fmap); cudaFree(F); cudaFree(normals); cudaFree(surf); return code; };
+    if (cudaMalloc((void**)&vol, n * 4) != cudaSuccess || cudaMalloc((void**)&smap, n * 4) != cudaSuccess ||
+        cudaMalloc((void**)&fmap, n * 4) != cudaSuccess || cudaMalloc((void**)&F, n * 4) != cudaSuccess) {
+        cudaGetLastError(); set_error("mrb_reconstruct: cudaMalloc failed"); return fail(MRB_ENOMEM);
+    }
+    if ((rc = mrb_copy(ctx, vol, volume, n * 4)) != MRB_OK) return fail(rc);
+    if ((rc = mrb_get_surface(ctx, vol, dims, nullptr, 0, &ns)) != MRB_OK) return fail(rc);
+    if (cudaMalloc((void**)&surf, (size_t)(ns > 0 ? ns : 1) * 4) != cudaSuccess ||
+        cudaMalloc((void**)&normals, (size_t)(ns > 0 ? ns : 1) * 12) != cudaSuccess) {
+        cudaGetLastError(); set_error("mrb_reconstruct: cudaMalloc failed"); return fail(MRB_ENOMEM);
+    }
+    if (ns > 0 && (rc = mrb_get_surface(ctx, vol, dims, surf, ns, &ns)) != MRB_OK) return fail(rc);
+    if ((rc = mrb_index_map(ctx, dims, surf, ns, smap)) != MRB_OK) return fail(rc);
+    if ((rc = mrb_surface_normals(ctx, vol, dims, surf, ns, normals)) != MRB_OK) return fail(rc);
+    if ((rc = mrb_feature_map(ctx, vol, smap, normals, ns, dims, o.feature_threshold, fmap)) != MRB_OK) return fail(rc);
+    if ((rc = mrb_optimize(ctx, vol, fmap, dims, 1, o.band_size, o.iters, F, stats)) != MRB_OK) return fail(rc);
+    rc = mrb_mcubes_features(ctx, F, smap, normals, ns, dims, o.isolevel, o.feature_threshold, o.corner_threshold, device_out, out);
+    if (rc == MRB_OK && device_out) {
+        // the mesh lives in the arena (valid until the next call); nothing to do
+    }
+    return fail(rc);
+}
+
 int mrb_reconstruct(mrb_ctx* ctx, const float* volume, const int dims[3], const mrb_options* opt, int device_out,
                     mrb_mesh* out, mrb_qp_stats* stats) {
     MRB_REQUIRE(ctx && volume && dims && out, "NULL argument");
     mrb_options o;
     if (opt) o = *opt; else mrb_options_default(&o);
     MRB_REQUIRE(o.band_size >= 1 && o.band_size <= 64 && o.iters >= 0, "bad band_size / iters");
-    if (o.using_features) {
-        set_error("mrb_reconstruct: the --feature-detection path (getSurfaceNormals/getFeatureMap/feature MC) "
-                  "is not implemented on the GPU yet");
-        return MRB_EINVAL;
-    }
+    if (o.using_features) return reconstruct_with_features(ctx, volume, dims, o, device_out, out, stats);
     MRB_CUDA(cudaSetDevice(ctx->device));
     MRB_TRY(ctx->arena.reset());
     memset(out, 0, sizeof(*out));

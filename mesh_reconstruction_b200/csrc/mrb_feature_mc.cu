@@ -1,0 +1,205 @@
+// mrb_feature_mc.cu -- marching cubes with feature points and edge flips (mcubes with USING_FEATURES).
+//
+// Replaces getGridCells + isFeature, the feature branch of Polygonise, flipEdges and the concatenation in mcubes
+// (marching_cubes/mcubes.cpp:9-152, 157-312, 396-588, 592-616).  Per-cell arithmetic = include/mrb_feature_mc.h (shared
+// with the oracle; parity unpinned against the reference's Eigen::JacobiSVD, bit-exact against our oracle).
+//
+//   1. classify   sign-bit planes -> ordered list of crossing cells (mrb_mcubes.cu)
+//   2. polygonise one thread per crossing cell: feature class, feature point, triangle fan or table triangles
+//   3. flip       flipEdges is order dependent (a cell's triangle list is edited by every earlier neighbour), so
+//                 the feature cells are visited in cell order by ONE warp: for each (cell, neighbour) pair the
+//                 lanes test the triangle pairs for a shared edge in parallel, lane 0 applies the flips in the
+//                 reference's order.  Only feature cells take part (a few thousand on sharp-edged shapes).
+//   4. emit       remaining per-cell triangles in cell order, then the flipped triangles; hashXYZ keys; de-dup.
+#include "mrb_internal.cuh"
+#include "mrb_compact.cuh"
+#include "mc_tables.h"
+#include "../../include/mrb_feature_mc.h"
+
+#include <string.h>
+
+namespace mrb {
+
+__constant__ uint64_t c_tri_f[256] = MRB_MC_TRI_WORDS;
+__constant__ int c_ea_f[12] = {0, 1, 2, 3, 4, 5, 6, 7, 0, 1, 2, 3};
+__constant__ int c_eb_f[12] = {1, 2, 3, 0, 5, 6, 7, 4, 4, 5, 6, 7};
+
+__global__ void k_fill_i32f(int* __restrict__ p, size_t n, int v) {
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) p[i] = v;
+}
+__global__ void k_scatter_slots(const int* __restrict__ cells, int n, int* __restrict__ cellmap) {
+    int a = blockIdx.x * blockDim.x + threadIdx.x;
+    if (a < n) cellmap[cells[a]] = a;
+}
+
+__global__ void __launch_bounds__(64) k_feat_polygonise(const float* __restrict__ F, const float* __restrict__ smap,
+                                                        const float* __restrict__ normals, int nnormals, Dims d,
+                                                        const int* __restrict__ cells, int ncells, float iso, float ft,
+                                                        float ct, MrbFeatCell* __restrict__ out, int* __restrict__ err) {
+    int a = blockIdx.x * blockDim.x + threadIdx.x;
+    if (a >= ncells) return;
+    const int cy = d.ny - 1, cz = d.nz - 1;
+    int cell = cells[a];
+    int k = cell % cz, t = cell / cz, j = t % cy, i = t / cy;
+    float val[8];
+    int nidx[8], cubeindex = 0, ea[12], eb[12];
+    for (int n = 0; n < 8; n++) {
+        size_t q = d.at(i + ((((n % 4) == 1) || ((n % 4) == 2)) ? 1 : 0), j + (n % 4) / 2, k + n / 4);
+        val[n] = F[q];
+        nidx[n] = (int)smap[q];
+        if (nidx[n] < -1 || nidx[n] >= nnormals) { *err = 1; nidx[n] = -1; }
+        if (val[n] < iso) cubeindex |= (1 << n);
+    }
+    for (int e = 0; e < 12; e++) { ea[e] = c_ea_f[e]; eb[e] = c_eb_f[e]; }
+    MrbFeatCell c;
+    mrb_polygonise_feature(i, j, k, val, nidx, normals, iso, ft, ct, c_tri_f[cubeindex], cubeindex, ea, eb, &c);
+    out[a] = c;
+}
+
+struct FeaturePred {
+    const MrbFeatCell* c;
+    __device__ bool operator()(size_t a) const { return c[a].feature != 0; }
+};
+
+// flipEdges (mcubes.cpp:434-588) by one warp.  fcells: slots of the feature cells in cell order.
+__global__ void __launch_bounds__(32) k_flip_edges(MrbFeatCell* cellsv, const int* __restrict__ cells, const int* __restrict__ fcells,
+                                                   int nf, const int* __restrict__ cellmap, Dims d, MrbTri* __restrict__ new_tris,
+                                                   int cap, int* __restrict__ nnew_out, int* __restrict__ err) {
+    const int lane = threadIdx.x;
+    const int cx = d.nx - 1, cy = d.ny - 1, cz = d.nz - 1;
+    __shared__ int s_si[MRB_FEAT_MAX_TRI * MRB_FEAT_MAX_TRI], s_sj[MRB_FEAT_MAX_TRI * MRB_FEAT_MAX_TRI];
+    __shared__ unsigned char s_flag[MRB_FEAT_MAX_TRI * MRB_FEAT_MAX_TRI];
+    int nnew = 0;
+    for (int f = 0; f < nf; f++) {
+        const int a = fcells[f];
+        MrbFeatCell* c = cellsv + a;
+        if (c->feature == 0) continue;
+        const int id = cells[a];
+        const int z = id % cz, y = (id / cz) % cy, x = id / (cz * cy);
+        int nb[6], nn = 0;
+        if (x != 0) nb[nn++] = id - cy * cz;
+        if (x != cx - 1) nb[nn++] = id + cy * cz;
+        if (y != 0) nb[nn++] = id - cz;
+        if (y != cy - 1) nb[nn++] = id + cz;
+        if (z != 0) nb[nn++] = id - 1;
+        if (z != cz - 1) nb[nn++] = id + 1;
+        for (int q = 0; q < nn; q++) {
+            const int b = cellmap[nb[q]];
+            if (b < 0) continue;                       // not a surface cell
+            MrbFeatCell* n = cellsv + b;
+            if (n->feature == 0) continue;
+            const int nc = c->ntri, nnb = n->ntri, np = nc * nnb;
+            for (int p = lane; p < np; p += 32) s_flag[p] = (unsigned char)mrb_flip_shared(c, n, p / nnb, p % nnb);
+            __syncwarp();
+            if (lane == 0) {
+                int ns = 0;
+                for (int p = 0; p < np; p++)
+                    if (s_flag[p]) { s_si[ns] = p / nnb; s_sj[ns] = p % nnb; ns++; }
+                if (ns > 0) {
+                    if (nnew + 2 * ns > cap) { *err = 2; }
+                    else nnew += mrb_flip_apply(c, n, s_si, s_sj, ns, new_tris + nnew, cap - nnew);
+                }
+            }
+            nnew = __shfl_sync(0xffffffffu, nnew, 0);
+            __threadfence_block();
+            __syncwarp();
+        }
+    }
+    if (lane == 0) *nnew_out = nnew;
+}
+
+__global__ void k_feat_counts(const MrbFeatCell* __restrict__ c, int n, int* __restrict__ cnt) {
+    int a = blockIdx.x * blockDim.x + threadIdx.x;
+    if (a < n) cnt[a] = c[a].ntri;
+}
+
+__device__ __forceinline__ unsigned long long hash_p3(MrbP3 s, int ny, int nz) {      // hashXYZ, hasher.h:99-104
+    unsigned long long val = (unsigned long long)__dmul_rn(__dmul_rn((double)s.x, 1000000000.0), (double)(ny * nz));
+    val += (unsigned long long)__dmul_rn(__dmul_rn((double)s.y, 1000000.0), (double)nz);
+    val += (unsigned long long)__dmul_rn((double)s.z, 1000.0);
+    return val;
+}
+__device__ __forceinline__ void put_tri(const MrbTri& t, size_t tri, float* __restrict__ soup, unsigned long long* __restrict__ keys,
+                                        int ny, int nz) {
+    for (int v = 0; v < 3; v++) {
+        soup[tri * 9 + v * 3 + 0] = t.p[v].x; soup[tri * 9 + v * 3 + 1] = t.p[v].y; soup[tri * 9 + v * 3 + 2] = t.p[v].z;
+        keys[tri * 3 + v] = hash_p3(t.p[v], ny, nz);
+    }
+}
+__global__ void k_feat_emit(const MrbFeatCell* __restrict__ c, int n, const int* __restrict__ off, float* __restrict__ soup,
+                            unsigned long long* __restrict__ keys, int ny, int nz) {
+    int a = blockIdx.x * blockDim.x + threadIdx.x;
+    if (a >= n) return;
+    for (int t = 0; t < c[a].ntri; t++) put_tri(c[a].tri[t], (size_t)off[a] + t, soup, keys, ny, nz);
+}
+__global__ void k_feat_emit_new(const MrbTri* __restrict__ tris, int n, int first, float* __restrict__ soup,
+                                unsigned long long* __restrict__ keys, int ny, int nz) {
+    int a = blockIdx.x * blockDim.x + threadIdx.x;
+    if (a < n) put_tri(tris[a], (size_t)first + a, soup, keys, ny, nz);
+}
+
+}  // namespace mrb
+
+using namespace mrb;
+
+extern "C" int mrb_mcubes_features(mrb_ctx* ctx, const float* F, const float* surface_map, const float* normals, int nnormals,
+                                   const int dims[3], float isolevel, float feat_thresh, float corner_thresh, int device_out,
+                                   mrb_mesh* out) {
+    MRB_REQUIRE(ctx && F && surface_map && dims && out && nnormals >= 0 && (nnormals == 0 || normals), "bad argument");
+    MRB_CUDA(cudaSetDevice(ctx->device));
+    MRB_TRY(ctx->arena.reset());
+    memset(out, 0, sizeof(*out));
+    Dims d = mkdims(dims);
+    if (d.nx < 2 || d.ny < 2 || d.nz < 2) return MRB_OK;
+    const float *dF = nullptr, *dm = nullptr, *dn = nullptr;
+    MRB_TRY(stage_in(ctx, F, d.count(), &dF));
+    MRB_TRY(stage_in(ctx, surface_map, d.count(), &dm));
+    MRB_TRY(stage_in(ctx, normals, (size_t)(nnormals > 0 ? nnormals : 1) * 3, &dn));
+    int* cells = nullptr;
+    int ncells = 0;
+    MRB_TRY(classify_cells(ctx, dF, d, isolevel, &cells, &ncells));
+    if (ncells == 0) return MRB_OK;
+    const size_t ncell_total = (size_t)(d.nx - 1) * (d.ny - 1) * (d.nz - 1);
+    int* cellmap = nullptr;
+    MrbFeatCell* fc = nullptr;
+    MRB_TRY(arena_alloc(ctx, ncell_total, &cellmap));
+    MRB_TRY(arena_alloc(ctx, (size_t)ncells, &fc));
+    size_t want = (ncell_total + 255) / 256, cap = (size_t)ctx->sm_count * 16;
+    MRB_LAUNCH(ctx, k_fill_i32f, (unsigned)(want < cap ? want : cap), 256, 0, cellmap, ncell_total, -1);
+    MRB_LAUNCH(ctx, k_scatter_slots, cdiv(ncells, 256), 256, 0, cells, ncells, cellmap);
+    int* err = ctx->d_mail + 54;
+    MRB_CUDA(cudaMemsetAsync(err, 0, 2 * sizeof(int), ctx->stream));
+    MRB_LAUNCH(ctx, k_feat_polygonise, cdiv(ncells, 64), 64, 0, dF, dm, dn, nnormals, d, cells, ncells, isolevel, feat_thresh,
+               corner_thresh, fc, err);
+    int* fcells = nullptr;
+    int nf = 0;
+    MRB_TRY(compact(ctx, FeaturePred{fc}, (size_t)ncells, &fcells, &nf));
+    MrbTri* new_tris = nullptr;
+    const int ncap = nf > 0 ? nf * 24 : 1;                 // every feature cell shares edges with a few neighbours
+    MRB_TRY(arena_alloc(ctx, (size_t)ncap, &new_tris));
+    int* nnew_dev = ctx->d_mail + 55;
+    if (nf > 0) MRB_LAUNCH(ctx, k_flip_edges, 1, 32, 0, fc, cells, fcells, nf, cellmap, d, new_tris, ncap, nnew_dev, err);
+    int* tri_off = nullptr;
+    MRB_TRY(arena_alloc(ctx, (size_t)ncells, &tri_off));
+    MRB_LAUNCH(ctx, k_feat_counts, cdiv(ncells, 256), 256, 0, fc, ncells, tri_off);
+    MRB_TRY(scan_exclusive(ctx, tri_off, tri_off, (size_t)ncells, ctx->d_mail));
+    MRB_CUDA(cudaMemcpyAsync(ctx->h_mail, ctx->d_mail, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    MRB_CUDA(cudaMemcpyAsync(ctx->h_mail + 54, err, 2 * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    MRB_TRY(sync(ctx));
+    if (ctx->h_mail[54] == 1) { set_error("mrb_mcubes_features: surface map refers to a normal index outside [0, nnormals)"); return MRB_EINVAL; }
+    if (ctx->h_mail[54] == 2) { set_error("mrb_mcubes_features: flipped-triangle buffer overflow"); return MRB_ECAPACITY; }
+    const int ntri_cells = ctx->h_mail[0], nnew = nf > 0 ? ctx->h_mail[55] : 0, ntri = ntri_cells + nnew;
+    if (ntri == 0) return MRB_OK;
+    float* soup = nullptr;
+    unsigned long long* keys = nullptr;
+    int* faces = nullptr;
+    MRB_TRY(arena_alloc(ctx, (size_t)ntri * 9, &soup));
+    MRB_TRY(arena_alloc(ctx, (size_t)ntri * 3, &keys));
+    MRB_TRY(arena_alloc(ctx, (size_t)ntri * 3, &faces));
+    MRB_LAUNCH(ctx, k_feat_emit, cdiv(ncells, 128), 128, 0, fc, ncells, tri_off, soup, keys, d.ny, d.nz);
+    if (nnew > 0) MRB_LAUNCH(ctx, k_feat_emit_new, cdiv(nnew, 128), 128, 0, new_tris, nnew, ntri_cells, soup, keys, d.ny, d.nz);
+    float* verts = nullptr;
+    int nv = 0;
+    MRB_TRY(dev_dedup(ctx, soup, keys, ntri * 3, faces, &verts, &nv));
+    return export_mesh(ctx, verts, faces, nv, ntri, device_out, out);
+}

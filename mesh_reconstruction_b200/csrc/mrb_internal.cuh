@@ -171,6 +171,12 @@ int dev_qp_solve(mrb_ctx* ctx, const BandDev& bd, Dims d, int band_size, int ite
 int dev_feature_reset(mrb_ctx* ctx, const int* feat_dev, int nfeat, int n, float* x);
 int dev_assemble_F(mrb_ctx* ctx, const float* volume, const BandDev& bd, const float* x, Dims d, int band_size,
                    float* F);
+// ordered list of surface-crossing cells (linear cell ids over (nx-1, ny-1, nz-1), k fastest)
+int classify_cells(mrb_ctx* ctx, const float* F, Dims d, float iso, int** cells_out, int* ncells_out);
+// triangle soup (3 floats per corner) + hashXYZ keys -> per-corner vertex ids and unique vertices (first-appearance order)
+int dev_dedup(mrb_ctx* ctx, const float* soup, const unsigned long long* keys, int ncorner, int* faces, float** verts_out,
+              int* nverts_out);
+int export_mesh(mrb_ctx* ctx, float* verts_dev, int* faces_dev, int nverts, int nfaces, int device_out, mrb_mesh* out);
 int dev_mcubes(mrb_ctx* ctx, const float* F, Dims d, float isolevel, float** verts_dev, int** faces_dev,
                int* nverts, int* nfaces);
 

@@ -317,7 +317,8 @@ __global__ void __launch_bounds__(256) k_cell_list(const uint32_t* __restrict__ 
     }
 }
 
-static int classify_cells(mrb_ctx* ctx, const float* F, Dims d, const CellDims& cd, float iso, int** cells_out, int* ncells_out) {
+int classify_cells(mrb_ctx* ctx, const float* F, Dims d, float iso, int** cells_out, int* ncells_out) {
+    const CellDims cd{d.nx, d.ny, d.nz, d.nx - 1, d.ny - 1, d.nz - 1};
     const int nzw = (d.nz + 31) / 32;
     const size_t nwords = (size_t)d.nx * d.ny * nzw, ncw = (size_t)cd.cx * cd.cy * nzw;
     uint32_t *sb = nullptr, *aw = nullptr;
@@ -350,7 +351,7 @@ int dev_mcubes(mrb_ctx* ctx, const float* F, Dims d, float isolevel, float** ver
     int* cells = nullptr;
     int ncells = 0;
     (void)ncell_total;
-    MRB_TRY(classify_cells(ctx, F, d, cd, isolevel, &cells, &ncells));
+    MRB_TRY(classify_cells(ctx, F, d, isolevel, &cells, &ncells));
     if (ncells == 0) return MRB_OK;
     int* tri_off = nullptr;
     MRB_TRY(arena_alloc(ctx, (size_t)ncells, &tri_off));

@@ -779,3 +779,85 @@ int mrbo_feature_map(const float* vol, const float* surface_map, const float* no
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+// Feature-preserving marching cubes (mcubes with USING_FEATURES, mcubes.cpp:592-662): getGridCells + isFeature,
+// Polygonise with feature points, flipEdges, concatenation, pointHashmap.  The per-cell arithmetic is the shared
+// definition in include/mrb_feature_mc.h (PARITY UNPINNED against the reference's Eigen::JacobiSVD); the loops --
+// cell order, neighbour order (x-1, x+1, y-1, y+1, z-1, z+1), triangle concatenation -- are restated here.
+// ---------------------------------------------------------------------------------------------
+#include "../include/mrb_feature_mc.h"
+
+extern "C" int mrbo_mcubes_features(const float* F, const float* surface_map, const float* normals, int nnormals,
+                                    const int* dims, float isolevel, float feat_thresh, float corner_thresh, mrbo_mesh* out) {
+    (void)nnormals;
+    Dims d = mk(dims);
+    const int cx = d.nx - 1, cy = d.ny - 1, cz = d.nz - 1;
+    int ea[12], eb[12];
+    for (int e = 0; e < 12; e++) { ea[e] = kEdgeCorner[e][0]; eb[e] = kEdgeCorner[e][1]; }
+    std::vector<MrbFeatCell> cells;                  // surface-crossing cells only, in (i,j,k) order
+    std::vector<long long> cell_id;                  // their linear cell index
+    std::unordered_map<long long, int> slot;
+    for (int i = 0; i < cx; i++)
+        for (int j = 0; j < cy; j++)
+            for (int k = 0; k < cz; k++) {
+                float val[8];
+                int nidx[8], cubeindex = 0;
+                for (int n = 0; n < 8; n++) {
+                    int x = i + (int)((n % 4 == 1) || (n % 4) == 2), y = j + ((n % 4) / 2), z = k + (n / 4);
+                    val[n] = F[at(d, x, y, z)];
+                    nidx[n] = (int)surface_map[at(d, x, y, z)];
+                    if (val[n] < isolevel) cubeindex |= (1 << n);
+                }
+                if (cubeindex == 0 || cubeindex == 255) continue;     // edgeTable == 0: isSurface = false, no triangles
+                MrbFeatCell c;
+                mrb_polygonise_feature(i, j, k, val, nidx, normals, isolevel, feat_thresh, corner_thresh, kTri[cubeindex],
+                                       cubeindex, ea, eb, &c);
+                long long id = ((long long)i * cy + j) * cz + k;
+                slot[id] = (int)cells.size();
+                cell_id.push_back(id);
+                cells.push_back(c);
+            }
+    // flipEdges, mcubes.cpp:434-588 (cells without triangles cannot take part, so only crossing cells are visited)
+    std::vector<MrbTri> new_tris;
+    for (size_t a = 0; a < cells.size(); a++) {
+        if (cells[a].feature == 0) continue;
+        long long id = cell_id[a];
+        int z = (int)(id % cz), y = (int)((id / cz) % cy), x = (int)(id / ((long long)cz * cy));
+        long long nb[6];
+        int nn = 0;
+        if (x != 0) nb[nn++] = id - (long long)cy * cz;
+        if (x != cx - 1) nb[nn++] = id + (long long)cy * cz;
+        if (y != 0) nb[nn++] = id - cz;
+        if (y != cy - 1) nb[nn++] = id + cz;
+        if (z != 0) nb[nn++] = id - 1;
+        if (z != cz - 1) nb[nn++] = id + 1;
+        for (int q = 0; q < nn; q++) {
+            auto it = slot.find(nb[q]);
+            if (it == slot.end() || cells[it->second].feature == 0) continue;
+            MrbTri buf[2 * MRB_FEAT_MAX_TRI * MRB_FEAT_MAX_TRI];
+            int m = mrb_flip_pair(&cells[a], &cells[it->second], buf, 2 * MRB_FEAT_MAX_TRI * MRB_FEAT_MAX_TRI);
+            for (int t = 0; t < m; t++) new_tris.push_back(buf[t]);
+        }
+    }
+    // all_triangles = per-cell lists in cell order ++ new_triangles (mcubes.cpp:606-616); pointHashmap
+    std::vector<XYZ> tri_pts;
+    for (auto& c : cells)
+        for (int t = 0; t < c.ntri; t++)
+            for (int v = 0; v < 3; v++) tri_pts.push_back(XYZ{c.tri[t].p[v].x, c.tri[t].p[v].y, c.tri[t].p[v].z});
+    for (auto& t : new_tris)
+        for (int v = 0; v < 3; v++) tri_pts.push_back(XYZ{t.p[v].x, t.p[v].y, t.p[v].z});
+    std::unordered_map<uint64_t, int> map;
+    std::vector<XYZ> points;
+    for (size_t i = 0; i < tri_pts.size(); i++) {
+        uint64_t id = hash_xyz(tri_pts[i], d);
+        if (map.find(id) == map.end()) { map[id] = (int)points.size(); points.push_back(tri_pts[i]); }
+    }
+    out->nverts = (int)points.size();
+    out->nfaces = (int)(tri_pts.size() / 3);
+    out->verts = (float*)std::malloc(sizeof(float) * 3 * std::max<size_t>(1, points.size()));
+    out->faces = (int*)std::malloc(sizeof(int) * std::max<size_t>(1, tri_pts.size()));
+    for (size_t i = 0; i < points.size(); i++) { out->verts[3 * i] = points[i].x; out->verts[3 * i + 1] = points[i].y; out->verts[3 * i + 2] = points[i].z; }
+    for (size_t i = 0; i < tri_pts.size(); i++) out->faces[i] = map.at(hash_xyz(tri_pts[i], d));
+    return 0;
+}

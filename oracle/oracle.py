@@ -224,3 +224,16 @@ def feature_map(vol, surface_map, normals, threshold):
     _check(lib().mrbo_feature_map(vp, mp, nrp, len(nr), _dims(v.shape), C.c_float(threshold),
                                   out.ctypes.data_as(C.POINTER(C.c_float))), "feature_map")
     return out
+
+
+def mcubes_features(F, surface_map, normals, isolevel=0.0, feat_thresh=0.75, corner_thresh=0.8):
+    f, fp = _f(F)
+    m, mp = _f(surface_map)
+    nr, nrp = _f(np.asarray(normals).reshape(-1, 3))
+    mesh = _Mesh()
+    _check(lib().mrbo_mcubes_features(fp, mp, nrp, len(nr), _dims(f.shape), C.c_float(isolevel), C.c_float(feat_thresh),
+                                      C.c_float(corner_thresh), C.byref(mesh)), "mcubes_features")
+    verts = np.ctypeslib.as_array(mesh.verts, shape=(max(mesh.nverts, 1), 3))[:mesh.nverts].copy()
+    faces = np.ctypeslib.as_array(mesh.faces, shape=(max(mesh.nfaces, 1), 3))[:mesh.nfaces].copy()
+    lib().mrbo_mesh_free(C.byref(mesh))
+    return verts, faces

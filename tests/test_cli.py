@@ -74,3 +74,15 @@ def test_cli_end_to_end(cli, synth, ctx, tmp_path):
     subprocess.run([cli, bv, pcd, str(out) + ".x", "--dump-volume", str(vol_path)], capture_output=True, text=True)
     verts, f2 = ctx.reconstruct(read_volume(vol_path))
     assert len(verts) == nv and np.array_equal(f2, faces)
+
+
+@pytest.mark.gpu
+def test_cli_feature_detection(cli, synth, tmp_path):
+    bv, pcd = synth.cli_inputs(str(tmp_path))
+    out = tmp_path / "feat.ply"
+    r = subprocess.run([cli, bv, pcd, str(out), "--feature-detection", "--cuda", "--feature-threshold", "0.8"],
+                       capture_output=True, text=True)
+    assert r.returncode == 1, r.stdout + r.stderr
+    assert "Using feature detection" in r.stdout and "Feature threshold is 0.8" in r.stdout
+    lines = out.read_text().splitlines()
+    assert lines[0] == "ply" and int(lines[2].split()[-1]) > 1000 and int(lines[6].split()[-1]) > 2000

@@ -50,3 +50,35 @@ def test_border_volume_is_an_error(ctx):
     v[0:4, 3:7, 3:7] = 1.0
     with pytest.raises(mrb.MrbError):
         ctx.getSurface(v)
+
+
+def test_feature_marching_cubes(ctx, O, synth):
+    """mcubes with USING_FEATURES: feature points, fans, edge flips -- GPU == oracle, topology and coordinates."""
+    for name, v in shapes(synth):
+        s = O.get_surface(v)
+        n = O.surface_normals(v, s)
+        smap = O.index_map(v.shape, s)
+        fm = O.feature_map(v, smap, n, 0.75)
+        F = O.optimize(v, fm, using_features=True)
+        verts_ref, faces_ref = O.mcubes_features(F, smap, n, 0.0, 0.75, 0.8)
+        verts, faces = ctx.mcubes_features(F, smap, n, 0.0, 0.75, 0.8)
+        assert faces.shape == faces_ref.shape and verts.shape == verts_ref.shape, name
+        assert np.array_equal(faces, faces_ref), name
+        assert np.array_equal(verts, verts_ref), name
+        # and it really differs from plain marching cubes on shapes with sharp edges
+        if name.startswith("box"):
+            v0, f0 = O.mcubes(F, 0.0)
+            assert len(faces) != len(f0)
+
+
+def test_reconstruct_with_feature_detection(ctx, O, synth):
+    """The whole --feature-detection pipeline in one call (mesh_reconstruction.cpp:123-134) == the oracle's composition."""
+    v = synth.union(synth.box(64, (18, 14, 10), None, 20.0, 35.0), synth.sphere(64, 14.0))
+    s = O.get_surface(v)
+    n = O.surface_normals(v, s)
+    smap = O.index_map(v.shape, s)
+    fm = O.feature_map(v, smap, n, 0.75)
+    F = O.optimize(v, fm, using_features=True)
+    verts_ref, faces_ref = O.mcubes_features(F, smap, n, 0.0, 0.75, 0.8)
+    verts, faces = ctx.reconstruct(v, using_features=True)
+    assert np.array_equal(faces, faces_ref) and np.array_equal(verts, verts_ref)
