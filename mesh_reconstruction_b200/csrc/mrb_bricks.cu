@@ -177,10 +177,11 @@ struct BrickRegs {
 
 __device__ __forceinline__ void put4(float (&d)[4], const float4 v) { d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w; }
 
-template <int DX, int DY, int J>
+template <int DX, int DY, int J, bool Fast = false>
 __device__ __forceinline__ float brick_voxel(const BrickRegs& r, uint32_t lo, uint32_t hi, uint32_t field,
                                              const float* __restrict__ s_sqrt, const float* __restrict__ s_inv) {
     constexpr int K = DX * 2 + DY, V = K * 4 + J;
+    if (Fast) { lo = 0xffffffffu; hi = 0xffffffffu; }      // timing experiment only (MRB_QP_DEBUG=32): all coefficients constant
     const bool a = lo & (1u << V);
     const bool txm = DX == 0 ? (lo & (1u << (16 + DY * 4 + J))) : (lo & (1u << ((0 * 2 + DY) * 4 + J)));
     const bool txp = DX == 0 ? (lo & (1u << ((1 * 2 + DY) * 4 + J))) : (lo & (1u << (24 + DY * 4 + J)));
@@ -228,15 +229,15 @@ __device__ __forceinline__ float brick_voxel(const BrickRegs& r, uint32_t lo, ui
     return fminf(fmaxf(t, lb), ub);
 }
 
-template <int K>
+template <int K, bool Fast = false>
 __device__ __forceinline__ float4 brick_strip(const BrickRegs& r, uint32_t lo, uint32_t hi, uint32_t w0, uint32_t w1,
                                               const float* __restrict__ s_sqrt, const float* __restrict__ s_inv) {
     constexpr int DX = K >> 1, DY = K & 1;
     float4 o;
-    o.x = brick_voxel<DX, DY, 0>(r, lo, hi, w0 & 0xffffu, s_sqrt, s_inv);
-    o.y = brick_voxel<DX, DY, 1>(r, lo, hi, w0 >> 16, s_sqrt, s_inv);
-    o.z = brick_voxel<DX, DY, 2>(r, lo, hi, w1 & 0xffffu, s_sqrt, s_inv);
-    o.w = brick_voxel<DX, DY, 3>(r, lo, hi, w1 >> 16, s_sqrt, s_inv);
+    o.x = brick_voxel<DX, DY, 0, Fast>(r, lo, hi, w0 & 0xffffu, s_sqrt, s_inv);
+    o.y = brick_voxel<DX, DY, 1, Fast>(r, lo, hi, w0 >> 16, s_sqrt, s_inv);
+    o.z = brick_voxel<DX, DY, 2, Fast>(r, lo, hi, w1 & 0xffffu, s_sqrt, s_inv);
+    o.w = brick_voxel<DX, DY, 3, Fast>(r, lo, hi, w1 >> 16, s_sqrt, s_inv);
     return o;
 }
 
@@ -255,6 +256,7 @@ __device__ __forceinline__ void brick_grid_barrier(unsigned* bar, unsigned epoch
 }
 
 // One Jacobi update of brick q: reads the iterate planes `in` (stride P), writes `out`.  Returns max |delta|.
+template <bool Fast = false>
 __device__ __forceinline__ float brick_update(int q, size_t P, const int4 na, const int2 nz, const uint2 c, const uint4 f0,
                                               const uint4 f1, const float4* in, float4* out, const float* __restrict__ s_sqrt,
                                               const float* __restrict__ s_inv, bool want_delta) {
@@ -273,10 +275,10 @@ __device__ __forceinline__ float brick_update(int q, size_t P, const int4 na, co
         r.zl[k][0] = l.x; r.zl[k][1] = l.y;
         r.zh[k][0] = h.x; r.zh[k][1] = h.y;
     }
-    const float4 o0 = brick_strip<0>(r, c.x, c.y, f0.x, f0.y, s_sqrt, s_inv);
-    const float4 o1 = brick_strip<1>(r, c.x, c.y, f0.z, f0.w, s_sqrt, s_inv);
-    const float4 o2 = brick_strip<2>(r, c.x, c.y, f1.x, f1.y, s_sqrt, s_inv);
-    const float4 o3 = brick_strip<3>(r, c.x, c.y, f1.z, f1.w, s_sqrt, s_inv);
+    const float4 o0 = brick_strip<0, Fast>(r, c.x, c.y, f0.x, f0.y, s_sqrt, s_inv);
+    const float4 o1 = brick_strip<1, Fast>(r, c.x, c.y, f0.z, f0.w, s_sqrt, s_inv);
+    const float4 o2 = brick_strip<2, Fast>(r, c.x, c.y, f1.x, f1.y, s_sqrt, s_inv);
+    const float4 o3 = brick_strip<3, Fast>(r, c.x, c.y, f1.z, f1.w, s_sqrt, s_inv);
     out[q] = o0; out[P + q] = o1; out[2 * P + q] = o2; out[3 * P + q] = o3;
     float dmax = 0.0f;
     if (want_delta) {
@@ -501,6 +503,205 @@ __global__ void __launch_bounds__(Threads, MinBlocks) k_qp_bricks(const uint2* _
     }
 }
 
+// ---- tiled brick order + boundary-first sweeps -----------------------------------------------------------------
+// In (X,Y,Z) order every brick of a block has its X+-1 neighbours in other blocks, so a block can publish
+// "sweep done" only after ALL its work and then sits through the release -> poll round trip (~1.3 us of the
+// ~7 us sweep at 256^3).  Here bricks are numbered along x-slabs of T brick columns, (slab, Y, x in slab, Z):
+// a block's contiguous id range is a compact T x L patch of columns, and only the bricks on the rim of the
+// patch are read by other blocks.  Inside each block's range the rim ("boundary") bricks are numbered first.
+// A sweep is then: wait for the neighbours' previous sweep, update the boundary bricks, publish, update the
+// interior bricks (which touch only this block's own bricks) while the flag travels.  The neighbours' flags
+// have usually arrived long before the next sweep polls them.  Results do not depend on the numbering: every
+// brick update reads the previous iterate only.
+struct TiledOrder {
+    BrickDims bd;
+    int T;
+    __host__ __device__ size_t count() const { return (size_t)((bd.bx + T - 1) / T) * T * bd.by * bd.bz; }
+    // traversal index -> linear brick-grid position (X*by + Y)*bz + Z, or -1 in the padding of the last slab
+    __host__ __device__ long long position(size_t i) const {
+        const int Z = (int)(i % bd.bz);
+        size_t t = i / bd.bz;
+        const int x = (int)(t % T);
+        t /= T;
+        const int Y = (int)(t % bd.by);
+        const int X = (int)(t / bd.by) * T + x;
+        if (X >= bd.bx) return -1;
+        return ((long long)X * bd.by + Y) * bd.bz + Z;
+    }
+};
+struct TiledBrickPred {
+    ActiveBrickPred base;
+    TiledOrder ord;
+    __device__ bool operator()(size_t i) const {
+        const long long p = ord.position(i);
+        return p >= 0 && base((size_t)p);
+    }
+};
+__global__ void k_tiled_scatter(const int* __restrict__ tpos, int Q, TiledOrder ord, int* __restrict__ bid1) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < Q) bid1[ord.position((size_t)tpos[i])] = i;
+}
+// isb[i] = 1 if a neighbour brick of i (tile-order id) belongs to another block
+__global__ void k_tiled_boundary(const int* __restrict__ tpos, int Q, int G, TiledOrder ord, const int* __restrict__ bid1,
+                                 int* __restrict__ isb) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= Q) return;
+    const BrickDims bd = ord.bd;
+    const long long p = ord.position((size_t)tpos[i]);
+    const int Z = (int)(p % bd.bz);
+    const long long t = p / bd.bz;
+    const int Y = (int)(t % bd.by), X = (int)(t / bd.by);
+    const int own = brick_owner(i, Q, G);
+    const long long cx = (long long)bd.by * bd.bz, cy = bd.bz;
+    bool rim = false;
+    auto look = [&](bool ok, long long dp) {
+        if (!ok) return;
+        const int id = bid1[p + dp];
+        if (id >= 0 && brick_owner(id, Q, G) != own) rim = true;
+    };
+    look(X >= 1, -cx); look(X <= bd.bx - 2, cx); look(Y >= 1, -cy); look(Y <= bd.by - 2, cy);
+    look(Z >= 1, -1); look(Z <= bd.bz - 2, 1);
+    isb[i] = rim ? 1 : 0;
+}
+// final id = block begin + (boundary ? rank among the block's boundary bricks : #boundary + rank among its interior bricks)
+__global__ void k_tiled_final(const int* __restrict__ tpos, const int* __restrict__ sb, int Q, int G, TiledOrder ord,
+                              int* __restrict__ bpos, int* __restrict__ bid, int* __restrict__ blk_nb) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= Q) return;
+    const int b = brick_owner(i, Q, G);
+    const int qb = (int)((long long)Q * b / G), qe = (int)((long long)Q * (b + 1) / G);
+    const int nbc = sb[qe] - sb[qb];
+    const int rank_b = sb[i] - sb[qb];
+    const bool rim = sb[i + 1] != sb[i];
+    const int id = rim ? qb + rank_b : qb + nbc + (i - qb) - rank_b;
+    const int p = (int)ord.position((size_t)tpos[i]);
+    bpos[id] = p;
+    bid[p] = id;
+    if (i == qb) blk_nb[b] = nbc;
+}
+
+template <int Threads, int MinBlocks>
+__global__ void __launch_bounds__(Threads, MinBlocks) k_qp_bricks_tiled(const uint2* __restrict__ code, const uint4* __restrict__ fields,
+                                                                        const int4* __restrict__ nbA, const int2* __restrict__ nbB,
+                                                                        float4* xa, float4* xb, int Q, int iters,
+                                                                        unsigned* __restrict__ maxdelta_bits, unsigned* bar, int dbg,
+                                                                        const int* __restrict__ blk_nb, unsigned* progress, int cap,
+                                                                        const int* __restrict__ plist, const int* __restrict__ pcount) {
+    __shared__ float s_sqrt[256];
+    __shared__ float s_inv[32];
+    for (int i = threadIdx.x; i < 256; i += Threads) s_sqrt[i] = c_brick_sqrt[i];
+    if (threadIdx.x < 32) s_inv[threadIdx.x] = c_brick_invdg[threadIdx.x];
+    const size_t P = (size_t)Q + 1;
+    const int q_begin = (int)((long long)Q * blockIdx.x / gridDim.x);
+    const int q_end = (int)((long long)Q * (blockIdx.x + 1) / gridDim.x);
+    const int q_int = q_begin + blk_nb[blockIdx.x];          // first interior brick
+    extern __shared__ uint4 s_dyn[];
+    uint4* s_f0 = s_dyn;
+    uint4* s_f1 = s_dyn + cap;
+    int4* s_na = (int4*)(s_dyn + 2 * cap);
+    int2* s_nz = (int2*)(s_dyn + 3 * cap);
+    uint2* s_code = (uint2*)(s_nz + cap);
+    const bool smem_consts = cap > 0;
+    if (smem_consts)
+        for (int q = q_begin + threadIdx.x; q < q_end; q += Threads) {
+            const int l = q - q_begin;
+            s_na[l] = __ldg(nbA + q); s_nz[l] = __ldg(nbB + q); s_code[l] = __ldg(code + q);
+            s_f0[l] = __ldg(fields + q); s_f1[l] = __ldg(fields + (size_t)Q + q);
+        }
+    __syncthreads();
+    // the blocks whose sweep this block has to wait for (at most kChunkListCap, checked by the host)
+    const int np = pcount[blockIdx.x];
+    const unsigned *watch = nullptr, *watch2 = nullptr;      // warp 0 polls: up to two producers per lane
+    if (threadIdx.x < 32) {
+        if ((int)threadIdx.x < np) watch = progress + (size_t)plist[(size_t)blockIdx.x * kChunkListCap + threadIdx.x] * kProgressStride;
+        if ((int)threadIdx.x + 32 < np) watch2 = progress + (size_t)plist[(size_t)blockIdx.x * kChunkListCap + threadIdx.x + 32] * kProgressStride;
+    }
+    unsigned* mine = progress + (size_t)blockIdx.x * kProgressStride;
+    // interior work is dealt from the last warp down, so warp 0 (which pays for the release) gets the remainder
+    constexpr int W = Threads / 32;
+    const int rtid = (W - 1 - (int)(threadIdx.x >> 5)) * 32 + (int)(threadIdx.x & 31);
+    // warps that own boundary bricks (they arrive on s_done once per sweep)
+    __shared__ unsigned s_done;
+    if (threadIdx.x == 0) s_done = 0;
+    const unsigned s_done_addr = (unsigned)__cvta_generic_to_shared(&s_done);
+    const int nbnd = q_int - q_begin;
+    const int n_bwarps = nbnd >= Threads ? W : (nbnd + 31) / 32;
+    const bool has_boundary = (int)(threadIdx.x >> 5) < n_bwarps;
+    __syncthreads();
+    const float4* in = xa;
+    float4* out = xb;
+    auto update = [&](int q, bool last) {
+        int4 na; int2 nz; uint2 c; uint4 f0, f1;
+        if (smem_consts) {
+            const int l = q - q_begin;
+            na = s_na[l]; nz = s_nz[l]; c = s_code[l]; f0 = s_f0[l]; f1 = s_f1[l];
+        } else {
+            na = __ldg(nbA + q); nz = __ldg(nbB + q); c = __ldg(code + q);
+            f0 = __ldg(fields + q); f1 = __ldg(fields + (size_t)Q + q);
+        }
+        if (dbg & 32) return brick_update<true>(q, P, na, nz, c, f0, f1, in, out, s_sqrt, s_inv, last);
+        return brick_update(q, P, na, nz, c, f0, f1, in, out, s_sqrt, s_inv, last);
+    };
+    for (int it = 0; it < iters; it++) {
+        const bool last = it == iters - 1;
+        float dmax = 0.0f;
+        if (it > 0) {
+            if ((dbg & 4) && !(dbg & 1)) brick_grid_barrier(bar, (unsigned)it, gridDim.x);
+            __syncthreads();        // neighbour flags are in (polled below); this block's interior bricks of sweep it-1 are stored
+        }
+        for (int q = q_begin + threadIdx.x; q < q_int; q += Threads) dmax = fmaxf(dmax, update(q, last));
+        const bool flags_on = !last && !(dbg & 5);
+        if (flags_on && !(dbg & 8)) {
+            // No block-wide barrier here: every warp that updated boundary bricks fences its stores and counts itself in;
+            // warp 0 publishes the sweep once all of them have arrived.  The other warps go straight on to the interior.
+            if (has_boundary) {
+                __threadfence();
+                __syncwarp();
+                if ((threadIdx.x & 31) == 0) asm volatile("red.release.cta.shared.add.u32 [%0], 1;" ::"r"(s_done_addr) : "memory");
+            }
+            if (threadIdx.x == 0) {
+                const unsigned want = (unsigned)n_bwarps * (unsigned)(it + 1);
+                unsigned v;
+                do {
+                    asm volatile("ld.acquire.cta.shared.u32 %0, [%1];" : "=r"(v) : "r"(s_done_addr) : "memory");
+                } while (v < want);
+                if (dbg & 64) asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(mine), "r"((unsigned)(it + 1)) : "memory");
+                else asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(mine), "r"((unsigned)(it + 1)) : "memory");
+            }
+            __syncwarp();
+        }
+        for (int q = q_int + rtid; q < q_end; q += Threads) dmax = fmaxf(dmax, update(q, last));
+        if (flags_on) {
+            if (dbg & 8) {          // tuning aid: publish after the whole sweep
+                __syncthreads();
+                if (threadIdx.x == 0) asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(mine), "r"((unsigned)(it + 1)) : "memory");
+            }
+            // warp 0 (last in line for interior work) collects the neighbours' flags of this sweep
+            if (watch) {
+                unsigned v, spins = 0;
+                for (;;) {
+                    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(watch) : "memory");
+                    if (v >= (unsigned)(it + 1)) break;
+                    if (dbg & 16) __nanosleep(100);
+                    if (++spins == (1u << 26)) __trap();       // a lost producer must not hang the GPU
+                }
+                if (watch2) for (;;) {
+                    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(watch2) : "memory");
+                    if (v >= (unsigned)(it + 1)) break;
+                    if (dbg & 16) __nanosleep(100);
+                    if (++spins == (1u << 26)) __trap();
+                }
+            }
+        }
+        if (last) {
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) dmax = fmaxf(dmax, __shfl_xor_sync(0xffffffffu, dmax, o));
+            if ((threadIdx.x & 31) == 0) atomicMax(maxdelta_bits, __float_as_uint(dmax));
+        }
+        const float4* t = in; in = out; out = (float4*)t;
+    }
+}
+
 // ---- feature reset + F assembly ---------------------------------------------------------------------------------
 __device__ __forceinline__ size_t brick_slot(const int* __restrict__ bid, const BrickDims& bd, size_t P, size_t idx) {
     int z = (int)(idx % bd.nz);
@@ -545,13 +746,44 @@ int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_
     const size_t nb = bd.count();
     int* bpos = nullptr;
     int Q = 0;
-    MRB_TRY(compact(ctx, ActiveBrickPred{flags, bd}, nb, &bpos, &Q));
+    // brick numbering: x-slab tiles with boundary-first blocks (default) or plain (X,Y,Z) (MRB_QP_ORDER=xyz)
+    const char* eo = getenv("MRB_QP_ORDER");
+    const bool tiled = !(eo && strcmp(eo, "xyz") == 0) && iters > 0;
+    int tile_T = 6;
+    if (getenv("MRB_QP_TILE")) tile_T = atoi(getenv("MRB_QP_TILE"));
+    if (tile_T < 1) tile_T = 1;
+    int t_threads = 256;
+    if (getenv("MRB_QP_BRICK_THREADS") && atoi(getenv("MRB_QP_BRICK_THREADS")) == 512) t_threads = 512;
+    void* t_kern = t_threads == 512 ? (void*)k_qp_bricks_tiled<512, 1> : (void*)k_qp_bricks_tiled<256, 2>;
+    int t_grid = 0, t_fit = 0;
+    int* blk_nb = nullptr;
+    int* tpos = nullptr;
+    const TiledOrder ord{bd, tile_T};
+    if (tiled) MRB_TRY(compact(ctx, TiledBrickPred{ActiveBrickPred{flags, bd}, ord}, ord.count(), &tpos, &Q));
+    else MRB_TRY(compact(ctx, ActiveBrickPred{flags, bd}, nb, &bpos, &Q));
     *n_bricks = Q;
     *closure_err_host = 0;
     if (last_delta_host) *last_delta_host = 0.0f;
     int* bid = nullptr;
     MRB_TRY(arena_alloc(ctx, nb, &bid));
     MRB_LAUNCH(ctx, k_fill_i32b, grid_for(ctx, nb, 256), 256, 0, bid, nb, -1);
+    if (tiled && Q > 0) {
+        MRB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&t_fit, t_kern, t_threads, 0));
+        if (t_fit < 1) { set_error("k_qp_bricks_tiled does not fit on an SM"); return MRB_ECUDA; }
+        t_grid = t_fit * ctx->sm_count;
+        const int need = (Q + t_threads - 1) / t_threads;
+        if (t_grid > need) t_grid = need;
+        int *bid1 = nullptr, *sb = nullptr;
+        MRB_TRY(arena_alloc(ctx, nb, &bid1));
+        MRB_TRY(arena_alloc(ctx, (size_t)Q + 1, &sb));
+        MRB_TRY(arena_alloc(ctx, (size_t)Q, &bpos));
+        MRB_TRY(arena_alloc(ctx, (size_t)t_grid, &blk_nb));
+        MRB_LAUNCH(ctx, k_fill_i32b, grid_for(ctx, nb, 256), 256, 0, bid1, nb, -1);
+        MRB_LAUNCH(ctx, k_tiled_scatter, cdiv(Q, 256), 256, 0, tpos, Q, ord, bid1);
+        MRB_LAUNCH(ctx, k_tiled_boundary, cdiv(Q, 256), 256, 0, tpos, Q, t_grid, ord, bid1, sb);
+        MRB_TRY(scan_exclusive(ctx, sb, sb, (size_t)Q, sb + Q));
+        MRB_LAUNCH(ctx, k_tiled_final, cdiv(Q, 256), 256, 0, tpos, sb, Q, t_grid, ord, bpos, bid, blk_nb);
+    }
     const size_t Qn = (size_t)(Q > 0 ? Q : 1);
     uint2* code = nullptr;
     uint4* fields = nullptr;
@@ -566,7 +798,7 @@ int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_
     MRB_TRY(arena_alloc(ctx, Qn, &nbB));
     const float* xres = (const float*)xa;
     if (Q > 0) {
-        MRB_LAUNCH(ctx, k_scatter_brick_ids, cdiv(Q, 256), 256, 0, bpos, Q, bid);
+        if (!tiled) MRB_LAUNCH(ctx, k_scatter_brick_ids, cdiv(Q, 256), 256, 0, bpos, Q, bid);
         int* err = ctx->d_mail + 24;
         MRB_CUDA(cudaMemsetAsync(err, 0, sizeof(int), ctx->stream));
         for (int k = 0; k < 4; k++) MRB_CUDA(cudaMemsetAsync(xa + (size_t)k * (Q + 1) + Q, 0, sizeof(float4), ctx->stream));
@@ -576,7 +808,48 @@ int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_
         MRB_CUDA(cudaStreamSynchronize(ctx->stream));
         *closure_err_host = ctx->h_mail[24];
         if (*closure_err_host) return MRB_OK;      // caller reports MRB_EBORDER
-        if (iters > 0) {
+        if (iters > 0 && tiled) {
+            unsigned* md = (unsigned*)(ctx->d_mail + 8);
+            unsigned* bar = (unsigned*)ctx->d_bar;
+            MRB_CUDA(cudaMemsetAsync(md, 0, sizeof(unsigned), ctx->stream));
+            MRB_CUDA(cudaMemsetAsync(bar, 0, 64 * sizeof(unsigned), ctx->stream));
+            const int grid = t_grid, NW = (grid + 31) / 32;
+            unsigned *progress = nullptr, *bitmap = nullptr;
+            int *plist = nullptr, *pcount = nullptr;
+            MRB_TRY(arena_alloc(ctx, (size_t)grid * kProgressStride, &progress));
+            MRB_TRY(arena_alloc(ctx, (size_t)grid * kChunkListCap, &plist));
+            MRB_TRY(arena_alloc(ctx, (size_t)grid, &pcount));
+            MRB_TRY(arena_alloc(ctx, (size_t)grid * NW, &bitmap));
+            int* ovf = ctx->d_mail + 50;
+            MRB_CUDA(cudaMemsetAsync(progress, 0, (size_t)grid * kProgressStride * sizeof(unsigned), ctx->stream));
+            MRB_CUDA(cudaMemsetAsync(bitmap, 0, (size_t)grid * NW * sizeof(unsigned), ctx->stream));
+            MRB_CUDA(cudaMemsetAsync(pcount, 0, (size_t)grid * sizeof(int), ctx->stream));
+            MRB_CUDA(cudaMemsetAsync(ovf, 0, sizeof(int), ctx->stream));
+            MRB_LAUNCH(ctx, k_chunk_bitmap, cdiv(Q, 256), 256, 0, nbA, nbB, Q, grid, 1, NW, bitmap);
+            MRB_LAUNCH(ctx, k_chunk_lists, cdiv((size_t)grid * 32, 256), 256, 0, bitmap, grid, NW, plist, pcount, ovf);
+            int overflow = 0;
+            MRB_TRY(read_int(ctx, ovf, &overflow));
+            int dbg = getenv("MRB_QP_DEBUG") ? atoi(getenv("MRB_QP_DEBUG")) : 0;
+            if (overflow) dbg |= 4;        // a block with more than kChunkListCap neighbour blocks: grid barrier per sweep
+            int cap = (Q + grid - 1) / grid + 1;
+            size_t smem = (size_t)cap * 64;
+            if (getenv("MRB_QP_BRICK_NOSMEM") || smem > 96 * 1024 / (size_t)t_fit) { cap = 0; smem = 0; }
+            if (smem > 48 * 1024) MRB_CUDA(cudaFuncSetAttribute(t_kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            int its = iters, QQ = Q;
+            void* args[] = {(void*)&code, (void*)&fields, (void*)&nbA, (void*)&nbB, (void*)&xa, (void*)&xb, (void*)&QQ, (void*)&its,
+                            (void*)&md, (void*)&bar, (void*)&dbg, (void*)&blk_nb, (void*)&progress, (void*)&cap, (void*)&plist, (void*)&pcount};
+            MRB_CUDA(cudaEventRecord(ctx->ev[6], ctx->stream));
+            MRB_CUDA(cudaLaunchCooperativeKernel(t_kern, dim3(grid), dim3(t_threads), args, smem, ctx->stream));
+            MRB_CUDA(cudaEventRecord(ctx->ev[7], ctx->stream));
+            ctx->launches++;
+            xres = (iters % 2) ? (const float*)xb : (const float*)xa;
+            if (last_delta_host) {
+                MRB_CUDA(cudaMemcpyAsync(ctx->h_mail + 8, md, sizeof(unsigned), cudaMemcpyDeviceToHost, ctx->stream));
+                MRB_CUDA(cudaStreamSynchronize(ctx->stream));
+                unsigned bits = (unsigned)ctx->h_mail[8];
+                memcpy(last_delta_host, &bits, sizeof(float));
+            }
+        } else if (iters > 0) {
             unsigned* md = (unsigned*)(ctx->d_mail + 8);
             unsigned* bar = (unsigned*)ctx->d_bar;
             MRB_CUDA(cudaMemsetAsync(md, 0, sizeof(unsigned), ctx->stream));
