@@ -177,11 +177,10 @@ struct BrickRegs {
 
 __device__ __forceinline__ void put4(float (&d)[4], const float4 v) { d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w; }
 
-template <int DX, int DY, int J, bool Fast = false>
+template <int DX, int DY, int J>
 __device__ __forceinline__ float brick_voxel(const BrickRegs& r, uint32_t lo, uint32_t hi, uint32_t field,
                                              const float* __restrict__ s_sqrt, const float* __restrict__ s_inv) {
     constexpr int K = DX * 2 + DY, V = K * 4 + J;
-    if (Fast) { lo = 0xffffffffu; hi = 0xffffffffu; }      // timing experiment only (MRB_QP_DEBUG=32): all coefficients constant
     const bool a = lo & (1u << V);
     const bool txm = DX == 0 ? (lo & (1u << (16 + DY * 4 + J))) : (lo & (1u << ((0 * 2 + DY) * 4 + J)));
     const bool txp = DX == 0 ? (lo & (1u << ((1 * 2 + DY) * 4 + J))) : (lo & (1u << (24 + DY * 4 + J)));
@@ -229,15 +228,15 @@ __device__ __forceinline__ float brick_voxel(const BrickRegs& r, uint32_t lo, ui
     return fminf(fmaxf(t, lb), ub);
 }
 
-template <int K, bool Fast = false>
+template <int K>
 __device__ __forceinline__ float4 brick_strip(const BrickRegs& r, uint32_t lo, uint32_t hi, uint32_t w0, uint32_t w1,
                                               const float* __restrict__ s_sqrt, const float* __restrict__ s_inv) {
     constexpr int DX = K >> 1, DY = K & 1;
     float4 o;
-    o.x = brick_voxel<DX, DY, 0, Fast>(r, lo, hi, w0 & 0xffffu, s_sqrt, s_inv);
-    o.y = brick_voxel<DX, DY, 1, Fast>(r, lo, hi, w0 >> 16, s_sqrt, s_inv);
-    o.z = brick_voxel<DX, DY, 2, Fast>(r, lo, hi, w1 & 0xffffu, s_sqrt, s_inv);
-    o.w = brick_voxel<DX, DY, 3, Fast>(r, lo, hi, w1 >> 16, s_sqrt, s_inv);
+    o.x = brick_voxel<DX, DY, 0>(r, lo, hi, w0 & 0xffffu, s_sqrt, s_inv);
+    o.y = brick_voxel<DX, DY, 1>(r, lo, hi, w0 >> 16, s_sqrt, s_inv);
+    o.z = brick_voxel<DX, DY, 2>(r, lo, hi, w1 & 0xffffu, s_sqrt, s_inv);
+    o.w = brick_voxel<DX, DY, 3>(r, lo, hi, w1 >> 16, s_sqrt, s_inv);
     return o;
 }
 
@@ -256,7 +255,6 @@ __device__ __forceinline__ void brick_grid_barrier(unsigned* bar, unsigned epoch
 }
 
 // One Jacobi update of brick q: reads the iterate planes `in` (stride P), writes `out`.  Returns max |delta|.
-template <bool Fast = false>
 __device__ __forceinline__ float brick_update(int q, size_t P, const int4 na, const int2 nz, const uint2 c, const uint4 f0,
                                               const uint4 f1, const float4* in, float4* out, const float* __restrict__ s_sqrt,
                                               const float* __restrict__ s_inv, bool want_delta) {
@@ -275,10 +273,10 @@ __device__ __forceinline__ float brick_update(int q, size_t P, const int4 na, co
         r.zl[k][0] = l.x; r.zl[k][1] = l.y;
         r.zh[k][0] = h.x; r.zh[k][1] = h.y;
     }
-    const float4 o0 = brick_strip<0, Fast>(r, c.x, c.y, f0.x, f0.y, s_sqrt, s_inv);
-    const float4 o1 = brick_strip<1, Fast>(r, c.x, c.y, f0.z, f0.w, s_sqrt, s_inv);
-    const float4 o2 = brick_strip<2, Fast>(r, c.x, c.y, f1.x, f1.y, s_sqrt, s_inv);
-    const float4 o3 = brick_strip<3, Fast>(r, c.x, c.y, f1.z, f1.w, s_sqrt, s_inv);
+    const float4 o0 = brick_strip<0>(r, c.x, c.y, f0.x, f0.y, s_sqrt, s_inv);
+    const float4 o1 = brick_strip<1>(r, c.x, c.y, f0.z, f0.w, s_sqrt, s_inv);
+    const float4 o2 = brick_strip<2>(r, c.x, c.y, f1.x, f1.y, s_sqrt, s_inv);
+    const float4 o3 = brick_strip<3>(r, c.x, c.y, f1.z, f1.w, s_sqrt, s_inv);
     out[q] = o0; out[P + q] = o1; out[2 * P + q] = o2; out[3 * P + q] = o3;
     float dmax = 0.0f;
     if (want_delta) {
@@ -503,16 +501,18 @@ __global__ void __launch_bounds__(Threads, MinBlocks) k_qp_bricks(const uint2* _
     }
 }
 
-// ---- tiled brick order + boundary-first sweeps -----------------------------------------------------------------
-// In (X,Y,Z) order every brick of a block has its X+-1 neighbours in other blocks, so a block can publish
-// "sweep done" only after ALL its work and then sits through the release -> poll round trip (~1.3 us of the
-// ~7 us sweep at 256^3).  Here bricks are numbered along x-slabs of T brick columns, (slab, Y, x in slab, Z):
-// a block's contiguous id range is a compact T x L patch of columns, and only the bricks on the rim of the
-// patch are read by other blocks.  Inside each block's range the rim ("boundary") bricks are numbered first.
-// A sweep is then: wait for the neighbours' previous sweep, update the boundary bricks, publish, update the
-// interior bricks (which touch only this block's own bricks) while the flag travels.  The neighbours' flags
-// have usually arrived long before the next sweep polls them.  Results do not depend on the numbering: every
-// brick update reads the previous iterate only.
+// ---- tiled brick order, rim bricks first ------------------------------------------------------------------------
+// In (X,Y,Z) order the X+-1 neighbours of a brick sit a whole x-plane of bricks away.  Here bricks are numbered along
+// x-slabs of T brick columns, (slab, Y, x in slab, Z): a block's contiguous id range is a compact T x L patch of
+// columns and most neighbour bricks belong to the same block or to a handful of adjacent ones.  Inside each block's
+// range the rim bricks (those with a neighbour in another block) are numbered first and updated first, the interior
+// bricks (which touch only this block's own bricks) second, dealt from the last warp down.  Results do not depend
+// on the numbering: every brick update reads the previous iterate only.  Measured on B200 at 256^3, 512 threads x 1
+// block per SM: 3.49 ms (X,Y,Z order, 256 x 2) -> 3.33 ms.
+// Tried on top of this and measured slower (profiles/r01_summary.md): publishing the sweep as soon as the rim bricks
+// are stored, so that the flag travels while the interior is updated -- with a barrier between the two phases
+// 3.85 ms, with per-warp fences and an arrive counter instead of the barrier 3.57-3.75 ms, polling during the
+// interior phase 4.4-5.5 ms.
 struct TiledOrder {
     BrickDims bd;
     int T;
@@ -620,14 +620,6 @@ __global__ void __launch_bounds__(Threads, MinBlocks) k_qp_bricks_tiled(const ui
     // interior work is dealt from the last warp down, so warp 0 (which pays for the release) gets the remainder
     constexpr int W = Threads / 32;
     const int rtid = (W - 1 - (int)(threadIdx.x >> 5)) * 32 + (int)(threadIdx.x & 31);
-    // warps that own boundary bricks (they arrive on s_done once per sweep)
-    __shared__ unsigned s_done;
-    if (threadIdx.x == 0) s_done = 0;
-    const unsigned s_done_addr = (unsigned)__cvta_generic_to_shared(&s_done);
-    const int nbnd = q_int - q_begin;
-    const int n_bwarps = nbnd >= Threads ? W : (nbnd + 31) / 32;
-    const bool has_boundary = (int)(threadIdx.x >> 5) < n_bwarps;
-    __syncthreads();
     const float4* in = xa;
     float4* out = xb;
     auto update = [&](int q, bool last) {
@@ -639,7 +631,6 @@ __global__ void __launch_bounds__(Threads, MinBlocks) k_qp_bricks_tiled(const ui
             na = __ldg(nbA + q); nz = __ldg(nbB + q); c = __ldg(code + q);
             f0 = __ldg(fields + q); f1 = __ldg(fields + (size_t)Q + q);
         }
-        if (dbg & 32) return brick_update<true>(q, P, na, nz, c, f0, f1, in, out, s_sqrt, s_inv, last);
         return brick_update(q, P, na, nz, c, f0, f1, in, out, s_sqrt, s_inv, last);
     };
     for (int it = 0; it < iters; it++) {
@@ -650,48 +641,20 @@ __global__ void __launch_bounds__(Threads, MinBlocks) k_qp_bricks_tiled(const ui
             __syncthreads();        // neighbour flags are in (polled below); this block's interior bricks of sweep it-1 are stored
         }
         for (int q = q_begin + threadIdx.x; q < q_int; q += Threads) dmax = fmaxf(dmax, update(q, last));
-        const bool flags_on = !last && !(dbg & 5);
-        if (flags_on && !(dbg & 8)) {
-            // No block-wide barrier here: every warp that updated boundary bricks fences its stores and counts itself in;
-            // warp 0 publishes the sweep once all of them have arrived.  The other warps go straight on to the interior.
-            if (has_boundary) {
-                __threadfence();
-                __syncwarp();
-                if ((threadIdx.x & 31) == 0) asm volatile("red.release.cta.shared.add.u32 [%0], 1;" ::"r"(s_done_addr) : "memory");
-            }
-            if (threadIdx.x == 0) {
-                const unsigned want = (unsigned)n_bwarps * (unsigned)(it + 1);
-                unsigned v;
-                do {
-                    asm volatile("ld.acquire.cta.shared.u32 %0, [%1];" : "=r"(v) : "r"(s_done_addr) : "memory");
-                } while (v < want);
-                if (dbg & 64) asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(mine), "r"((unsigned)(it + 1)) : "memory");
-                else asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(mine), "r"((unsigned)(it + 1)) : "memory");
-            }
-            __syncwarp();
-        }
         for (int q = q_int + rtid; q < q_end; q += Threads) dmax = fmaxf(dmax, update(q, last));
-        if (flags_on) {
-            if (dbg & 8) {          // tuning aid: publish after the whole sweep
-                __syncthreads();
-                if (threadIdx.x == 0) asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(mine), "r"((unsigned)(it + 1)) : "memory");
-            }
-            // warp 0 (last in line for interior work) collects the neighbours' flags of this sweep
-            if (watch) {
-                unsigned v, spins = 0;
-                for (;;) {
-                    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(watch) : "memory");
-                    if (v >= (unsigned)(it + 1)) break;
-                    if (dbg & 16) __nanosleep(100);
-                    if (++spins == (1u << 26)) __trap();       // a lost producer must not hang the GPU
-                }
-                if (watch2) for (;;) {
-                    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(watch2) : "memory");
-                    if (v >= (unsigned)(it + 1)) break;
-                    if (dbg & 16) __nanosleep(100);
-                    if (++spins == (1u << 26)) __trap();
-                }
-            }
+        if (!last && !(dbg & 5)) {
+            __syncthreads();        // the block's stores of this sweep are issued
+            if (threadIdx.x == 0) asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(mine), "r"((unsigned)(it + 1)) : "memory");
+            // warp 0 collects the neighbours' flags of this sweep; the barrier at the top of the next sweep hands them on
+            unsigned v, spins = 0;
+            if (watch) do {
+                asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(watch) : "memory");
+                if (++spins == (1u << 26)) __trap();       // a lost producer must not hang the GPU
+            } while (v < (unsigned)(it + 1));
+            if (watch2) do {
+                asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(watch2) : "memory");
+                if (++spins == (1u << 26)) __trap();
+            } while (v < (unsigned)(it + 1));
         }
         if (last) {
 #pragma unroll
@@ -746,14 +709,14 @@ int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_
     const size_t nb = bd.count();
     int* bpos = nullptr;
     int Q = 0;
-    // brick numbering: x-slab tiles with boundary-first blocks (default) or plain (X,Y,Z) (MRB_QP_ORDER=xyz)
+    // brick numbering: x-slab tiles, rim bricks first (default), or plain (X,Y,Z) (MRB_QP_ORDER=xyz)
     const char* eo = getenv("MRB_QP_ORDER");
     const bool tiled = !(eo && strcmp(eo, "xyz") == 0) && iters > 0;
-    int tile_T = 6;
+    int tile_T = 8;
     if (getenv("MRB_QP_TILE")) tile_T = atoi(getenv("MRB_QP_TILE"));
     if (tile_T < 1) tile_T = 1;
-    int t_threads = 256;
-    if (getenv("MRB_QP_BRICK_THREADS") && atoi(getenv("MRB_QP_BRICK_THREADS")) == 512) t_threads = 512;
+    int t_threads = 512;       // one block of 16 warps per SM: the patches are larger, so fewer of their bricks are rim bricks
+    if (getenv("MRB_QP_BRICK_THREADS") && atoi(getenv("MRB_QP_BRICK_THREADS")) == 256) t_threads = 256;
     void* t_kern = t_threads == 512 ? (void*)k_qp_bricks_tiled<512, 1> : (void*)k_qp_bricks_tiled<256, 2>;
     int t_grid = 0, t_fit = 0;
     int* blk_nb = nullptr;
