@@ -302,7 +302,7 @@ def main():
                     "meshes_per_s": world / (e2e_ms_per_step / 1000.0),
                     "h2d_bytes_per_step": int(volume.nbytes), "d2h_bytes_per_step": int(d2h)},
             "gpu_launches": int(launches),
-            "roofline": {"kernel": "k_qp_strips (all %d sweeps in one persistent cooperative launch)" % args.iters,
+            "roofline": {"kernel": "k_qp_bricks_tiled (all %d sweeps in one persistent cooperative launch)" % args.iters,
                          "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": alg_bytes, "kernel_ms": qp_kernel_ms},
