@@ -289,6 +289,146 @@ __device__ __forceinline__ float brick_update(int q, size_t P, const int4 na, co
     return dmax;
 }
 
+// ---- expanded per-brick constants (shared-memory resident) --------------------------------------------------
+// When a block's bricks fit, the sweep kernel decodes their constants ONCE into shared memory: lb, ub and invdg as
+// floats and one byte of seven tight bits per voxel (self, x-, y-, z-, z+, y+, x+ : the order of use).  The sweep then
+// spends no instructions on field decoding, table look-ups or bit gathering (about 700 -> 470 instructions per brick
+// update); the global layout (64 B per brick) is unchanged.
+struct BrickConstsX {
+    float4 lb[4], ub[4], inv[4];     // [k = dx*2+dy], components j = 0..3
+    uint4 pred;                      // word k, byte j
+};
+
+__device__ __forceinline__ uint32_t brick_pred_byte(int DX, int DY, int J, uint32_t lo, uint32_t hi) {
+    const int K = DX * 2 + DY, V = K * 4 + J;
+    auto L = [&](int b) { return (lo >> b) & 1u; };
+    auto H = [&](int b) { return (hi >> b) & 1u; };
+    const uint32_t a = L(V);
+    const uint32_t txm = DX == 0 ? L(16 + DY * 4 + J) : L((0 * 2 + DY) * 4 + J);
+    const uint32_t txp = DX == 0 ? L((1 * 2 + DY) * 4 + J) : L(24 + DY * 4 + J);
+    const uint32_t tym = DY == 0 ? H(DX * 4 + J) : L((DX * 2 + 0) * 4 + J);
+    const uint32_t typ = DY == 0 ? L((DX * 2 + 1) * 4 + J) : H(8 + DX * 4 + J);
+    const uint32_t tzm = J > 0 ? L(V - 1) : H(16 + K);
+    const uint32_t tzp = J < 3 ? L(V + 1) : H(20 + K);
+    return a | (txm << 1) | (tym << 2) | (tzm << 3) | (tzp << 4) | (typ << 5) | (txp << 6);
+}
+
+__device__ __forceinline__ BrickConstsX brick_expand(const uint2 c, const uint4 f0, const uint4 f1, const float* __restrict__ s_sqrt,
+                                                     const float* __restrict__ s_inv) {
+    BrickConstsX x;
+    const uint32_t w[8] = {f0.x, f0.y, f0.z, f0.w, f1.x, f1.y, f1.z, f1.w};
+    uint32_t pw[4];
+    float lb[16], ub[16], iv[16];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        pw[k] = 0;
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const int v = k * 4 + j;
+            const uint32_t field = (w[v >> 1] >> ((v & 1) * 16)) & 0xffffu;
+            const float m = s_sqrt[field & 0xffu];
+            iv[v] = s_inv[(field >> 8) & 31u];
+            lb[v] = (field & (1u << 13)) ? -1000.0f : m;
+            ub[v] = (field & (1u << 14)) ? 1000.0f : -m;
+            pw[k] |= brick_pred_byte(k >> 1, k & 1, j, c.x, c.y) << (8 * j);
+        }
+        x.lb[k] = make_float4(lb[k * 4], lb[k * 4 + 1], lb[k * 4 + 2], lb[k * 4 + 3]);
+        x.ub[k] = make_float4(ub[k * 4], ub[k * 4 + 1], ub[k * 4 + 2], ub[k * 4 + 3]);
+        x.inv[k] = make_float4(iv[k * 4], iv[k * 4 + 1], iv[k * 4 + 2], iv[k * 4 + 3]);
+    }
+    x.pred = make_uint4(pw[0], pw[1], pw[2], pw[3]);
+    return x;
+}
+
+template <int DX, int DY, int J>
+__device__ __forceinline__ float brick_voxel_x(const BrickRegs& r, uint32_t pw, float lb, float ub, float inv) {
+    constexpr int K = DX * 2 + DY;
+    const uint32_t pb = pw >> (8 * J);
+    const bool a = pb & 1u, txm = pb & 2u, tym = pb & 4u, tzm = pb & 8u, tzp = pb & 16u, typ = pb & 32u, txp = pb & 64u;
+    const float xm2 = DX == 0 ? r.xm[0 * 2 + DY][J] : r.xm[1 * 2 + DY][J];
+    const float xm1 = DX == 0 ? r.xm[1 * 2 + DY][J] : r.own[0 * 2 + DY][J];
+    const float xp1 = DX == 0 ? r.own[1 * 2 + DY][J] : r.xp[0 * 2 + DY][J];
+    const float xp2 = DX == 0 ? r.xp[0 * 2 + DY][J] : r.xp[1 * 2 + DY][J];
+    const float ym2 = DY == 0 ? r.ym[DX * 2 + 0][J] : r.ym[DX * 2 + 1][J];
+    const float ym1 = DY == 0 ? r.ym[DX * 2 + 1][J] : r.own[DX * 2 + 0][J];
+    const float yp1 = DY == 0 ? r.own[DX * 2 + 1][J] : r.yp[DX * 2 + 0][J];
+    const float yp2 = DY == 0 ? r.yp[DX * 2 + 0][J] : r.yp[DX * 2 + 1][J];
+    const float zm2 = J >= 2 ? r.own[K][J >= 2 ? J - 2 : 0] : r.zl[K][J < 2 ? J : 0];
+    const float zm1 = J >= 1 ? r.own[K][J >= 1 ? J - 1 : 0] : r.zl[K][1];
+    const float zp1 = J <= 2 ? r.own[K][J <= 2 ? J + 1 : 0] : r.zh[K][0];
+    const float zp2 = J <= 1 ? r.own[K][J <= 1 ? J + 2 : 0] : r.zh[K][J >= 2 ? J - 2 : 0];
+    const float xc = r.own[K][J];
+    const float cA = a ? -4.0f : -2.0f;       // same arithmetic, same order as brick_voxel
+    const float cB = a ? -2.0f : 0.0f;
+    float res = txm ? xm2 : 0.0f;
+    res = __fmaf_rn(txm ? cA : cB, xm1, res);
+    if (tym) res = __fadd_rn(res, ym2);
+    res = __fmaf_rn(tym ? cA : cB, ym1, res);
+    if (tzm) res = __fadd_rn(res, zm2);
+    res = __fmaf_rn(tzm ? cA : cB, zm1, res);
+    res = __fmaf_rn(tzp ? cA : cB, zp1, res);
+    if (tzp) res = __fadd_rn(res, zp2);
+    res = __fmaf_rn(typ ? cA : cB, yp1, res);
+    if (typ) res = __fadd_rn(res, yp2);
+    res = __fmaf_rn(txp ? cA : cB, xp1, res);
+    if (txp) res = __fadd_rn(res, xp2);
+    float t = __fsub_rn(xc, __fmul_rn(res, inv));
+    t = t * 0.5f;
+    return fminf(fmaxf(t, lb), ub);
+}
+
+template <int K>
+__device__ __forceinline__ float4 brick_strip_x(const BrickRegs& r, uint32_t pw, const float4 lb, const float4 ub, const float4 inv) {
+    constexpr int DX = K >> 1, DY = K & 1;
+    float4 o;
+    o.x = brick_voxel_x<DX, DY, 0>(r, pw, lb.x, ub.x, inv.x);
+    o.y = brick_voxel_x<DX, DY, 1>(r, pw, lb.y, ub.y, inv.y);
+    o.z = brick_voxel_x<DX, DY, 2>(r, pw, lb.z, ub.z, inv.z);
+    o.w = brick_voxel_x<DX, DY, 3>(r, pw, lb.w, ub.w, inv.w);
+    return o;
+}
+
+__device__ __forceinline__ void brick_load(BrickRegs& r, int q, size_t P, const int4 na, const int2 nz, const float4* in) {
+    // the iterate is rewritten by other SMs every sweep: plain loads, ordered by the sweep synchronisation
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const float4* pl = in + k * P;
+        put4(r.own[k], pl[q]);
+        put4(r.xm[k], pl[na.x]);
+        put4(r.xp[k], pl[na.y]);
+        put4(r.ym[k], pl[na.z]);
+        put4(r.yp[k], pl[na.w]);
+        const float2 l = *reinterpret_cast<const float2*>(reinterpret_cast<const float*>(pl + nz.x) + 2);
+        const float2 h = *reinterpret_cast<const float2*>(pl + nz.y);
+        r.zl[k][0] = l.x; r.zl[k][1] = l.y;
+        r.zh[k][0] = h.x; r.zh[k][1] = h.y;
+    }
+}
+
+// Same as brick_update with the constants of brick q read from the expanded shared-memory arrays (slot l, stride cap).
+__device__ __forceinline__ float brick_update_x(int q, size_t P, int l, int cap, const float4* __restrict__ s_lb,
+                                                const float4* __restrict__ s_ub, const float4* __restrict__ s_iv,
+                                                const uint4* __restrict__ s_pred, const int4 na, const int2 nz, const float4* in,
+                                                float4* out, bool want_delta) {
+    BrickRegs r;
+    brick_load(r, q, P, na, nz, in);
+    const uint4 pw = s_pred[l];
+    const float4 o0 = brick_strip_x<0>(r, pw.x, s_lb[l], s_ub[l], s_iv[l]);
+    const float4 o1 = brick_strip_x<1>(r, pw.y, s_lb[cap + l], s_ub[cap + l], s_iv[cap + l]);
+    const float4 o2 = brick_strip_x<2>(r, pw.z, s_lb[2 * cap + l], s_ub[2 * cap + l], s_iv[2 * cap + l]);
+    const float4 o3 = brick_strip_x<3>(r, pw.w, s_lb[3 * cap + l], s_ub[3 * cap + l], s_iv[3 * cap + l]);
+    out[q] = o0; out[P + q] = o1; out[2 * P + q] = o2; out[3 * P + q] = o3;
+    float dmax = 0.0f;
+    if (want_delta) {
+        const float4 os[4] = {o0, o1, o2, o3};
+#pragma unroll
+        for (int k = 0; k < 4; k++)
+            dmax = fmaxf(fmaxf(dmax, fmaxf(fabsf(os[k].x - r.own[k][0]), fabsf(os[k].y - r.own[k][1]))),
+                         fmaxf(fabsf(os[k].z - r.own[k][2]), fabsf(os[k].w - r.own[k][3])));
+    }
+    return dmax;
+}
+
 // ---- neighbour-only synchronisation --------------------------------------------------------------------------
 // Block b owns bricks [Q*b/G, Q*(b+1)/G).  Its sweep k+1 reads bricks owned by a few other blocks only
 // (bricks are ordered (X,Y,Z): the X+-1 neighbours sit about one x-plane of bricks away), so instead of
@@ -586,7 +726,8 @@ __global__ void __launch_bounds__(Threads, MinBlocks) k_qp_bricks_tiled(const ui
                                                                         float4* xa, float4* xb, int Q, int iters,
                                                                         unsigned* __restrict__ maxdelta_bits, unsigned* bar, int dbg,
                                                                         const int* __restrict__ blk_nb, unsigned* progress, int cap,
-                                                                        const int* __restrict__ plist, const int* __restrict__ pcount) {
+                                                                        const int* __restrict__ plist, const int* __restrict__ pcount,
+                                                                        int expanded) {
     __shared__ float s_sqrt[256];
     __shared__ float s_inv[32];
     for (int i = threadIdx.x; i < 256; i += Threads) s_sqrt[i] = c_brick_sqrt[i];
@@ -595,18 +736,33 @@ __global__ void __launch_bounds__(Threads, MinBlocks) k_qp_bricks_tiled(const ui
     const int q_begin = (int)((long long)Q * blockIdx.x / gridDim.x);
     const int q_end = (int)((long long)Q * (blockIdx.x + 1) / gridDim.x);
     const int q_int = q_begin + blk_nb[blockIdx.x];          // first interior brick
+    __syncthreads();
+    // Per-brick constants in shared memory, copied once: expanded (232 B per brick, see BrickConstsX) when they fit,
+    // else in the global 64-byte form, else not at all (cap == 0: read through L1/L2 every sweep).
     extern __shared__ uint4 s_dyn[];
     uint4* s_f0 = s_dyn;
     uint4* s_f1 = s_dyn + cap;
     int4* s_na = (int4*)(s_dyn + 2 * cap);
     int2* s_nz = (int2*)(s_dyn + 3 * cap);
     uint2* s_code = (uint2*)(s_nz + cap);
+    float4* s_lb = (float4*)s_dyn;
+    float4* s_ub = s_lb + 4 * cap;
+    float4* s_iv = s_ub + 4 * cap;
+    uint4* s_pred = (uint4*)(s_iv + 4 * cap);
+    if (expanded) { s_na = (int4*)(s_pred + cap); s_nz = (int2*)(s_na + cap); }
     const bool smem_consts = cap > 0;
     if (smem_consts)
         for (int q = q_begin + threadIdx.x; q < q_end; q += Threads) {
             const int l = q - q_begin;
-            s_na[l] = __ldg(nbA + q); s_nz[l] = __ldg(nbB + q); s_code[l] = __ldg(code + q);
-            s_f0[l] = __ldg(fields + q); s_f1[l] = __ldg(fields + (size_t)Q + q);
+            s_na[l] = __ldg(nbA + q); s_nz[l] = __ldg(nbB + q);
+            if (expanded) {
+                const BrickConstsX x = brick_expand(__ldg(code + q), __ldg(fields + q), __ldg(fields + (size_t)Q + q), s_sqrt, s_inv);
+#pragma unroll
+                for (int k = 0; k < 4; k++) { s_lb[k * cap + l] = x.lb[k]; s_ub[k * cap + l] = x.ub[k]; s_iv[k * cap + l] = x.inv[k]; }
+                s_pred[l] = x.pred;
+            } else {
+                s_code[l] = __ldg(code + q); s_f0[l] = __ldg(fields + q); s_f1[l] = __ldg(fields + (size_t)Q + q);
+            }
         }
     __syncthreads();
     // the blocks whose sweep this block has to wait for (at most kChunkListCap, checked by the host)
@@ -623,6 +779,10 @@ __global__ void __launch_bounds__(Threads, MinBlocks) k_qp_bricks_tiled(const ui
     const float4* in = xa;
     float4* out = xb;
     auto update = [&](int q, bool last) {
+        if (expanded) {
+            const int l = q - q_begin;
+            return brick_update_x(q, P, l, cap, s_lb, s_ub, s_iv, s_pred, s_na[l], s_nz[l], in, out, last);
+        }
         int4 na; int2 nz; uint2 c; uint4 f0, f1;
         if (smem_consts) {
             const int l = q - q_begin;
@@ -795,12 +955,17 @@ int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_
             int dbg = getenv("MRB_QP_DEBUG") ? atoi(getenv("MRB_QP_DEBUG")) : 0;
             if (overflow) dbg |= 4;        // a block with more than kChunkListCap neighbour blocks: grid barrier per sweep
             int cap = (Q + grid - 1) / grid + 1;
-            size_t smem = (size_t)cap * 64;
-            if (getenv("MRB_QP_BRICK_NOSMEM") || smem > 96 * 1024 / (size_t)t_fit) { cap = 0; smem = 0; }
+            // expanded constants (232 B per brick) if one block's share fits next to the static tables, else the 64-byte form
+            int expanded = 1;
+            size_t smem = (size_t)cap * 232;
+            const size_t smem_max = (size_t)220 * 1024 / (size_t)t_fit;
+            if (getenv("MRB_QP_BRICK_COMPACT") || smem > smem_max) { expanded = 0; smem = (size_t)cap * 64; }
+            if (getenv("MRB_QP_BRICK_NOSMEM") || smem > 96 * 1024 / (size_t)t_fit) { if (!expanded) { cap = 0; smem = 0; } }
             if (smem > 48 * 1024) MRB_CUDA(cudaFuncSetAttribute(t_kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
             int its = iters, QQ = Q;
             void* args[] = {(void*)&code, (void*)&fields, (void*)&nbA, (void*)&nbB, (void*)&xa, (void*)&xb, (void*)&QQ, (void*)&its,
-                            (void*)&md, (void*)&bar, (void*)&dbg, (void*)&blk_nb, (void*)&progress, (void*)&cap, (void*)&plist, (void*)&pcount};
+                            (void*)&md, (void*)&bar, (void*)&dbg, (void*)&blk_nb, (void*)&progress, (void*)&cap, (void*)&plist, (void*)&pcount,
+                            (void*)&expanded};
             MRB_CUDA(cudaEventRecord(ctx->ev[6], ctx->stream));
             MRB_CUDA(cudaLaunchCooperativeKernel(t_kern, dim3(grid), dim3(t_threads), args, smem, ctx->stream));
             MRB_CUDA(cudaEventRecord(ctx->ev[7], ctx->stream));
