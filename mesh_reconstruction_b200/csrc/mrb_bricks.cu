@@ -290,12 +290,17 @@ __device__ __forceinline__ float brick_update(int q, size_t P, const int4 na, co
 }
 
 // ---- expanded per-brick constants (shared-memory resident) --------------------------------------------------
-// When a block's bricks fit, the sweep kernel decodes their constants ONCE into shared memory: lb, ub and invdg as
-// floats and one byte of seven tight bits per voxel (self, x-, y-, z-, z+, y+, x+ : the order of use).  The sweep then
-// spends no instructions on field decoding, table look-ups or bit gathering (about 700 -> 470 instructions per brick
-// update); the global layout (64 B per brick) is unchanged.
+// When a block's bricks fit (and the volume is binary), the sweep kernel decodes their constants ONCE into shared
+// memory: the signed margin and invdg as floats and one byte of seven tight bits per voxel (self, x-, y-, z-, z+, y+,
+// x+ : the order of use).  The sweep then spends no instructions on field decoding, table look-ups or bit gathering
+// (about 700 -> 500 instructions per brick update); the global layout (64 B per brick) is unchanged.
+// Signed margin s: +margin where volume == 1 (lb = margin, ub = 1000), -margin where volume == 0 (lb = -1000,
+// ub = -margin; -0.0f on the perimeter itself), so one float carries both bounds (getlb/getub, primeqp.cpp:115-165):
+//   volume == 1:  min(max(t,  s), 1000)          volume == 0:  min(max(t, -1000), s) == max(min(t, s), -1000)
+// Voxels of a brick outside the band get s = +0 (invdg = 0 keeps them at exactly 0).  A voxel whose volume is neither
+// 0 nor 1 has lb = margin > ub = -margin, which this encoding cannot express: such grids use the 64-byte form.
 struct BrickConstsX {
-    float4 lb[4], ub[4], inv[4];     // [k = dx*2+dy], components j = 0..3
+    float4 sm[4], inv[4];            // [k = dx*2+dy], components j = 0..3
     uint4 pred;                      // word k, byte j
 };
 
@@ -318,7 +323,7 @@ __device__ __forceinline__ BrickConstsX brick_expand(const uint2 c, const uint4 
     BrickConstsX x;
     const uint32_t w[8] = {f0.x, f0.y, f0.z, f0.w, f1.x, f1.y, f1.z, f1.w};
     uint32_t pw[4];
-    float lb[16], ub[16], iv[16];
+    float sm[16], iv[16];
 #pragma unroll
     for (int k = 0; k < 4; k++) {
         pw[k] = 0;
@@ -328,12 +333,11 @@ __device__ __forceinline__ BrickConstsX brick_expand(const uint2 c, const uint4 
             const uint32_t field = (w[v >> 1] >> ((v & 1) * 16)) & 0xffffu;
             const float m = s_sqrt[field & 0xffu];
             iv[v] = s_inv[(field >> 8) & 31u];
-            lb[v] = (field & (1u << 13)) ? -1000.0f : m;
-            ub[v] = (field & (1u << 14)) ? 1000.0f : -m;
+            // band voxel of a binary volume: exactly one of bit 13 (volume == 0) / bit 14 (volume == 1)
+            sm[v] = (field & (1u << 15)) ? ((field & (1u << 13)) ? -m : m) : 0.0f;
             pw[k] |= brick_pred_byte(k >> 1, k & 1, j, c.x, c.y) << (8 * j);
         }
-        x.lb[k] = make_float4(lb[k * 4], lb[k * 4 + 1], lb[k * 4 + 2], lb[k * 4 + 3]);
-        x.ub[k] = make_float4(ub[k * 4], ub[k * 4 + 1], ub[k * 4 + 2], ub[k * 4 + 3]);
+        x.sm[k] = make_float4(sm[k * 4], sm[k * 4 + 1], sm[k * 4 + 2], sm[k * 4 + 3]);
         x.inv[k] = make_float4(iv[k * 4], iv[k * 4 + 1], iv[k * 4 + 2], iv[k * 4 + 3]);
     }
     x.pred = make_uint4(pw[0], pw[1], pw[2], pw[3]);
@@ -341,7 +345,7 @@ __device__ __forceinline__ BrickConstsX brick_expand(const uint2 c, const uint4 
 }
 
 template <int DX, int DY, int J>
-__device__ __forceinline__ float brick_voxel_x(const BrickRegs& r, uint32_t pw, float lb, float ub, float inv) {
+__device__ __forceinline__ float brick_voxel_x(const BrickRegs& r, uint32_t pw, float sm, float inv) {
     constexpr int K = DX * 2 + DY;
     const uint32_t pb = pw >> (8 * J);
     const bool a = pb & 1u, txm = pb & 2u, tym = pb & 4u, tzm = pb & 8u, tzp = pb & 16u, typ = pb & 32u, txp = pb & 64u;
@@ -374,17 +378,22 @@ __device__ __forceinline__ float brick_voxel_x(const BrickRegs& r, uint32_t pw, 
     if (txp) res = __fadd_rn(res, xp2);
     float t = __fsub_rn(xc, __fmul_rn(res, inv));
     t = t * 0.5f;
-    return fminf(fmaxf(t, lb), ub);
+    // clamp to [lb, ub] from the signed margin (see BrickConstsX); differs from "if (t < lb) t = lb; if (t > ub) t = ub"
+    // at most in the sign of a zero, as in brick_voxel
+    const bool outside = __float_as_int(sm) < 0;
+    const float far = __int_as_float((__float_as_int(sm) & 0x80000000) ^ 0x447a0000);      // volume==0 ? -1000 : 1000
+    const float u = outside ? fminf(t, sm) : fmaxf(t, sm);
+    return outside ? fmaxf(u, far) : fminf(u, far);
 }
 
 template <int K>
-__device__ __forceinline__ float4 brick_strip_x(const BrickRegs& r, uint32_t pw, const float4 lb, const float4 ub, const float4 inv) {
+__device__ __forceinline__ float4 brick_strip_x(const BrickRegs& r, uint32_t pw, const float4 sm, const float4 inv) {
     constexpr int DX = K >> 1, DY = K & 1;
     float4 o;
-    o.x = brick_voxel_x<DX, DY, 0>(r, pw, lb.x, ub.x, inv.x);
-    o.y = brick_voxel_x<DX, DY, 1>(r, pw, lb.y, ub.y, inv.y);
-    o.z = brick_voxel_x<DX, DY, 2>(r, pw, lb.z, ub.z, inv.z);
-    o.w = brick_voxel_x<DX, DY, 3>(r, pw, lb.w, ub.w, inv.w);
+    o.x = brick_voxel_x<DX, DY, 0>(r, pw, sm.x, inv.x);
+    o.y = brick_voxel_x<DX, DY, 1>(r, pw, sm.y, inv.y);
+    o.z = brick_voxel_x<DX, DY, 2>(r, pw, sm.z, inv.z);
+    o.w = brick_voxel_x<DX, DY, 3>(r, pw, sm.w, inv.w);
     return o;
 }
 
@@ -406,17 +415,16 @@ __device__ __forceinline__ void brick_load(BrickRegs& r, int q, size_t P, const 
 }
 
 // Same as brick_update with the constants of brick q read from the expanded shared-memory arrays (slot l, stride cap).
-__device__ __forceinline__ float brick_update_x(int q, size_t P, int l, int cap, const float4* __restrict__ s_lb,
-                                                const float4* __restrict__ s_ub, const float4* __restrict__ s_iv,
-                                                const uint4* __restrict__ s_pred, const int4 na, const int2 nz, const float4* in,
-                                                float4* out, bool want_delta) {
+__device__ __forceinline__ float brick_update_x(int q, size_t P, int l, int cap, const float4* __restrict__ s_sm,
+                                                const float4* __restrict__ s_iv, const uint4* __restrict__ s_pred, const int4 na,
+                                                const int2 nz, const float4* in, float4* out, bool want_delta) {
     BrickRegs r;
     brick_load(r, q, P, na, nz, in);
     const uint4 pw = s_pred[l];
-    const float4 o0 = brick_strip_x<0>(r, pw.x, s_lb[l], s_ub[l], s_iv[l]);
-    const float4 o1 = brick_strip_x<1>(r, pw.y, s_lb[cap + l], s_ub[cap + l], s_iv[cap + l]);
-    const float4 o2 = brick_strip_x<2>(r, pw.z, s_lb[2 * cap + l], s_ub[2 * cap + l], s_iv[2 * cap + l]);
-    const float4 o3 = brick_strip_x<3>(r, pw.w, s_lb[3 * cap + l], s_ub[3 * cap + l], s_iv[3 * cap + l]);
+    const float4 o0 = brick_strip_x<0>(r, pw.x, s_sm[l], s_iv[l]);
+    const float4 o1 = brick_strip_x<1>(r, pw.y, s_sm[cap + l], s_iv[cap + l]);
+    const float4 o2 = brick_strip_x<2>(r, pw.z, s_sm[2 * cap + l], s_iv[2 * cap + l]);
+    const float4 o3 = brick_strip_x<3>(r, pw.w, s_sm[3 * cap + l], s_iv[3 * cap + l]);
     out[q] = o0; out[P + q] = o1; out[2 * P + q] = o2; out[3 * P + q] = o3;
     float dmax = 0.0f;
     if (want_delta) {
@@ -737,7 +745,7 @@ __global__ void __launch_bounds__(Threads, MinBlocks) k_qp_bricks_tiled(const ui
     const int q_end = (int)((long long)Q * (blockIdx.x + 1) / gridDim.x);
     const int q_int = q_begin + blk_nb[blockIdx.x];          // first interior brick
     __syncthreads();
-    // Per-brick constants in shared memory, copied once: expanded (232 B per brick, see BrickConstsX) when they fit,
+    // Per-brick constants in shared memory, copied once: expanded (168 B per brick, see BrickConstsX) when they fit,
     // else in the global 64-byte form, else not at all (cap == 0: read through L1/L2 every sweep).
     extern __shared__ uint4 s_dyn[];
     uint4* s_f0 = s_dyn;
@@ -745,9 +753,8 @@ __global__ void __launch_bounds__(Threads, MinBlocks) k_qp_bricks_tiled(const ui
     int4* s_na = (int4*)(s_dyn + 2 * cap);
     int2* s_nz = (int2*)(s_dyn + 3 * cap);
     uint2* s_code = (uint2*)(s_nz + cap);
-    float4* s_lb = (float4*)s_dyn;
-    float4* s_ub = s_lb + 4 * cap;
-    float4* s_iv = s_ub + 4 * cap;
+    float4* s_sm = (float4*)s_dyn;
+    float4* s_iv = s_sm + 4 * cap;
     uint4* s_pred = (uint4*)(s_iv + 4 * cap);
     if (expanded) { s_na = (int4*)(s_pred + cap); s_nz = (int2*)(s_na + cap); }
     const bool smem_consts = cap > 0;
@@ -758,7 +765,7 @@ __global__ void __launch_bounds__(Threads, MinBlocks) k_qp_bricks_tiled(const ui
             if (expanded) {
                 const BrickConstsX x = brick_expand(__ldg(code + q), __ldg(fields + q), __ldg(fields + (size_t)Q + q), s_sqrt, s_inv);
 #pragma unroll
-                for (int k = 0; k < 4; k++) { s_lb[k * cap + l] = x.lb[k]; s_ub[k * cap + l] = x.ub[k]; s_iv[k * cap + l] = x.inv[k]; }
+                for (int k = 0; k < 4; k++) { s_sm[k * cap + l] = x.sm[k]; s_iv[k * cap + l] = x.inv[k]; }
                 s_pred[l] = x.pred;
             } else {
                 s_code[l] = __ldg(code + q); s_f0[l] = __ldg(fields + q); s_f1[l] = __ldg(fields + (size_t)Q + q);
@@ -781,7 +788,7 @@ __global__ void __launch_bounds__(Threads, MinBlocks) k_qp_bricks_tiled(const ui
     auto update = [&](int q, bool last) {
         if (expanded) {
             const int l = q - q_begin;
-            return brick_update_x(q, P, l, cap, s_lb, s_ub, s_iv, s_pred, s_na[l], s_nz[l], in, out, last);
+            return brick_update_x(q, P, l, cap, s_sm, s_iv, s_pred, s_na[l], s_nz[l], in, out, last);
         }
         int4 na; int2 nz; uint2 c; uint4 f0, f1;
         if (smem_consts) {
@@ -863,7 +870,7 @@ __global__ void __launch_bounds__(256) k_assemble_F_b(const float* __restrict__ 
 // *n_bricks / *closure_err_host are outputs; ev[6], ev[7] bracket the sweep kernel.
 int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_t* flags, const uint8_t* sq, Dims d,
                  int band_size, int iters, int using_features, float* F_dev, float* last_delta_host, int* n_bricks,
-                 int* closure_err_host) {
+                 int* closure_err_host, int binary_volume) {
     MRB_TRY(upload_tables(ctx->device));
     BrickDims bd{d.nx, d.ny, d.nz, (d.nx + 1) / 2, (d.ny + 1) / 2, (d.nz + 3) / 4};
     const size_t nb = bd.count();
@@ -955,11 +962,11 @@ int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_
             int dbg = getenv("MRB_QP_DEBUG") ? atoi(getenv("MRB_QP_DEBUG")) : 0;
             if (overflow) dbg |= 4;        // a block with more than kChunkListCap neighbour blocks: grid barrier per sweep
             int cap = (Q + grid - 1) / grid + 1;
-            // expanded constants (232 B per brick) if one block's share fits next to the static tables, else the 64-byte form
-            int expanded = 1;
-            size_t smem = (size_t)cap * 232;
+            // expanded constants (168 B per brick) for binary volumes if one block's share fits, else the 64-byte form
+            int expanded = binary_volume ? 1 : 0;
+            size_t smem = (size_t)cap * 168;
             const size_t smem_max = (size_t)220 * 1024 / (size_t)t_fit;
-            if (getenv("MRB_QP_BRICK_COMPACT") || smem > smem_max) { expanded = 0; smem = (size_t)cap * 64; }
+            if (getenv("MRB_QP_BRICK_COMPACT") || !expanded || smem > smem_max) { expanded = 0; smem = (size_t)cap * 64; }
             if (getenv("MRB_QP_BRICK_NOSMEM") || smem > 96 * 1024 / (size_t)t_fit) { if (!expanded) { cap = 0; smem = 0; } }
             if (smem > 48 * 1024) MRB_CUDA(cudaFuncSetAttribute(t_kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
             int its = iters, QQ = Q;

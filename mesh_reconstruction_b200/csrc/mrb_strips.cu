@@ -606,7 +606,7 @@ __global__ void __launch_bounds__(256) k_assemble_F_s(const float* __restrict__ 
 int stage12_binary(mrb_ctx* ctx, const float* vol, Dims d, int W, uint8_t* sq, uint8_t* flags, int* counts, int* binary_out);
 int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_t* flags, const uint8_t* sq, Dims d,
                  int band_size, int iters, int using_features, float* F_dev, float* last_delta_host, int* n_bricks,
-                 int* closure_err_host);
+                 int* closure_err_host, int binary_volume);
 
 // Stages 1-3 on device pointers.  F_dev: N^3 floats.  Records events ev[0..3] (+ ev[6..7] around the sweeps).
 int optimize_strips(mrb_ctx* ctx, const float* vol, const float* fmap, Dims d, int using_features, int band_size,
@@ -647,7 +647,7 @@ int optimize_strips(mrb_ctx* ctx, const float* vol, const float* fmap, Dims d, i
             int Q = 0, closure_err = 0;
             float last_delta = 0.0f;
             MRB_TRY(bricks_solve(ctx, vol, fmap, flags, sq, d, band_size, iters, using_features, F_dev,
-                                 stats ? &last_delta : nullptr, &Q, &closure_err));
+                                 stats ? &last_delta : nullptr, &Q, &closure_err, binary));
             MRB_CUDA(cudaEventRecord(ctx->ev[3], ctx->stream));
             MRB_CUDA(cudaStreamSynchronize(ctx->stream));
             if (ctx->h_mail[34] || closure_err) {
