@@ -882,9 +882,18 @@ int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_
     int tile_T = 8;
     if (getenv("MRB_QP_TILE")) tile_T = atoi(getenv("MRB_QP_TILE"));
     if (tile_T < 1) tile_T = 1;
-    int t_threads = 512;       // one block of 16 warps per SM: the patches are larger, so fewer of their bricks are rim bricks
-    if (getenv("MRB_QP_BRICK_THREADS") && atoi(getenv("MRB_QP_BRICK_THREADS")) == 256) t_threads = 256;
-    void* t_kern = t_threads == 512 ? (void*)k_qp_bricks_tiled<512, 1> : (void*)k_qp_bricks_tiled<256, 2>;
+    // One block of 15 warps per SM: the patches are larger than with two 256-thread blocks, so fewer of their bricks
+    // are rim bricks, and 480 threads leave ptxas 136 registers per thread (the update needs 127; at 512 threads the
+    // limit is 128 and the allocation is fragile: one build put part of the brick on the stack, 3.0 -> 4.3 ms).
+    int t_threads = 480;
+    if (getenv("MRB_QP_BRICK_THREADS")) t_threads = atoi(getenv("MRB_QP_BRICK_THREADS"));
+    void* t_kern = nullptr;
+    switch (t_threads) {
+        case 256: t_kern = (void*)k_qp_bricks_tiled<256, 2>; break;
+        case 448: t_kern = (void*)k_qp_bricks_tiled<448, 1>; break;
+        case 512: t_kern = (void*)k_qp_bricks_tiled<512, 1>; break;
+        default: t_threads = 480; t_kern = (void*)k_qp_bricks_tiled<480, 1>; break;
+    }
     int t_grid = 0, t_fit = 0;
     int* blk_nb = nullptr;
     int* tpos = nullptr;
@@ -1147,8 +1156,8 @@ __global__ void __launch_bounds__(Threads, MinBlocks) k_qp_bricks_sharded(const 
     float4* in = xa;
     float4* out = xb;
     for (int it = 0; it < iters; it++) {
-        float4* plo = sh.peer_lo[(it + 1) & 1];       // sweep `it` writes buffer B when it is even
-        float4* phi = sh.peer_hi[(it + 1) & 1];
+        float4* plo = (it & 1) ? sh.peer_lo[0] : sh.peer_lo[1];       // sweep `it` writes buffer B when it is even
+        float4* phi = (it & 1) ? sh.peer_hi[0] : sh.peer_hi[1];
         for (int q = q_begin + threadIdx.x; q < q_end; q += Threads) {
             const int4 na = __ldg(nbA + q);
             const int2 nz = __ldg(nbB + q);

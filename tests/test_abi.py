@@ -57,3 +57,20 @@ def test_product_does_not_reference_the_oracle():
                 if "mrbo_" in txt or "libmrb_oracle" in txt or re.search(r"^\s*(from|import)\s+oracle", txt, re.M):
                     bad.append(f)
     assert not bad, bad
+
+
+def test_sweep_kernels_keep_the_brick_in_registers():
+    """ptxas must not put any part of a brick update on the stack (it did once at 512 threads: 3.0 -> 4.3 ms)."""
+    log = os.path.join(ROOT, "mesh_reconstruction_b200", "_build", "mrb_bricks.ptxas.log")
+    if not os.path.exists(log):
+        pytest.skip("no ptxas log (library built elsewhere)")
+    text = open(log).read()
+    blocks = re.split(r"ptxas info\s*: Compiling entry function ", text)
+    seen = 0
+    for b in blocks:
+        m = re.match(r"'(\S+)'", b)
+        if not m or not any(k in m.group(1) for k in ("k_qp_bricks_tiledILi480", "k_qp_bricks_shardedILi256", "11k_qp_bricksILi256ELi2ELb0")):
+            continue
+        seen += 1
+        assert re.search(r"\b0 bytes stack frame, 0 bytes spill stores, 0 bytes spill loads", b), m.group(1)
+    assert seen >= 3
