@@ -2,7 +2,7 @@
 (exact EDT -> narrow band -> smoothness QP -> marching cubes) behind the module API of
 CRLab/Mesh_Reconstruction.  The compute lives in libmrb.so (hand-written sm_100a CUDA, C-ABI in
 include/mrb.h); this package is the Python host-side mirror used by the tests and bench.py."""
-from .api import Context, MrbError  # noqa: F401
+from .api import Context, MrbError, Pool  # noqa: F401
 from . import synth  # noqa: F401
 
-__all__ = ["Context", "MrbError", "synth"]
+__all__ = ["Context", "MrbError", "Pool", "synth"]

@@ -326,3 +326,46 @@ def _stats(st):
     return {k: getattr(st, k) for k, _ in L.QPStats._fields_}
 
 
+
+
+class Pool:
+    """Several contexts on ONE GPU, one host thread each: a context is single-threaded and synchronous (like the
+    reference's functions), but contexts are independent, so while one thread's object is in its sweep kernel the
+    other threads' host->device copies, small kernels and result read-backs overlap with it.  map() keeps the input
+    order.  This is host-side plumbing only: every object still goes through mrb_reconstruct with host buffers."""
+
+    def __init__(self, device=0, workers=2):
+        self.ctxs = [Context(device) for _ in range(int(workers))]
+
+    def close(self):
+        for c in self.ctxs:
+            c.close()
+        self.ctxs = []
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def map(self, volumes, **kw):
+        """reconstruct() of every volume (list of arrays; the same array may appear several times)."""
+        import threading
+        out = [None] * len(volumes)
+        err = []
+
+        def work(w):
+            try:
+                for i in range(w, len(volumes), len(self.ctxs)):
+                    out[i] = self.ctxs[w].reconstruct(volumes[i], **kw)
+            except BaseException as e:      # noqa: BLE001 - re-raised in the caller's thread
+                err.append(e)
+
+        ts = [threading.Thread(target=work, args=(w,)) for w in range(len(self.ctxs))]
+        for t in ts:
+            t.start()
+        for t in ts:
+            t.join()
+        if err:
+            raise err[0]
+        return out

@@ -238,3 +238,15 @@ def test_device_pointers(ctx, O, synth):
     verts, faces = ctx.reconstruct(vt)
     verts_ref, faces_ref = O.mcubes(F_ref, 0.0)
     assert np.array_equal(verts.cpu().numpy(), verts_ref) and np.array_equal(faces.cpu().numpy(), faces_ref)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("band_size", [1, 2, 3, 4, 5, 6, 7, 8, 9])
+def test_fused_stages_every_band_size(ctx, O, synth, band_size):
+    """The fused stage-1+2 tile kernels are instantiated per band_size (bit-sliced <= 4, byte arrays <= 8, global
+    passes above): each against the oracle, on a grid whose dims are not multiples of the 8 x 8 x 32 tile."""
+    v = synth.random_spheres((70, 61, 75), 4, 9, 14, seed=100 + band_size, pad=band_size + 3)
+    F_ref, info = O.optimize(v, band_size=band_size, iters=12, brute_edt=False, return_info=True)
+    F, st = ctx.optimize(v, band_size=band_size, iters=12, return_stats=True)
+    assert st["n_band"] == info["n_band"]
+    assert np.array_equal(F, F_ref)
