@@ -93,8 +93,8 @@ __global__ void __launch_bounds__(128) k_brick_build(const float* __restrict__ v
                                                      const int* __restrict__ bpos, int Q, BrickDims bd,
                                                      uint2* __restrict__ code, uint4* __restrict__ fields,
                                                      float4* __restrict__ x0, int4* __restrict__ nbA, int2* __restrict__ nbB,
-                                                     int* __restrict__ err) {
-    const size_t P = (size_t)Q + 1;      // plane stride of the SoA iterate: x[k][q], k = dx*2+dy
+                                                     int* __restrict__ err, size_t P) {
+    // P = plane stride of the SoA iterate: x[k][q], k = dx*2+dy (>= Q + 1; slot Q is the all-zero dummy brick)
     int q = blockIdx.x * blockDim.x + threadIdx.x;
     if (q >= Q) return;
     int p = bpos[q];
@@ -661,6 +661,22 @@ __global__ void __launch_bounds__(Threads, MinBlocks) k_qp_bricks(const uint2* _
 // are stored, so that the flag travels while the interior is updated -- with a barrier between the two phases
 // 3.85 ms, with per-warp fences and an arrive counter instead of the barrier 3.57-3.75 ms, polling during the
 // interior phase 4.4-5.5 ms.
+// Block b of the tiled kernel owns bricks [tiled_begin(b), tiled_begin(b+1)): whole groups of 8 bricks, and the plane
+// stride is a multiple of 8 float4, so no 128-byte line of the iterate holds bricks of two blocks (see the kernel).
+__host__ __device__ __forceinline__ int tiled_begin(int b, int Q, int G) {
+    const long long U = ((long long)Q + 7) / 8;
+    const long long q = (U * b / G) * 8;
+    return (int)(q < Q ? q : Q);
+}
+__host__ __device__ __forceinline__ int tiled_owner(int q, int Q, int G) {
+    const long long U = ((long long)Q + 7) / 8, u = q / 8;
+    int b = (int)((u * G) / U);
+    while (b + 1 < G && U * (b + 1) / G <= u) b++;
+    while (b > 0 && U * b / G > u) b--;
+    return b;
+}
+__host__ __device__ __forceinline__ size_t tiled_stride(int Q) { return ((size_t)Q + 1 + 7) & ~(size_t)7; }
+
 struct TiledOrder {
     BrickDims bd;
     int T;
@@ -699,13 +715,13 @@ __global__ void k_tiled_boundary(const int* __restrict__ tpos, int Q, int G, Til
     const int Z = (int)(p % bd.bz);
     const long long t = p / bd.bz;
     const int Y = (int)(t % bd.by), X = (int)(t / bd.by);
-    const int own = brick_owner(i, Q, G);
+    const int own = tiled_owner(i, Q, G);
     const long long cx = (long long)bd.by * bd.bz, cy = bd.bz;
     bool rim = false;
     auto look = [&](bool ok, long long dp) {
         if (!ok) return;
         const int id = bid1[p + dp];
-        if (id >= 0 && brick_owner(id, Q, G) != own) rim = true;
+        if (id >= 0 && tiled_owner(id, Q, G) != own) rim = true;
     };
     look(X >= 1, -cx); look(X <= bd.bx - 2, cx); look(Y >= 1, -cy); look(Y <= bd.by - 2, cy);
     look(Z >= 1, -1); look(Z <= bd.bz - 2, 1);
@@ -716,8 +732,8 @@ __global__ void k_tiled_final(const int* __restrict__ tpos, const int* __restric
                               int* __restrict__ bpos, int* __restrict__ bid, int* __restrict__ blk_nb) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= Q) return;
-    const int b = brick_owner(i, Q, G);
-    const int qb = (int)((long long)Q * b / G), qe = (int)((long long)Q * (b + 1) / G);
+    const int b = tiled_owner(i, Q, G);
+    const int qb = tiled_begin(b, Q, G), qe = tiled_begin(b + 1, Q, G);
     const int nbc = sb[qe] - sb[qb];
     const int rank_b = sb[i] - sb[qb];
     const bool rim = sb[i + 1] != sb[i];
@@ -728,6 +744,21 @@ __global__ void k_tiled_final(const int* __restrict__ tpos, const int* __restric
     if (i == qb) blk_nb[b] = nbc;
 }
 
+__global__ void k_tiled_bitmap(const int4* __restrict__ nbA, const int2* __restrict__ nbB, int Q, int G, int NW,
+                               unsigned* __restrict__ bitmap) {
+    int q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= Q) return;
+    const int g = tiled_owner(q, Q, G);
+    const int4 a = nbA[q];
+    const int2 z = nbB[q];
+    const int n[6] = {a.x, a.y, a.z, a.w, z.x, z.y};
+    for (int i = 0; i < 6; i++)
+        if (n[i] < Q) {
+            int o = tiled_owner(n[i], Q, G);
+            if (o != g) atomicOr(&bitmap[(size_t)g * NW + (o >> 5)], 1u << (o & 31));
+        }
+}
+
 template <int Threads, int MinBlocks>
 __global__ void __launch_bounds__(Threads, MinBlocks) k_qp_bricks_tiled(const uint2* __restrict__ code, const uint4* __restrict__ fields,
                                                                         const int4* __restrict__ nbA, const int2* __restrict__ nbB,
@@ -735,14 +766,13 @@ __global__ void __launch_bounds__(Threads, MinBlocks) k_qp_bricks_tiled(const ui
                                                                         unsigned* __restrict__ maxdelta_bits, unsigned* bar, int dbg,
                                                                         const int* __restrict__ blk_nb, unsigned* progress, int cap,
                                                                         const int* __restrict__ plist, const int* __restrict__ pcount,
-                                                                        int expanded) {
+                                                                        int expanded, size_t P) {
     __shared__ float s_sqrt[256];
     __shared__ float s_inv[32];
     for (int i = threadIdx.x; i < 256; i += Threads) s_sqrt[i] = c_brick_sqrt[i];
     if (threadIdx.x < 32) s_inv[threadIdx.x] = c_brick_invdg[threadIdx.x];
-    const size_t P = (size_t)Q + 1;
-    const int q_begin = (int)((long long)Q * blockIdx.x / gridDim.x);
-    const int q_end = (int)((long long)Q * (blockIdx.x + 1) / gridDim.x);
+    const int q_begin = tiled_begin(blockIdx.x, Q, gridDim.x);
+    const int q_end = tiled_begin(blockIdx.x + 1, Q, gridDim.x);
     const int q_int = q_begin + blk_nb[blockIdx.x];          // first interior brick
     __syncthreads();
     // Per-brick constants in shared memory, copied once: expanded (168 B per brick, see BrickConstsX) when they fit,
@@ -780,9 +810,14 @@ __global__ void __launch_bounds__(Threads, MinBlocks) k_qp_bricks_tiled(const ui
         if ((int)threadIdx.x + 32 < np) watch2 = progress + (size_t)plist[(size_t)blockIdx.x * kChunkListCap + threadIdx.x + 32] * kProgressStride;
     }
     unsigned* mine = progress + (size_t)blockIdx.x * kProgressStride;
-    // interior work is dealt from the last warp down, so warp 0 (which pays for the release) gets the remainder
+    // Work order inside a sweep: interior bricks first, dealt from warp 0 up; rim bricks second, dealt from the last warp
+    // down, so that warp 0 (which publishes and polls) has the least to do.
     constexpr int W = Threads / 32;
     const int rtid = (W - 1 - (int)(threadIdx.x >> 5)) * 32 + (int)(threadIdx.x & 31);
+    __shared__ unsigned s_seen;              // number of sweeps whose neighbour flags have all been observed
+    if (threadIdx.x == 0) s_seen = 0;
+    const unsigned s_seen_addr = (unsigned)__cvta_generic_to_shared(&s_seen);
+    __syncthreads();
     const float4* in = xa;
     float4* out = xb;
     auto update = [&](int q, bool last) {
@@ -800,33 +835,49 @@ __global__ void __launch_bounds__(Threads, MinBlocks) k_qp_bricks_tiled(const ui
         }
         return brick_update(q, P, na, nz, c, f0, f1, in, out, s_sqrt, s_inv, last);
     };
+    // Sweep it: (1) interior bricks -- they read this block's own bricks only, so they start right after the barrier
+    // that ended sweep it-1, while that sweep's flag is still travelling; (2) rim bricks -- they wait until warp 0 has seen
+    // "sweep it-1 done" from every neighbour block (which also means the neighbours no longer read the buffer this sweep
+    // overwrites); (3) barrier, publish.  One block-wide barrier per sweep; the release -> poll round trip (about 1.3 us)
+    // is hidden behind the interior phase instead of being paid by every warp.
+    // L1 coherence: warp 0's acquire loads invalidate this SM's L1 after the neighbours' stores are visible.  Loads that
+    // are in flight at that moment belong to interior bricks and touch this block's own lines only (block ranges and the
+    // plane stride are multiples of 8 bricks = 128 bytes), so no line with another block's bricks can be cached stale.
     for (int it = 0; it < iters; it++) {
         const bool last = it == iters - 1;
         float dmax = 0.0f;
-        if (it > 0) {
-            if ((dbg & 4) && !(dbg & 1)) brick_grid_barrier(bar, (unsigned)it, gridDim.x);
-            __syncthreads();        // neighbour flags are in (polled below); this block's interior bricks of sweep it-1 are stored
-        }
-        for (int q = q_begin + threadIdx.x; q < q_int; q += Threads) dmax = fmaxf(dmax, update(q, last));
-        for (int q = q_int + rtid; q < q_end; q += Threads) dmax = fmaxf(dmax, update(q, last));
-        if (!last && !(dbg & 5)) {
-            __syncthreads();        // the block's stores of this sweep are issued
-            if (threadIdx.x == 0) asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(mine), "r"((unsigned)(it + 1)) : "memory");
-            // warp 0 collects the neighbours' flags of this sweep; the barrier at the top of the next sweep hands them on
+        const bool flags_on = !(dbg & 5);
+        if (it > 0 && (dbg & 4) && !(dbg & 1)) brick_grid_barrier(bar, (unsigned)it, gridDim.x);
+        if (it > 0 && flags_on && threadIdx.x < 32) {
+            // warp 0: collect the neighbours' flags of sweep it-1, then tell the block
             unsigned v, spins = 0;
             if (watch) do {
                 asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(watch) : "memory");
                 if (++spins == (1u << 26)) __trap();       // a lost producer must not hang the GPU
-            } while (v < (unsigned)(it + 1));
+            } while (v < (unsigned)it);
             if (watch2) do {
                 asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(watch2) : "memory");
                 if (++spins == (1u << 26)) __trap();
-            } while (v < (unsigned)(it + 1));
+            } while (v < (unsigned)it);
+            __syncwarp();
+            if (threadIdx.x == 0) asm volatile("st.release.cta.shared.u32 [%0], %1;" ::"r"(s_seen_addr), "r"((unsigned)it) : "memory");
         }
+        for (int q = q_int + threadIdx.x; q < q_end; q += Threads) dmax = fmaxf(dmax, update(q, last));
+        if (it > 0 && flags_on && q_begin + rtid < q_int) {
+            unsigned v;
+            do {
+                asm volatile("ld.acquire.cta.shared.u32 %0, [%1];" : "=r"(v) : "r"(s_seen_addr) : "memory");
+            } while (v < (unsigned)it);
+        }
+        for (int q = q_begin + rtid; q < q_int; q += Threads) dmax = fmaxf(dmax, update(q, last));
         if (last) {
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) dmax = fmaxf(dmax, __shfl_xor_sync(0xffffffffu, dmax, o));
             if ((threadIdx.x & 31) == 0) atomicMax(maxdelta_bits, __float_as_uint(dmax));
+        } else if (!(dbg & 1)) {
+            __syncthreads();        // the block's stores of this sweep are issued; its reads of the neighbours' bricks are done
+            if (flags_on && threadIdx.x == 0)
+                asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(mine), "r"((unsigned)(it + 1)) : "memory");
         }
         const float4* t = in; in = out; out = (float4*)t;
     }
@@ -917,6 +968,7 @@ int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_
         MRB_TRY(arena_alloc(ctx, (size_t)Q + 1, &sb));
         MRB_TRY(arena_alloc(ctx, (size_t)Q, &bpos));
         MRB_TRY(arena_alloc(ctx, (size_t)t_grid, &blk_nb));
+        MRB_CUDA(cudaMemsetAsync(blk_nb, 0, (size_t)t_grid * sizeof(int), ctx->stream));      // blocks with an empty range
         MRB_LAUNCH(ctx, k_fill_i32b, grid_for(ctx, nb, 256), 256, 0, bid1, nb, -1);
         MRB_LAUNCH(ctx, k_tiled_scatter, cdiv(Q, 256), 256, 0, tpos, Q, ord, bid1);
         MRB_LAUNCH(ctx, k_tiled_boundary, cdiv(Q, 256), 256, 0, tpos, Q, t_grid, ord, bid1, sb);
@@ -924,6 +976,7 @@ int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_
         MRB_LAUNCH(ctx, k_tiled_final, cdiv(Q, 256), 256, 0, tpos, sb, Q, t_grid, ord, bpos, bid, blk_nb);
     }
     const size_t Qn = (size_t)(Q > 0 ? Q : 1);
+    const size_t P = tiled ? tiled_stride(Q) : (size_t)Q + 1;       // plane stride of the SoA iterate
     uint2* code = nullptr;
     uint4* fields = nullptr;
     float4 *xa = nullptr, *xb = nullptr;
@@ -931,8 +984,8 @@ int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_
     int2* nbB = nullptr;
     MRB_TRY(arena_alloc(ctx, Qn, &code));
     MRB_TRY(arena_alloc(ctx, 2 * Qn, &fields));
-    MRB_TRY(arena_alloc(ctx, 4 * (Qn + 1), &xa));
-    MRB_TRY(arena_alloc(ctx, 4 * (Qn + 1), &xb));
+    MRB_TRY(arena_alloc(ctx, 4 * P, &xa));
+    MRB_TRY(arena_alloc(ctx, 4 * P, &xb));
     MRB_TRY(arena_alloc(ctx, Qn, &nbA));
     MRB_TRY(arena_alloc(ctx, Qn, &nbB));
     const float* xres = (const float*)xa;
@@ -940,9 +993,9 @@ int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_
         if (!tiled) MRB_LAUNCH(ctx, k_scatter_brick_ids, cdiv(Q, 256), 256, 0, bpos, Q, bid);
         int* err = ctx->d_mail + 24;
         MRB_CUDA(cudaMemsetAsync(err, 0, sizeof(int), ctx->stream));
-        for (int k = 0; k < 4; k++) MRB_CUDA(cudaMemsetAsync(xa + (size_t)k * (Q + 1) + Q, 0, sizeof(float4), ctx->stream));
-        MRB_CUDA(cudaMemsetAsync(xb, 0, 4 * (Qn + 1) * sizeof(float4), ctx->stream));
-        MRB_LAUNCH(ctx, k_brick_build, cdiv(Q, 128), 128, 0, vol, sq, flags, bid, bpos, Q, bd, code, fields, xa, nbA, nbB, err);
+        for (int k = 0; k < 4; k++) MRB_CUDA(cudaMemsetAsync(xa + (size_t)k * P + Q, 0, (P - Q) * sizeof(float4), ctx->stream));
+        MRB_CUDA(cudaMemsetAsync(xb, 0, 4 * P * sizeof(float4), ctx->stream));
+        MRB_LAUNCH(ctx, k_brick_build, cdiv(Q, 128), 128, 0, vol, sq, flags, bid, bpos, Q, bd, code, fields, xa, nbA, nbB, err, P);
         MRB_CUDA(cudaMemcpyAsync(ctx->h_mail + 24, err, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
         MRB_CUDA(cudaStreamSynchronize(ctx->stream));
         *closure_err_host = ctx->h_mail[24];
@@ -964,13 +1017,13 @@ int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_
             MRB_CUDA(cudaMemsetAsync(bitmap, 0, (size_t)grid * NW * sizeof(unsigned), ctx->stream));
             MRB_CUDA(cudaMemsetAsync(pcount, 0, (size_t)grid * sizeof(int), ctx->stream));
             MRB_CUDA(cudaMemsetAsync(ovf, 0, sizeof(int), ctx->stream));
-            MRB_LAUNCH(ctx, k_chunk_bitmap, cdiv(Q, 256), 256, 0, nbA, nbB, Q, grid, 1, NW, bitmap);
+            MRB_LAUNCH(ctx, k_tiled_bitmap, cdiv(Q, 256), 256, 0, nbA, nbB, Q, grid, NW, bitmap);
             MRB_LAUNCH(ctx, k_chunk_lists, cdiv((size_t)grid * 32, 256), 256, 0, bitmap, grid, NW, plist, pcount, ovf);
             int overflow = 0;
             MRB_TRY(read_int(ctx, ovf, &overflow));
             int dbg = getenv("MRB_QP_DEBUG") ? atoi(getenv("MRB_QP_DEBUG")) : 0;
             if (overflow) dbg |= 4;        // a block with more than kChunkListCap neighbour blocks: grid barrier per sweep
-            int cap = (Q + grid - 1) / grid + 1;
+            int cap = (Q + grid - 1) / grid + 9;       // block ranges are whole groups of 8 bricks
             // expanded constants (168 B per brick) for binary volumes if one block's share fits, else the 64-byte form
             int expanded = binary_volume ? 1 : 0;
             size_t smem = (size_t)cap * 168;
@@ -981,7 +1034,7 @@ int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_
             int its = iters, QQ = Q;
             void* args[] = {(void*)&code, (void*)&fields, (void*)&nbA, (void*)&nbB, (void*)&xa, (void*)&xb, (void*)&QQ, (void*)&its,
                             (void*)&md, (void*)&bar, (void*)&dbg, (void*)&blk_nb, (void*)&progress, (void*)&cap, (void*)&plist, (void*)&pcount,
-                            (void*)&expanded};
+                            (void*)&expanded, (void*)&P};
             MRB_CUDA(cudaEventRecord(ctx->ev[6], ctx->stream));
             MRB_CUDA(cudaLaunchCooperativeKernel(t_kern, dim3(grid), dim3(t_threads), args, smem, ctx->stream));
             MRB_CUDA(cudaEventRecord(ctx->ev[7], ctx->stream));
@@ -1076,9 +1129,9 @@ int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_
         MRB_CUDA(cudaMemsetAsync(flag, 0, sizeof(int), ctx->stream));
         const unsigned g = grid_for(ctx, n, 256);
         MRB_LAUNCH(ctx, k_feat_check_b, g, 256, 0, fmap, flags, n, flag);
-        MRB_LAUNCH(ctx, k_feat_apply_b, g, 256, 0, fmap, flags, bid, bd, (size_t)Q + 1, flag, (float*)xres);
+        MRB_LAUNCH(ctx, k_feat_apply_b, g, 256, 0, fmap, flags, bid, bd, P, flag, (float*)xres);
     }
-    MRB_LAUNCH(ctx, k_assemble_F_b, grid_for(ctx, n, 256), 256, 0, vol, flags, bid, xres, bd, (size_t)Q + 1, (double)band_size + 1.0,
+    MRB_LAUNCH(ctx, k_assemble_F_b, grid_for(ctx, n, 256), 256, 0, vol, flags, bid, xres, bd, P, (double)band_size + 1.0,
                F_dev);
     return MRB_OK;
 }
@@ -1306,7 +1359,7 @@ int mrb_qp_plan_create(mrb_ctx* ctx, const float* volume, const int dims[3], int
         MRB_CUDA(cudaMemsetAsync(err, 0, sizeof(int), ctx->stream));
         MRB_CUDA(cudaMemsetAsync(p->x0, 0, 4 * (Qn + 1) * sizeof(float4), ctx->stream));
         MRB_LAUNCH(ctx, k_brick_build, cdiv(Q, 128), 128, 0, dv, p->sq, p->flags, p->bid, bpos, Q, p->bd, p->code, p->fields,
-                   p->x0, p->nbA, p->nbB, err);
+                   p->x0, p->nbA, p->nbB, err, (size_t)Q + 1);
         std::vector<int> hpos((size_t)Q);
         MRB_CUDA(cudaMemcpyAsync(hpos.data(), bpos, (size_t)Q * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
         MRB_CUDA(cudaMemcpyAsync(ctx->h_mail + 24, err, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
