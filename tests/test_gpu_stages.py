@@ -250,3 +250,15 @@ def test_fused_stages_every_band_size(ctx, O, synth, band_size):
     F, st = ctx.optimize(v, band_size=band_size, iters=12, return_stats=True)
     assert st["n_band"] == info["n_band"]
     assert np.array_equal(F, F_ref)
+
+
+@pytest.mark.gpu
+def test_sweep_synchronisation_is_repeatable(ctx, synth):
+    """The persistent sweep kernel synchronises blocks with flags in global memory: a lost wait would show up as a
+    run-to-run difference.  Many short runs (different grid sizes -> different block / neighbour-list shapes)."""
+    for n, r, iters in ((96, 30.0, 40), (160, 60.0, 30), (256, 110.0, 12)):
+        v = synth.sphere(n, r)
+        first = ctx.optimize(v, iters=iters)
+        for _ in range(12 if n < 256 else 4):
+            again = ctx.optimize(v, iters=iters)
+            assert np.array_equal(first, again)
