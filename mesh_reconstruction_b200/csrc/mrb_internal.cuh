@@ -175,9 +175,17 @@ int dev_assemble_F(mrb_ctx* ctx, const float* volume, const BandDev& bd, const f
 int classify_cells(mrb_ctx* ctx, const float* F, Dims d, float iso, int** cells_out, int* ncells_out);
 // triangle soup (3 floats per corner) + hashXYZ keys -> per-corner vertex ids and unique vertices (first-appearance order)
 int dev_dedup(mrb_ctx* ctx, const float* soup, const unsigned long long* keys, int ncorner, int* faces, float** verts_out,
-              int* nverts_out);
+              int* nverts_out, int** vid_out = nullptr);
 int export_mesh(mrb_ctx* ctx, float* verts_dev, int* faces_dev, int nverts, int nfaces, int device_out, mrb_mesh* out);
+// Stacked batch: d is nobj objects of xpitch x-planes each, stacked along x.  Faces come back with per-object vertex
+// ids; face_off_host / vert_off_host (nobj + 1 entries) delimit the objects.  *seam_err_host = 1 (and no mesh) if a
+// surface-crossing cell spans two objects.
+struct McStack {
+    int nobj, xpitch;
+    unsigned long long kstride;
+    int *face_off_host, *vert_off_host, *seam_err_host;
+};
 int dev_mcubes(mrb_ctx* ctx, const float* F, Dims d, float isolevel, float** verts_dev, int** faces_dev,
-               int* nverts, int* nfaces);
+               int* nverts, int* nfaces, const McStack* stack = nullptr);
 
 }  // namespace mrb

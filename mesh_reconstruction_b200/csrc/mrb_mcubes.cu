@@ -33,6 +33,11 @@ __constant__ int c_edge_b[12] = {1, 2, 3, 0, 5, 6, 7, 4, 4, 5, 6, 7};
 struct CellDims {
     int nx, ny, nz;      // grid dims
     int cx, cy, cz;      // cell dims = grid dims - 1
+    // stacked batch (mrb_reconstruct_batch): the grid is nobj objects of xpitch x-planes each, one after the other along
+    // x.  Vertex coordinates are local to the object and its hash keys are shifted by obj * kstride, so every object
+    // gets exactly the vertices, keys and first-appearance order it would get alone.  0 = one object.
+    int xpitch;
+    unsigned long long kstride;
 };
 
 // corner n of cell (i,j,k): (i + [n%4 in {1,2}], j + (n%4)/2, k + n/4)  (mcubes.cpp:166-168)
@@ -127,6 +132,9 @@ __device__ __forceinline__ int polygonise(const float* __restrict__ F, const Cel
     int ci = cube_index(v, iso);
     uint64_t w = c_tri[ci];
     int ntri = (int)(w & 15);
+    const int ob = cd.xpitch ? i / cd.xpitch : 0;
+    const unsigned long long kofs = (unsigned long long)ob * cd.kstride;
+    i -= ob * cd.xpitch;             // coordinates local to the object (the corner values were read above)
     F3 vert[12];
 #pragma unroll
     for (int e = 0; e < 12; e++) {
@@ -153,9 +161,9 @@ __device__ __forceinline__ int polygonise(const float* __restrict__ F, const Cel
             soup[o + 3] = b.x; soup[o + 4] = b.y; soup[o + 5] = b.z;
             soup[o + 6] = c.x; soup[o + 7] = c.y; soup[o + 8] = c.z;
             size_t kq = (size_t)(first_tri + out) * 3;
-            keys[kq + 0] = hash_xyz(a, cd.ny, cd.nz);
-            keys[kq + 1] = hash_xyz(b, cd.ny, cd.nz);
-            keys[kq + 2] = hash_xyz(c, cd.ny, cd.nz);
+            keys[kq + 0] = hash_xyz(a, cd.ny, cd.nz) + kofs;
+            keys[kq + 1] = hash_xyz(b, cd.ny, cd.nz) + kofs;
+            keys[kq + 2] = hash_xyz(c, cd.ny, cd.nz) + kofs;
         }
         out++;
     }
@@ -163,10 +171,45 @@ __device__ __forceinline__ int polygonise(const float* __restrict__ F, const Cel
 }
 
 __global__ void __launch_bounds__(128) k_mc_count(const float* __restrict__ F, CellDims cd, const int* __restrict__ cells,
-                                                  int ncells, float iso, int* __restrict__ ntri) {
+                                                  int ncells, float iso, int* __restrict__ ntri, int* __restrict__ seam_err) {
     int a = blockIdx.x * blockDim.x + threadIdx.x;
     if (a >= ncells) return;
+    if (cd.xpitch) {                 // a crossing cell that spans two objects of a stacked batch: the caller falls back
+        const int i = cells[a] / (cd.cz * cd.cy);
+        if (i % cd.xpitch == cd.xpitch - 1) *seam_err = 1;
+    }
     ntri[a] = polygonise<false>(F, cd, cells[a], iso, nullptr, nullptr, 0);
+}
+
+// ---- per-object offsets of a stacked batch ------------------------------------------------------------------------
+__global__ void k_stack_face_off(const int* __restrict__ cells, int ncells, const int* __restrict__ tri_off, int ntri, CellDims cd,
+                                 int nobj, int* __restrict__ face_off) {
+    int a = blockIdx.x * blockDim.x + threadIdx.x;
+    if (a > ncells) return;
+    const int plane = cd.cz * cd.cy;
+    const int prev = a > 0 ? (cells[a - 1] / plane) / cd.xpitch : -1;
+    const int cur = a < ncells ? (cells[a] / plane) / cd.xpitch : nobj;
+    const int off = a < ncells ? tri_off[a] : ntri;
+    for (int o = prev + 1; o <= cur; o++) face_off[o] = off;       // objects without a crossing cell get an empty range
+}
+__global__ void k_stack_vert_off(const int* __restrict__ face_off, const int* __restrict__ vid, int ntri, int nverts, int nobj,
+                                 int* __restrict__ vert_off) {
+    int o = blockIdx.x * blockDim.x + threadIdx.x;
+    if (o > nobj) return;
+    const int f = face_off[o];
+    vert_off[o] = f < ntri ? vid[3 * (size_t)f] : nverts;          // first-appearance ids grow with the corner position
+}
+__global__ void k_stack_localise(int* __restrict__ faces, int ntri, const int* __restrict__ face_off, const int* __restrict__ vert_off,
+                                 int nobj) {
+    int f = blockIdx.x * blockDim.x + threadIdx.x;
+    if (f >= ntri) return;
+    int lo = 0, hi = nobj;           // largest o with face_off[o] <= f
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (face_off[mid] <= f) lo = mid; else hi = mid;
+    }
+    const int v0 = vert_off[lo];
+    faces[3 * (size_t)f] -= v0; faces[3 * (size_t)f + 1] -= v0; faces[3 * (size_t)f + 2] -= v0;
 }
 
 __global__ void __launch_bounds__(128) k_mc_emit(const float* __restrict__ F, CellDims cd, const int* __restrict__ cells,
@@ -230,7 +273,7 @@ __global__ void k_assign_ids(const int* __restrict__ slot_of, const int* __restr
 
 // keys -> (vertex ids per corner, unique vertices).  Scratch comes from the ctx arena.
 int dev_dedup(mrb_ctx* ctx, const float* soup, const unsigned long long* keys, int ncorner, int* faces, float** verts_out,
-              int* nverts_out) {
+              int* nverts_out, int** vid_out) {
     size_t cap = 1024;
     while (cap < (size_t)ncorner * 2) cap <<= 1;
     unsigned long long* tkeys = nullptr;
@@ -251,6 +294,7 @@ int dev_dedup(mrb_ctx* ctx, const float* soup, const unsigned long long* keys, i
     MRB_LAUNCH(ctx, k_assign_ids, cdiv(ncorner, 256), 256, 0, slot_of, tfirst, is_first, soup, ncorner, faces, verts);
     *verts_out = verts;
     *nverts_out = nverts;
+    if (vid_out) *vid_out = is_first;       // exclusive scan of the first-appearance marks = vertex id per first corner
     return MRB_OK;
 }
 
@@ -343,22 +387,29 @@ int classify_cells(mrb_ctx* ctx, const float* F, Dims d, float iso, int** cells_
 }
 
 int dev_mcubes(mrb_ctx* ctx, const float* F, Dims d, float isolevel, float** verts_dev, int** faces_dev, int* nverts,
-               int* nfaces) {
+               int* nfaces, const McStack* stack) {
     *verts_dev = nullptr; *faces_dev = nullptr; *nverts = 0; *nfaces = 0;
+    if (stack) {
+        for (int o = 0; o <= stack->nobj; o++) { stack->face_off_host[o] = 0; stack->vert_off_host[o] = 0; }
+        *stack->seam_err_host = 0;
+    }
     if (d.nx < 2 || d.ny < 2 || d.nz < 2) return MRB_OK;
-    CellDims cd{d.nx, d.ny, d.nz, d.nx - 1, d.ny - 1, d.nz - 1};
-    size_t ncell_total = (size_t)cd.cx * cd.cy * cd.cz;
+    CellDims cd{d.nx, d.ny, d.nz, d.nx - 1, d.ny - 1, d.nz - 1, 0, 0ull};
+    if (stack) { cd.xpitch = stack->xpitch; cd.kstride = stack->kstride; }
     int* cells = nullptr;
     int ncells = 0;
-    (void)ncell_total;
     MRB_TRY(classify_cells(ctx, F, d, isolevel, &cells, &ncells));
     if (ncells == 0) return MRB_OK;
     int* tri_off = nullptr;
     MRB_TRY(arena_alloc(ctx, (size_t)ncells, &tri_off));
-    MRB_LAUNCH(ctx, k_mc_count, cdiv(ncells, 128), 128, 0, F, cd, cells, ncells, isolevel, tri_off);
+    int* seam = ctx->d_mail + 54;
+    MRB_CUDA(cudaMemsetAsync(seam, 0, sizeof(int), ctx->stream));
+    MRB_LAUNCH(ctx, k_mc_count, cdiv(ncells, 128), 128, 0, F, cd, cells, ncells, isolevel, tri_off, seam);
     MRB_TRY(scan_exclusive(ctx, tri_off, tri_off, (size_t)ncells, ctx->d_mail));
+    MRB_CUDA(cudaMemcpyAsync(ctx->h_mail + 54, seam, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
     int ntri = 0;
     MRB_TRY(read_int(ctx, ctx->d_mail, &ntri));
+    if (stack && ctx->h_mail[54]) { *stack->seam_err_host = 1; return MRB_OK; }
     if (ntri == 0) return MRB_OK;
     float* soup = nullptr;
     unsigned long long* keys = nullptr;
@@ -367,9 +418,22 @@ int dev_mcubes(mrb_ctx* ctx, const float* F, Dims d, float isolevel, float** ver
     MRB_TRY(arena_alloc(ctx, (size_t)ntri * 3, &keys));
     MRB_TRY(arena_alloc(ctx, (size_t)ntri * 3, &faces));
     MRB_LAUNCH(ctx, k_mc_emit, cdiv(ncells, 128), 128, 0, F, cd, cells, ncells, isolevel, tri_off, soup, keys);
-    MRB_TRY(dev_dedup(ctx, soup, keys, ntri * 3, faces, verts_dev, nverts));
+    int* vid = nullptr;
+    MRB_TRY(dev_dedup(ctx, soup, keys, ntri * 3, faces, verts_dev, nverts, &vid));
     *faces_dev = faces;
     *nfaces = ntri;
+    if (stack) {
+        int *foff = nullptr, *voff = nullptr;
+        const int n1 = stack->nobj + 1;
+        MRB_TRY(arena_alloc(ctx, (size_t)n1, &foff));
+        MRB_TRY(arena_alloc(ctx, (size_t)n1, &voff));
+        MRB_LAUNCH(ctx, k_stack_face_off, cdiv(ncells + 1, 256), 256, 0, cells, ncells, tri_off, ntri, cd, stack->nobj, foff);
+        MRB_LAUNCH(ctx, k_stack_vert_off, cdiv(n1, 256), 256, 0, foff, vid, ntri, *nverts, stack->nobj, voff);
+        MRB_LAUNCH(ctx, k_stack_localise, cdiv(ntri, 256), 256, 0, faces, ntri, foff, voff, stack->nobj);
+        MRB_CUDA(cudaMemcpyAsync(stack->face_off_host, foff, sizeof(int) * n1, cudaMemcpyDeviceToHost, ctx->stream));
+        MRB_CUDA(cudaMemcpyAsync(stack->vert_off_host, voff, sizeof(int) * n1, cudaMemcpyDeviceToHost, ctx->stream));
+        MRB_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
     return MRB_OK;
 }
 

@@ -82,3 +82,29 @@ def test_config5_batch_of_objects(ctx, O, synth):
     for i, (verts, faces) in enumerate(meshes):
         verts_ref, faces_ref = O.mcubes(O.optimize(vols[i]), 0.0)
         assert np.array_equal(faces, faces_ref) and np.array_equal(verts, verts_ref), i
+
+
+@pytest.mark.gpu
+def test_batch_stacked_equals_one_by_one(ctx, synth):
+    """mrb_reconstruct_batch runs a batch as ONE stacked grid when the objects' x-borders are empty; every object must
+    come out exactly as from mrb_reconstruct on that object alone (odd x size: bricks straddle the object seams)."""
+    vols = np.stack([synth.random_object(2000 + i, n=47) for i in range(9)])
+    meshes = ctx.reconstruct_batch(vols)
+    for i, (verts, faces) in enumerate(meshes):
+        v1, f1 = ctx.reconstruct(vols[i])
+        assert np.array_equal(faces, f1) and np.array_equal(verts, v1), i
+    # an object whose shape comes too close to its x-border cannot be stacked; alone it is the reference's "band touches the
+    # border" exit, and the batch must report it the same way, naming the object
+    vols2 = vols.copy()
+    vols2[4] = 0.0
+    vols2[4, 4:20, 15:30, 15:30] = 1.0
+    with pytest.raises(Exception, match="object 4.*border"):
+        ctx.reconstruct_batch(vols2)
+    # an empty object in the middle of a stack, and iso != 0
+    vols3 = vols.copy()
+    vols3[2] = 0.0
+    meshes3 = ctx.reconstruct_batch(vols3, isolevel=0.25)
+    for i, (verts, faces) in enumerate(meshes3):
+        v1, f1 = ctx.reconstruct(vols3[i], isolevel=0.25)
+        assert np.array_equal(faces, f1) and np.array_equal(verts, v1), i
+    assert len(meshes3[2][1]) == 0
