@@ -313,6 +313,12 @@ def main():
                        "mesh": {"verts": int(len(verts)), "faces": int(len(faces))}},
             "meshes_per_s": world / (ms_per_step / 1000.0),
             "stages_ms": {k: float(np.mean([s[k] for s in stats])) for k in ("ms_dfield", "ms_band", "ms_qp", "ms_mc")},
+            # SURVEY 8d algorithmic bytes per stage / stage time / measured peak (stage 2's time includes the brick build)
+            "stages_roofline_frac": {
+                "stage1_edt": 8.0 * volume.size / (np.mean([s["ms_dfield"] for s in stats]) * 1e6) / peak,
+                "stage2_band": (4.0 * volume.size + 4.0 * B) / (np.mean([s["ms_band"] for s in stats]) * 1e6) / peak,
+                "stage3_qp": alg_bytes / (np.mean([s["ms_qp"] for s in stats]) * 1e6) / peak,
+                "stage4_mc": (4.0 * volume.size + 12.0 * len(faces) + 12.0 * len(verts)) / (np.mean([s["ms_mc"] for s in stats]) * 1e6) / peak},
             "qp_kernel_voxel_updates_per_s": float(B) * args.iters / (qp_kernel_ms / 1000.0),
             "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_ms_per_step,
                     "host_threads": E2E_WORKERS, "latency_ms_one_call": float(np.median(lat_ms)),
