@@ -10,6 +10,7 @@
 #include <string.h>
 #include <algorithm>
 #include <string>
+#include <thread>
 #include <vector>
 
 namespace mrb {
@@ -242,34 +243,54 @@ int mrb_reconstruct_batch(mrb_ctx* ctx, const float* volumes, const int dims[3],
     return MRB_OK;
 }
 
-// ASCII PLY, mcubes.cpp:626-660.  "%g" == default ostream float formatting (6 significant digits).
+// ASCII PLY, mcubes.cpp:626-660.  "%g" == default ostream float formatting (6 significant digits).  The text is
+// formatted by several host threads (one contiguous range of lines each) and written with one fwrite per range: the
+// reference's `<< endl` per line makes this file write the slowest part of its whole run once the kernels are fast.
 int mrb_write_ply(const char* path, const float* verts, int nverts, const int* faces, int nfaces, const float scale[3],
                   const float shift[3], int pad) {
     if (!path || (nverts > 0 && !verts) || (nfaces > 0 && !faces) || !scale || !shift) { set_error("mrb_write_ply: NULL argument"); return MRB_EINVAL; }
     FILE* f = fopen(path, "w");
     if (!f) { set_error("mrb_write_ply: cannot open %s", path); return MRB_EINVAL; }
-    std::string buf;
-    buf.reserve(1 << 20);
-    char line[512];
-    int len = snprintf(line, sizeof(line),
-                       "ply\nformat ascii 1.0\nelement vertex %d\nproperty float x\nproperty float y\nproperty float z\n"
-                       "element face %d\nproperty list uchar int vertex_indices\nend_header\n", nverts, nfaces);
-    buf.append(line, len);
-    for (int i = 0; i < nverts; i++) {
-        float p[3];
-        // grid::getCloudPoint, grid.cpp:204-210
-        for (int a = 0; a < 3; a++) p[a] = ((verts[3 * (size_t)i + a] - (float)pad) * scale[a]) + shift[a];
-        len = snprintf(line, sizeof(line), "%g %g %g\n", p[0], p[1], p[2]);
-        buf.append(line, len);
-        if (buf.size() > (1 << 20) - 256) { fwrite(buf.data(), 1, buf.size(), f); buf.clear(); }
+    char head[512];
+    int hl = snprintf(head, sizeof(head),
+                      "ply\nformat ascii 1.0\nelement vertex %d\nproperty float x\nproperty float y\nproperty float z\n"
+                      "element face %d\nproperty list uchar int vertex_indices\nend_header\n", nverts, nfaces);
+    const size_t lines = (size_t)nverts + (size_t)nfaces;
+    unsigned hw = std::thread::hardware_concurrency();
+    size_t nth = hw ? hw : 4;
+    if (nth > 32) nth = 32;
+    if (lines < 20000) nth = 1;
+    std::vector<std::string> part(nth);
+    auto work = [&](size_t t) {
+        const size_t l0 = lines * t / nth, l1 = lines * (t + 1) / nth;
+        std::string& buf = part[t];
+        buf.reserve((l1 - l0) * 28 + 64);
+        char line[128];
+        for (size_t l = l0; l < l1; l++) {
+            int len;
+            if (l < (size_t)nverts) {
+                float p[3];
+                // grid::getCloudPoint, grid.cpp:204-210
+                for (int a = 0; a < 3; a++) p[a] = ((verts[3 * l + a] - (float)pad) * scale[a]) + shift[a];
+                len = snprintf(line, sizeof(line), "%g %g %g\n", p[0], p[1], p[2]);
+            } else {
+                const size_t i = l - (size_t)nverts;
+                len = snprintf(line, sizeof(line), "3 %d %d %d\n", faces[3 * i], faces[3 * i + 1], faces[3 * i + 2]);
+            }
+            buf.append(line, len);
+        }
+    };
+    if (nth == 1) {
+        work(0);
+    } else {
+        std::vector<std::thread> th;
+        for (size_t t = 0; t < nth; t++) th.emplace_back(work, t);
+        for (auto& t : th) t.join();
     }
-    for (int i = 0; i < nfaces; i++) {
-        len = snprintf(line, sizeof(line), "3 %d %d %d\n", faces[3 * (size_t)i], faces[3 * (size_t)i + 1], faces[3 * (size_t)i + 2]);
-        buf.append(line, len);
-        if (buf.size() > (1 << 20) - 256) { fwrite(buf.data(), 1, buf.size(), f); buf.clear(); }
-    }
-    fwrite(buf.data(), 1, buf.size(), f);
-    fclose(f);
+    bool ok = fwrite(head, 1, hl, f) == (size_t)hl;
+    for (size_t t = 0; t < nth && ok; t++) ok = fwrite(part[t].data(), 1, part[t].size(), f) == part[t].size();
+    ok = (fclose(f) == 0) && ok;
+    if (!ok) { set_error("mrb_write_ply: write to %s failed", path); return MRB_EINVAL; }
     return MRB_OK;
 }
 
