@@ -759,14 +759,61 @@ __global__ void k_tiled_bitmap(const int4* __restrict__ nbA, const int2* __restr
         }
 }
 
-template <int Threads, int MinBlocks>
+// Slab-sharded runs (mrb_qp_plan_solve_sharded): the same kernel on every GPU over its own x-slab.  The bricks of the
+// neighbour GPUs' adjacent planes are halo slots behind the owned bricks (never updated here); a rim brick of this
+// GPU's first / last plane is also stored into the neighbour's halo slot over NVLink peer memory, so the halo travels
+// with the sweep's own stores.  Blocks that own such bricks publish the sweep in a slot of the neighbour's flag array
+// (system scope) and wait for the neighbour's slots the same way as for local blocks: behind the interior phase.
+static const int kShardSlots = 128;
+struct TShard {
+    float4* peer_lo[2];          // lower / upper neighbour's iterate buffers (A, B); nullptr = no neighbour
+    float4* peer_hi[2];
+    size_t P_lo, P_hi;           // their plane strides
+    const int2* peer_ids;        // per owned brick: slot in the lower (.x) / upper (.y) neighbour's layout, -1 = none
+    const int* slot_lo;          // per block: its slot among this GPU's blocks that push down / up, -1 = none
+    const int* slot_hi;
+    unsigned* flag_lo_remote;    // lower neighbour's "from upper" slots / upper neighbour's "from lower" slots
+    unsigned* flag_hi_remote;
+    unsigned* flags_local;       // [0,128) from lower, [128,256) from upper, [256] / [257]: pusher blocks of the lower / upper neighbour + 1
+};
+
+// The constants of one brick for the tiled kernel, from wherever they live (expanded / compact shared memory, global).
+struct TiledConsts {
+    bool expanded, smem_consts;
+    int q_begin, cap, Q;
+    const float4 *s_sm, *s_iv;
+    const uint4* s_pred;
+    const int4* s_na;
+    const int2* s_nz;
+    const uint2* s_code;
+    const uint4 *s_f0, *s_f1;
+    const uint2* code;
+    const uint4* fields;
+    const int4* nbA;
+    const int2* nbB;
+    const float *s_sqrt, *s_inv;
+};
+__device__ __forceinline__ float tiled_update(const TiledConsts& tc, int q, size_t P, const float4* in, float4* out, bool last) {
+    const int l = q - tc.q_begin;
+    if (tc.expanded) return brick_update_x(q, P, l, tc.cap, tc.s_sm, tc.s_iv, tc.s_pred, tc.s_na[l], tc.s_nz[l], in, out, last);
+    int4 na; int2 nz; uint2 c; uint4 f0, f1;
+    if (tc.smem_consts) {
+        na = tc.s_na[l]; nz = tc.s_nz[l]; c = tc.s_code[l]; f0 = tc.s_f0[l]; f1 = tc.s_f1[l];
+    } else {
+        na = __ldg(tc.nbA + q); nz = __ldg(tc.nbB + q); c = __ldg(tc.code + q);
+        f0 = __ldg(tc.fields + q); f1 = __ldg(tc.fields + (size_t)tc.Q + q);
+    }
+    return brick_update(q, P, na, nz, c, f0, f1, in, out, tc.s_sqrt, tc.s_inv, last);
+}
+
+template <int Threads, int MinBlocks, bool Sharded>
 __global__ void __launch_bounds__(Threads, MinBlocks) k_qp_bricks_tiled(const uint2* __restrict__ code, const uint4* __restrict__ fields,
                                                                         const int4* __restrict__ nbA, const int2* __restrict__ nbB,
                                                                         float4* xa, float4* xb, int Q, int iters,
                                                                         unsigned* __restrict__ maxdelta_bits, unsigned* bar, int dbg,
                                                                         const int* __restrict__ blk_nb, unsigned* progress, int cap,
                                                                         const int* __restrict__ plist, const int* __restrict__ pcount,
-                                                                        int expanded, size_t P) {
+                                                                        int expanded, size_t P, TShard sh) {
     __shared__ float s_sqrt[256];
     __shared__ float s_inv[32];
     for (int i = threadIdx.x; i < 256; i += Threads) s_sqrt[i] = c_brick_sqrt[i];
@@ -815,26 +862,31 @@ __global__ void __launch_bounds__(Threads, MinBlocks) k_qp_bricks_tiled(const ui
     constexpr int W = Threads / 32;
     const int rtid = (W - 1 - (int)(threadIdx.x >> 5)) * 32 + (int)(threadIdx.x & 31);
     __shared__ unsigned s_seen;              // number of sweeps whose neighbour flags have all been observed
+    __shared__ int s_nrem[2];                // slots to wait for in the lower / upper neighbour's flag rows
     if (threadIdx.x == 0) s_seen = 0;
     const unsigned s_seen_addr = (unsigned)__cvta_generic_to_shared(&s_seen);
+    int my_lo = -1, my_hi = -1;
+    if (Sharded) {
+        my_lo = sh.slot_lo[blockIdx.x];
+        my_hi = sh.slot_hi[blockIdx.x];
+        if (threadIdx.x < 2) {
+            // the neighbour wrote "number of its pusher blocks + 1" before launching its kernel
+            unsigned v = 1;
+            if (threadIdx.x == 0 ? my_lo >= 0 : my_hi >= 0) {
+                unsigned spins = 0;
+                do {
+                    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(sh.flags_local + 2 * kShardSlots + threadIdx.x) : "memory");
+                    if (++spins == (1u << 27)) __trap();
+                } while (v == 0);
+            }
+            s_nrem[threadIdx.x] = (int)v - 1;
+        }
+    }
     __syncthreads();
     const float4* in = xa;
     float4* out = xb;
-    auto update = [&](int q, bool last) {
-        if (expanded) {
-            const int l = q - q_begin;
-            return brick_update_x(q, P, l, cap, s_sm, s_iv, s_pred, s_na[l], s_nz[l], in, out, last);
-        }
-        int4 na; int2 nz; uint2 c; uint4 f0, f1;
-        if (smem_consts) {
-            const int l = q - q_begin;
-            na = s_na[l]; nz = s_nz[l]; c = s_code[l]; f0 = s_f0[l]; f1 = s_f1[l];
-        } else {
-            na = __ldg(nbA + q); nz = __ldg(nbB + q); c = __ldg(code + q);
-            f0 = __ldg(fields + q); f1 = __ldg(fields + (size_t)Q + q);
-        }
-        return brick_update(q, P, na, nz, c, f0, f1, in, out, s_sqrt, s_inv, last);
-    };
+    const TiledConsts tc{expanded != 0, smem_consts, q_begin, cap, Q, s_sm, s_iv, s_pred, s_na, s_nz, s_code, s_f0, s_f1,
+                         code, fields, nbA, nbB, s_sqrt, s_inv};
     // Sweep it: (1) interior bricks -- they read this block's own bricks only, so they start right after the barrier
     // that ended sweep it-1, while that sweep's flag is still travelling; (2) rim bricks -- they wait until warp 0 has seen
     // "sweep it-1 done" from every neighbour block (which also means the neighbours no longer read the buffer this sweep
@@ -859,25 +911,61 @@ __global__ void __launch_bounds__(Threads, MinBlocks) k_qp_bricks_tiled(const ui
                 asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(watch2) : "memory");
                 if (++spins == (1u << 26)) __trap();
             } while (v < (unsigned)it);
+            if (Sharded) {
+                // the neighbour GPUs' blocks that push into this GPU's halo: one slot each, system scope
+                if (my_lo >= 0)
+                    for (int sl = threadIdx.x; sl < s_nrem[0]; sl += 32) do {
+                        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(sh.flags_local + sl) : "memory");
+                        if (++spins == (1u << 26)) __trap();
+                    } while (v < (unsigned)it);
+                if (my_hi >= 0)
+                    for (int sl = threadIdx.x; sl < s_nrem[1]; sl += 32) do {
+                        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(sh.flags_local + kShardSlots + sl) : "memory");
+                        if (++spins == (1u << 26)) __trap();
+                    } while (v < (unsigned)it);
+            }
             __syncwarp();
             if (threadIdx.x == 0) asm volatile("st.release.cta.shared.u32 [%0], %1;" ::"r"(s_seen_addr), "r"((unsigned)it) : "memory");
         }
-        for (int q = q_int + threadIdx.x; q < q_end; q += Threads) dmax = fmaxf(dmax, update(q, last));
+        for (int q = q_int + threadIdx.x; q < q_end; q += Threads) dmax = fmaxf(dmax, tiled_update(tc, q, P, in, out, last));
         if (it > 0 && flags_on && q_begin + rtid < q_int) {
             unsigned v;
             do {
                 asm volatile("ld.acquire.cta.shared.u32 %0, [%1];" : "=r"(v) : "r"(s_seen_addr) : "memory");
             } while (v < (unsigned)it);
         }
-        for (int q = q_begin + rtid; q < q_int; q += Threads) dmax = fmaxf(dmax, update(q, last));
+        for (int q = q_begin + rtid; q < q_int; q += Threads) {
+            dmax = fmaxf(dmax, tiled_update(tc, q, P, in, out, last));
+            if (Sharded && !last && (my_lo >= 0 || my_hi >= 0)) {
+                // first / last plane of the slab: the same values go into the neighbour's halo slot over NVLink
+                const int2 pid = sh.peer_ids[q];
+                if (pid.x >= 0) {
+                    float4* dst = (it & 1) ? sh.peer_lo[0] : sh.peer_lo[1];       // sweep `it` writes buffer B when it is even
+#pragma unroll
+                    for (int k = 0; k < 4; k++) dst[k * sh.P_lo + pid.x] = out[k * P + q];
+                }
+                if (pid.y >= 0) {
+                    float4* dst = (it & 1) ? sh.peer_hi[0] : sh.peer_hi[1];
+#pragma unroll
+                    for (int k = 0; k < 4; k++) dst[k * sh.P_hi + pid.y] = out[k * P + q];
+                }
+            }
+        }
         if (last) {
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) dmax = fmaxf(dmax, __shfl_xor_sync(0xffffffffu, dmax, o));
             if ((threadIdx.x & 31) == 0) atomicMax(maxdelta_bits, __float_as_uint(dmax));
         } else if (!(dbg & 1)) {
             __syncthreads();        // the block's stores of this sweep are issued; its reads of the neighbours' bricks are done
-            if (flags_on && threadIdx.x == 0)
+            if (flags_on && threadIdx.x == 0) {
+                if (Sharded && (my_lo >= 0 || my_hi >= 0)) {
+                    // one system-scope fence covers the stores into the neighbour GPUs (made cumulative by the barrier)
+                    asm volatile("fence.acq_rel.sys;" ::: "memory");
+                    if (my_lo >= 0) asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(sh.flag_lo_remote + my_lo), "r"((unsigned)(it + 1)) : "memory");
+                    if (my_hi >= 0) asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(sh.flag_hi_remote + my_hi), "r"((unsigned)(it + 1)) : "memory");
+                }
                 asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(mine), "r"((unsigned)(it + 1)) : "memory");
+            }
         }
         const float4* t = in; in = out; out = (float4*)t;
     }
@@ -940,10 +1028,10 @@ int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_
     if (getenv("MRB_QP_BRICK_THREADS")) t_threads = atoi(getenv("MRB_QP_BRICK_THREADS"));
     void* t_kern = nullptr;
     switch (t_threads) {
-        case 256: t_kern = (void*)k_qp_bricks_tiled<256, 2>; break;
-        case 448: t_kern = (void*)k_qp_bricks_tiled<448, 1>; break;
-        case 512: t_kern = (void*)k_qp_bricks_tiled<512, 1>; break;
-        default: t_threads = 480; t_kern = (void*)k_qp_bricks_tiled<480, 1>; break;
+        case 256: t_kern = (void*)k_qp_bricks_tiled<256, 2, false>; break;
+        case 448: t_kern = (void*)k_qp_bricks_tiled<448, 1, false>; break;
+        case 512: t_kern = (void*)k_qp_bricks_tiled<512, 1, false>; break;
+        default: t_threads = 480; t_kern = (void*)k_qp_bricks_tiled<480, 1, false>; break;
     }
     int t_grid = 0, t_fit = 0;
     int* blk_nb = nullptr;
@@ -1032,9 +1120,11 @@ int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_
             if (getenv("MRB_QP_BRICK_NOSMEM") || smem > 96 * 1024 / (size_t)t_fit) { if (!expanded) { cap = 0; smem = 0; } }
             if (smem > 48 * 1024) MRB_CUDA(cudaFuncSetAttribute(t_kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
             int its = iters, QQ = Q;
+            TShard no_shard;
+            memset(&no_shard, 0, sizeof(no_shard));
             void* args[] = {(void*)&code, (void*)&fields, (void*)&nbA, (void*)&nbB, (void*)&xa, (void*)&xb, (void*)&QQ, (void*)&its,
                             (void*)&md, (void*)&bar, (void*)&dbg, (void*)&blk_nb, (void*)&progress, (void*)&cap, (void*)&plist, (void*)&pcount,
-                            (void*)&expanded, (void*)&P};
+                            (void*)&expanded, (void*)&P, (void*)&no_shard};
             MRB_CUDA(cudaEventRecord(ctx->ev[6], ctx->stream));
             MRB_CUDA(cudaLaunchCooperativeKernel(t_kern, dim3(grid), dim3(t_threads), args, smem, ctx->stream));
             MRB_CUDA(cudaEventRecord(ctx->ev[7], ctx->stream));
@@ -1178,7 +1268,6 @@ struct ShardArgs {
     int first_lo, first_hi;   // first block of this rank that owns lo / hi plane bricks (slot = block - first)
     int nrem_lo, nrem_hi;     // boundary blocks of the lower / upper neighbour (slots to wait for)
 };
-static const int kShardSlots = 128;
 
 __device__ __forceinline__ void spin_until(const unsigned* p, unsigned target) {
     unsigned v, spins = 0;
@@ -1271,6 +1360,158 @@ __global__ void k_block_ranges_local(const int4* __restrict__ nbA, const int2* _
         if (n[i] >= qa && n[i] < qb) { int o = brick_owner(n[i] - qa, Ql, G); mn = min(mn, o); mx = max(mx, o); }
     if (mn < b) atomicMin(&lo[b], mn);
     if (mx > b) atomicMax(&hi[b], mx);
+}
+
+}  // namespace mrb
+
+namespace mrb {
+
+// ---- slab-local brick numbering for the sharded tiled kernel -------------------------------------------------------
+// A rank owns the brick planes [X0, X0 + nX).  Its bricks are renumbered like the single-GPU path (x-slab tiles, rim
+// bricks first inside each block's range); the bricks of the planes X0 - 1 and X0 + nX (owned by the neighbour ranks)
+// follow as halo slots in the plan's global (Y,Z) order, which both sides know without talking to each other.
+struct ShardSub {
+    BrickDims bd;
+    int T, X0, nX;
+    __host__ __device__ size_t count() const { return (size_t)((nX + T - 1) / T) * T * bd.by * bd.bz; }
+    __host__ __device__ long long position(size_t i) const {        // global brick-grid position, -1 in the padding
+        const int Z = (int)(i % bd.bz);
+        size_t t = i / bd.bz;
+        const int x = (int)(t % T);
+        t /= T;
+        const int Y = (int)(t % bd.by);
+        const int Xl = (int)(t / bd.by) * T + x;
+        if (Xl >= nX) return -1;
+        return ((long long)(X0 + Xl) * bd.by + Y) * bd.bz + Z;
+    }
+    // index into the local id map, which covers the planes X0 - 1 .. X0 + nX
+    __host__ __device__ size_t map_index(long long p) const { return (size_t)(p - (long long)(X0 - 1) * bd.by * bd.bz); }
+    __host__ __device__ size_t map_size() const { return (size_t)(nX + 2) * bd.by * bd.bz; }
+};
+struct ShardSubPred {
+    const int* gbid;
+    ShardSub sub;
+    __device__ bool operator()(size_t i) const {
+        const long long p = sub.position(i);
+        return p >= 0 && gbid[p] >= 0;
+    }
+};
+__global__ void k_sh_scatter1(const int* __restrict__ tpos, int Qo, ShardSub sub, int* __restrict__ lmap1) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < Qo) lmap1[sub.map_index(sub.position((size_t)tpos[i]))] = i;
+}
+// halo plane X: local id = base + rank of the brick inside its plane in the global numbering
+__global__ void k_sh_halo_ids(const int* __restrict__ gbid, ShardSub sub, int X, int base, int plane_first, int* __restrict__ lmap1,
+                              int* __restrict__ lmap) {
+    const int n = sub.bd.by * sub.bd.bz;
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const long long p = (long long)X * n + i;
+    const int g = gbid[p];
+    if (g < 0) return;
+    const int id = base + (g - plane_first);
+    lmap1[sub.map_index(p)] = id;
+    lmap[sub.map_index(p)] = id;
+}
+__global__ void k_sh_boundary(const int* __restrict__ tpos, int Qo, int G, ShardSub sub, const int* __restrict__ lmap1,
+                              int* __restrict__ isb) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= Qo) return;
+    const BrickDims bd = sub.bd;
+    const long long p = sub.position((size_t)tpos[i]);
+    const int Z = (int)(p % bd.bz);
+    const long long t = p / bd.bz;
+    const int Y = (int)(t % bd.by), X = (int)(t / bd.by);
+    const int own = tiled_owner(i, Qo, G);
+    const long long cx = (long long)bd.by * bd.bz, cy = bd.bz;
+    bool rim = false;
+    auto look = [&](bool ok, long long dp) {
+        if (!ok) return;
+        const int id = lmap1[sub.map_index(p + dp)];
+        if (id >= Qo || (id >= 0 && tiled_owner(id, Qo, G) != own)) rim = true;     // halo slot or another block's brick
+    };
+    look(X >= 1, -cx); look(X <= bd.bx - 2, cx); look(Y >= 1, -cy); look(Y <= bd.by - 2, cy);
+    look(Z >= 1, -1); look(Z <= bd.bz - 2, 1);
+    isb[i] = rim ? 1 : 0;
+}
+__global__ void k_sh_final(const int* __restrict__ tpos, const int* __restrict__ sb, int Qo, int G, ShardSub sub,
+                           const int* __restrict__ gbid, int* __restrict__ lmap, int* __restrict__ gid_of, int* __restrict__ pos_of,
+                           int* __restrict__ blk_nb) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= Qo) return;
+    const int b = tiled_owner(i, Qo, G);
+    const int qb = tiled_begin(b, Qo, G), qe = tiled_begin(b + 1, Qo, G);
+    const int nbc = sb[qe] - sb[qb];
+    const int rank_b = sb[i] - sb[qb];
+    const bool rim = sb[i + 1] != sb[i];
+    const int id = rim ? qb + rank_b : qb + nbc + (i - qb) - rank_b;
+    const long long p = sub.position((size_t)tpos[i]);
+    lmap[sub.map_index(p)] = id;
+    gid_of[id] = gbid[p];
+    pos_of[id] = (int)p;
+    if (i == qb) blk_nb[b] = nbc;
+}
+struct ShardBuild {
+    int Qo, D, Qg, G;             // owned bricks, dummy slot, bricks of the whole plan, blocks
+    int has_lo, has_hi, base_lo, base_hi, first_lo_plane_id, first_hi_plane_id;   // peer slot = base + (global id - first id of the plane)
+};
+__global__ void k_sh_build(ShardBuild sbd, ShardSub sub, size_t P, const int* __restrict__ lmap, const int* __restrict__ gid_of,
+                           const int* __restrict__ pos_of, const uint2* __restrict__ gcode, const uint4* __restrict__ gfields,
+                           const float4* __restrict__ gx0, uint2* __restrict__ code, uint4* __restrict__ fields,
+                           int4* __restrict__ nbA, int2* __restrict__ nbB, float4* __restrict__ xa, int2* __restrict__ peer_ids,
+                           int* __restrict__ blk_has) {
+    int q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= sbd.Qo) return;
+    const BrickDims bd = sub.bd;
+    const int g = gid_of[q];
+    const long long p = pos_of[q];
+    const int Z = (int)(p % bd.bz);
+    const long long t = p / bd.bz;
+    const int Y = (int)(t % bd.by), X = (int)(t / bd.by);
+    code[q] = gcode[g];
+    fields[q] = gfields[g];
+    fields[(size_t)sbd.Qo + q] = gfields[(size_t)sbd.Qg + g];
+    for (int k = 0; k < 4; k++) xa[k * P + q] = gx0[(size_t)k * ((size_t)sbd.Qg + 1) + g];
+    const long long cx = (long long)bd.by * bd.bz, cy = bd.bz;
+    auto nid = [&](bool ok, long long dp) {
+        int id = ok ? lmap[sub.map_index(p + dp)] : -1;
+        return id >= 0 ? id : sbd.D;
+    };
+    nbA[q] = make_int4(nid(X >= 1, -cx), nid(X <= bd.bx - 2, cx), nid(Y >= 1, -cy), nid(Y <= bd.by - 2, cy));
+    nbB[q] = make_int2(nid(Z >= 1, -1), nid(Z <= bd.bz - 2, 1));
+    int2 pid = make_int2(-1, -1);
+    if (sbd.has_lo && X == sub.X0) pid.x = sbd.base_lo + (g - sbd.first_lo_plane_id);
+    if (sbd.has_hi && X == sub.X0 + sub.nX - 1) pid.y = sbd.base_hi + (g - sbd.first_hi_plane_id);
+    peer_ids[q] = pid;
+    const int b = tiled_owner(q, sbd.Qo, sbd.G);
+    if (pid.x >= 0) blk_has[2 * b] = 1;
+    if (pid.y >= 0) blk_has[2 * b + 1] = 1;
+}
+// initial values of the halo slots of plane X
+__global__ void k_sh_halo_x(const int* __restrict__ gbid, ShardSub sub, int X, const int* __restrict__ lmap, int Qg, size_t P,
+                            const float4* __restrict__ gx0, float4* __restrict__ xa) {
+    const int n = sub.bd.by * sub.bd.bz;
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const long long p = (long long)X * n + i;
+    const int g = gbid[p];
+    if (g < 0) return;
+    const int id = lmap[sub.map_index(p)];
+    for (int k = 0; k < 4; k++) xa[k * P + id] = gx0[(size_t)k * ((size_t)Qg + 1) + g];
+}
+__global__ void k_sh_result(const float4* __restrict__ tmp, const int* __restrict__ gid_of, int Qo, int Qg, float4* __restrict__ out) {
+    int q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= Qo) return;
+    const int g = gid_of[q];
+    for (int k = 0; k < 4; k++) out[(size_t)k * ((size_t)Qg + 1) + g] = tmp[(size_t)k * Qo + q];
+}
+__global__ void k_sh_gather_owned(const float4* __restrict__ x, size_t P, int Qo, float4* __restrict__ tmp) {
+    int q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= Qo) return;
+    for (int k = 0; k < 4; k++) tmp[(size_t)k * Qo + q] = x[k * P + q];
+}
+__global__ void k_sh_ctrl(unsigned* p, unsigned v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
 }  // namespace mrb
@@ -1432,6 +1673,182 @@ static int shard_grid(int fit, int sm_count, int Ql, int threads) {
     return grid > need ? need : grid;
 }
 
+// Slab-sharded solve with the tiled kernel (default; MRB_SHARD_KERNEL=xyz selects the older range kernel below).
+// Buffers: 16 * (Q + 9) floats each (the slab-local layout needs a plane stride that is a multiple of 8 bricks);
+// flags: 512 ints, zeroed by the caller before a barrier across the ranks.  On return the owned bricks' values sit in
+// xa (even iters) / xb (odd iters) in the plan's GLOBAL layout (four planes of Q + 1 float4), like the older kernel.
+static int solve_sharded_tiled(mrb_qp_plan* plan, int rank, int world, void* const* xa_ptrs, void* const* xb_ptrs,
+                               void* const* flag_ptrs, const int* cuts, int iters) {
+    mrb_ctx* ctx = plan->ctx;
+    const std::vector<int>& po = plan->plane_off;
+    const BrickDims bd = plan->bd;
+    const int Qg = plan->Q;
+    const int Xa = cuts[rank], Xb = cuts[rank + 1], nX = Xb - Xa;
+    const int Qo = po[Xb] - po[Xa];
+    const bool has_lo = rank > 0, has_hi = rank < world - 1;
+    const int nh_lo = has_lo ? po[Xa] - po[Xa - 1] : 0, nh_hi = has_hi ? po[Xb + 1] - po[Xb] : 0;
+    const int D = Qo + nh_lo + nh_hi;
+    const size_t P = tiled_stride(D);
+    auto layout = [&](int r, int* Qo_r, int* nlo_r, int* nhi_r) {
+        *Qo_r = po[cuts[r + 1]] - po[cuts[r]];
+        *nlo_r = r > 0 ? po[cuts[r]] - po[cuts[r] - 1] : 0;
+        *nhi_r = r < world - 1 ? po[cuts[r + 1] + 1] - po[cuts[r + 1]] : 0;
+    };
+    float4* xa = (float4*)xa_ptrs[rank];
+    float4* xb = (float4*)xb_ptrs[rank];
+    int tile_T = 8;
+    if (getenv("MRB_QP_TILE")) tile_T = atoi(getenv("MRB_QP_TILE"));
+    if (tile_T < 1) tile_T = 1;
+    const int threads = 480;
+    void* kern = world > 1 ? (void*)k_qp_bricks_tiled<480, 1, true> : (void*)k_qp_bricks_tiled<480, 1, false>;
+    int fit = 0;
+    MRB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&fit, kern, threads, 0));
+    if (fit < 1) { set_error("k_qp_bricks_tiled does not fit on an SM"); return MRB_ECUDA; }
+    int grid = fit * ctx->sm_count;
+    const int need = (Qo + threads - 1) / threads;
+    if (grid > need) grid = need;
+    if (grid < 1) grid = 1;
+
+    // ---- slab-local numbering
+    const ShardSub sub{bd, tile_T, Xa, nX};
+    int* tpos = nullptr;
+    int Qc = 0;
+    MRB_TRY(compact(ctx, ShardSubPred{plan->bid, sub}, sub.count(), &tpos, &Qc));
+    if (Qc != Qo) { set_error("mrb_qp_plan_solve_sharded: slab brick count mismatch (%d vs %d)", Qc, Qo); return MRB_ECUDA; }
+    int *lmap1 = nullptr, *lmap = nullptr, *sbuf = nullptr, *gid_of = nullptr, *pos_of = nullptr, *blk_nb = nullptr, *blk_has = nullptr;
+    const size_t msz = sub.map_size();
+    MRB_TRY(arena_alloc(ctx, msz, &lmap1));
+    MRB_TRY(arena_alloc(ctx, msz, &lmap));
+    MRB_TRY(arena_alloc(ctx, (size_t)Qo + 1, &sbuf));
+    MRB_TRY(arena_alloc(ctx, (size_t)Qo, &gid_of));
+    MRB_TRY(arena_alloc(ctx, (size_t)Qo, &pos_of));
+    MRB_TRY(arena_alloc(ctx, (size_t)grid, &blk_nb));
+    MRB_TRY(arena_alloc(ctx, (size_t)grid * 2, &blk_has));
+    MRB_LAUNCH(ctx, k_fill_i32b, grid_for(ctx, msz, 256), 256, 0, lmap1, msz, -1);
+    MRB_LAUNCH(ctx, k_fill_i32b, grid_for(ctx, msz, 256), 256, 0, lmap, msz, -1);
+    MRB_CUDA(cudaMemsetAsync(blk_nb, 0, (size_t)grid * sizeof(int), ctx->stream));
+    MRB_CUDA(cudaMemsetAsync(blk_has, 0, (size_t)grid * 2 * sizeof(int), ctx->stream));
+    const int plane_n = bd.by * bd.bz;
+    MRB_LAUNCH(ctx, k_sh_scatter1, cdiv(Qo, 256), 256, 0, tpos, Qo, sub, lmap1);
+    if (has_lo) MRB_LAUNCH(ctx, k_sh_halo_ids, cdiv(plane_n, 256), 256, 0, plan->bid, sub, Xa - 1, Qo, po[Xa - 1], lmap1, lmap);
+    if (has_hi) MRB_LAUNCH(ctx, k_sh_halo_ids, cdiv(plane_n, 256), 256, 0, plan->bid, sub, Xb, Qo + nh_lo, po[Xb], lmap1, lmap);
+    MRB_LAUNCH(ctx, k_sh_boundary, cdiv(Qo, 256), 256, 0, tpos, Qo, grid, sub, lmap1, sbuf);
+    MRB_TRY(scan_exclusive(ctx, sbuf, sbuf, (size_t)Qo, sbuf + Qo));
+    MRB_LAUNCH(ctx, k_sh_final, cdiv(Qo, 256), 256, 0, tpos, sbuf, Qo, grid, sub, plan->bid, lmap, gid_of, pos_of, blk_nb);
+
+    // ---- slab-local constants, neighbour ids, initial iterate, peer slots
+    uint2* code = nullptr;
+    uint4* fields = nullptr;
+    int4* nbA = nullptr;
+    int2 *nbB = nullptr, *peer_ids = nullptr;
+    MRB_TRY(arena_alloc(ctx, (size_t)Qo, &code));
+    MRB_TRY(arena_alloc(ctx, (size_t)Qo * 2, &fields));
+    MRB_TRY(arena_alloc(ctx, (size_t)Qo, &nbA));
+    MRB_TRY(arena_alloc(ctx, (size_t)Qo, &nbB));
+    MRB_TRY(arena_alloc(ctx, (size_t)Qo, &peer_ids));
+    ShardBuild sbd;
+    memset(&sbd, 0, sizeof(sbd));
+    sbd.Qo = Qo; sbd.D = D; sbd.Qg = Qg; sbd.G = grid;
+    sbd.has_lo = has_lo; sbd.has_hi = has_hi;
+    TShard sh;
+    memset(&sh, 0, sizeof(sh));
+    if (has_lo) {
+        int q, nl, nh;
+        layout(rank - 1, &q, &nl, &nh);
+        sbd.base_lo = q + nl;                       // my first plane is its upper halo
+        sbd.first_lo_plane_id = po[Xa];
+        sh.P_lo = tiled_stride(q + nl + nh);
+        sh.peer_lo[0] = (float4*)xa_ptrs[rank - 1]; sh.peer_lo[1] = (float4*)xb_ptrs[rank - 1];
+        sh.flag_lo_remote = (unsigned*)flag_ptrs[rank - 1] + kShardSlots;       // its "from upper" slots
+    }
+    if (has_hi) {
+        int q, nl, nh;
+        layout(rank + 1, &q, &nl, &nh);
+        sbd.base_hi = q;                            // my last plane is its lower halo
+        sbd.first_hi_plane_id = po[Xb - 1];
+        sh.P_hi = tiled_stride(q + nl + nh);
+        sh.peer_hi[0] = (float4*)xa_ptrs[rank + 1]; sh.peer_hi[1] = (float4*)xb_ptrs[rank + 1];
+        sh.flag_hi_remote = (unsigned*)flag_ptrs[rank + 1];                      // its "from lower" slots
+    }
+    sh.flags_local = (unsigned*)flag_ptrs[rank];
+    // xa: owned + halo values + zero dummy / padding; xb: only the dummy / padding (the neighbours may already be
+    // pushing their first sweep into xb's halo slots)
+    for (int k = 0; k < 4; k++) {
+        MRB_CUDA(cudaMemsetAsync(xa + (size_t)k * P + D, 0, (P - D) * sizeof(float4), ctx->stream));
+        MRB_CUDA(cudaMemsetAsync(xb + (size_t)k * P + D, 0, (P - D) * sizeof(float4), ctx->stream));
+    }
+    MRB_LAUNCH(ctx, k_sh_build, cdiv(Qo, 128), 128, 0, sbd, sub, P, lmap, gid_of, pos_of, plan->code, plan->fields, plan->x0, code, fields,
+               nbA, nbB, xa, peer_ids, blk_has);
+    if (has_lo) MRB_LAUNCH(ctx, k_sh_halo_x, cdiv(plane_n, 256), 256, 0, plan->bid, sub, Xa - 1, lmap, Qg, P, plan->x0, xa);
+    if (has_hi) MRB_LAUNCH(ctx, k_sh_halo_x, cdiv(plane_n, 256), 256, 0, plan->bid, sub, Xb, lmap, Qg, P, plan->x0, xa);
+    // pusher blocks -> slots; tell the neighbours how many slots to wait for
+    std::vector<int> h_has((size_t)grid * 2), h_slot_lo((size_t)grid, -1), h_slot_hi((size_t)grid, -1);
+    MRB_CUDA(cudaMemcpyAsync(h_has.data(), blk_has, h_has.size() * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    MRB_CUDA(cudaStreamSynchronize(ctx->stream));
+    int n_lo = 0, n_hi = 0;
+    for (int b = 0; b < grid; b++) {
+        if (h_has[2 * (size_t)b]) h_slot_lo[b] = n_lo++;
+        if (h_has[2 * (size_t)b + 1]) h_slot_hi[b] = n_hi++;
+    }
+    if (n_lo > kShardSlots || n_hi > kShardSlots) { set_error("mrb_qp_plan_solve_sharded: more than %d boundary blocks per side", kShardSlots); return MRB_EINVAL; }
+    int *slot_lo = nullptr, *slot_hi = nullptr;
+    MRB_TRY(arena_alloc(ctx, (size_t)grid, &slot_lo));
+    MRB_TRY(arena_alloc(ctx, (size_t)grid, &slot_hi));
+    MRB_CUDA(cudaMemcpyAsync(slot_lo, h_slot_lo.data(), (size_t)grid * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+    MRB_CUDA(cudaMemcpyAsync(slot_hi, h_slot_hi.data(), (size_t)grid * sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+    sh.peer_ids = peer_ids; sh.slot_lo = slot_lo; sh.slot_hi = slot_hi;
+    if (has_lo) MRB_LAUNCH(ctx, k_sh_ctrl, 1, 1, 0, (unsigned*)flag_ptrs[rank - 1] + 2 * kShardSlots + 1, (unsigned)n_lo + 1u);
+    if (has_hi) MRB_LAUNCH(ctx, k_sh_ctrl, 1, 1, 0, (unsigned*)flag_ptrs[rank + 1] + 2 * kShardSlots + 0, (unsigned)n_hi + 1u);
+
+    if (iters > 0 && Qo > 0) {
+        unsigned* md = (unsigned*)(ctx->d_mail + 8);
+        unsigned* bar = (unsigned*)ctx->d_bar;
+        MRB_CUDA(cudaMemsetAsync(md, 0, sizeof(unsigned), ctx->stream));
+        MRB_CUDA(cudaMemsetAsync(bar, 0, 64 * sizeof(unsigned), ctx->stream));
+        const int NW = (grid + 31) / 32;
+        unsigned *progress = nullptr, *bitmap = nullptr;
+        int *plist = nullptr, *pcount = nullptr;
+        MRB_TRY(arena_alloc(ctx, (size_t)grid * kProgressStride, &progress));
+        MRB_TRY(arena_alloc(ctx, (size_t)grid * kChunkListCap, &plist));
+        MRB_TRY(arena_alloc(ctx, (size_t)grid, &pcount));
+        MRB_TRY(arena_alloc(ctx, (size_t)grid * NW, &bitmap));
+        int* ovf = ctx->d_mail + 50;
+        MRB_CUDA(cudaMemsetAsync(progress, 0, (size_t)grid * kProgressStride * sizeof(unsigned), ctx->stream));
+        MRB_CUDA(cudaMemsetAsync(bitmap, 0, (size_t)grid * NW * sizeof(unsigned), ctx->stream));
+        MRB_CUDA(cudaMemsetAsync(pcount, 0, (size_t)grid * sizeof(int), ctx->stream));
+        MRB_CUDA(cudaMemsetAsync(ovf, 0, sizeof(int), ctx->stream));
+        MRB_LAUNCH(ctx, k_tiled_bitmap, cdiv(Qo, 256), 256, 0, nbA, nbB, Qo, grid, NW, bitmap);
+        MRB_LAUNCH(ctx, k_chunk_lists, cdiv((size_t)grid * 32, 256), 256, 0, bitmap, grid, NW, plist, pcount, ovf);
+        int overflow = 0;
+        MRB_TRY(read_int(ctx, ovf, &overflow));
+        if (overflow) { set_error("mrb_qp_plan_solve_sharded: a block has more than %d neighbour blocks", kChunkListCap); return MRB_EINVAL; }
+        int cap = (Qo + grid - 1) / grid + 9;
+        int expanded = 1;
+        size_t smem = (size_t)cap * 168;
+        if (getenv("MRB_QP_BRICK_COMPACT") || smem > (size_t)220 * 1024 / (size_t)fit) { expanded = 0; smem = (size_t)cap * 64; }
+        if (!expanded && smem > 96 * 1024 / (size_t)fit) { cap = 0; smem = 0; }
+        if (smem > 48 * 1024) MRB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        int its = iters, QQ = Qo, dbg = 0;
+        size_t PP = P;
+        void* args[] = {(void*)&code, (void*)&fields, (void*)&nbA, (void*)&nbB, (void*)&xa, (void*)&xb, (void*)&QQ, (void*)&its,
+                        (void*)&md, (void*)&bar, (void*)&dbg, (void*)&blk_nb, (void*)&progress, (void*)&cap, (void*)&plist, (void*)&pcount,
+                        (void*)&expanded, (void*)&PP, (void*)&sh};
+        MRB_CUDA(cudaEventRecord(ctx->ev[6], ctx->stream));
+        MRB_CUDA(cudaLaunchCooperativeKernel(kern, dim3(grid), dim3(threads), args, smem, ctx->stream));
+        MRB_CUDA(cudaEventRecord(ctx->ev[7], ctx->stream));
+        ctx->launches++;
+    }
+    // owned values back into the plan's global layout, in the buffer that holds the result
+    float4* res = (iters % 2) ? xb : xa;
+    float4* tmp = nullptr;
+    MRB_TRY(arena_alloc(ctx, (size_t)(Qo > 0 ? Qo : 1) * 4, &tmp));
+    if (Qo > 0) {
+        MRB_LAUNCH(ctx, k_sh_gather_owned, cdiv(Qo, 256), 256, 0, res, P, Qo, tmp);
+        MRB_LAUNCH(ctx, k_sh_result, cdiv(Qo, 256), 256, 0, tmp, gid_of, Qo, Qg, res);
+    }
+    return sync(ctx);
+}
+
 int mrb_qp_plan_solve_sharded(mrb_qp_plan* plan, int rank, int world, void* const* xa_ptrs, void* const* xb_ptrs,
                               void* const* flag_ptrs, const int* plane_cuts, int iters) {
     MRB_REQUIRE(plan && xa_ptrs && xb_ptrs && flag_ptrs && plane_cuts && world >= 1 && rank >= 0 && rank < world && iters >= 0,
@@ -1443,6 +1860,10 @@ int mrb_qp_plan_solve_sharded(mrb_qp_plan* plan, int rank, int world, void* cons
     for (int r = 0; r < world; r++)
         MRB_REQUIRE(plane_cuts[r] < plane_cuts[r + 1] && po[plane_cuts[r]] < po[plane_cuts[r + 1]], "every rank must own at least one brick");
     MRB_REQUIRE(plane_cuts[0] == 0 && plane_cuts[world] == plan->bd.bx, "plane cuts must cover the grid");
+    {
+        const char* ek = getenv("MRB_SHARD_KERNEL");
+        if (!(ek && strcmp(ek, "xyz") == 0)) return solve_sharded_tiled(plan, rank, world, xa_ptrs, xb_ptrs, flag_ptrs, plane_cuts, iters);
+    }
     const int Xa = plane_cuts[rank], Xb = plane_cuts[rank + 1];
     ShardArgs sh;
     memset(&sh, 0, sizeof(sh));

@@ -202,19 +202,19 @@ def solve_fused(ctx, volume, iters=500, band_size=4, timings=None):
     rank = dist.get_rank() if distributed else 0
     plan = Plan(ctx, volume, band_size)
     cuts = balanced_cuts(plan.plane_off, world)
-    nfloat = 16 * (plan.Q + 1)
+    nfloat = 16 * (plan.Q + 9)                       # slab-local layout: plane stride rounded up to 8 bricks
     if distributed:
         import torch.distributed._symmetric_memory as symm_mem
         group = dist.group.WORLD.group_name
         xa = symm_mem.empty(nfloat, dtype=torch.float32, device=plan.device)
         xb = symm_mem.empty(nfloat, dtype=torch.float32, device=plan.device)
-        flags = symm_mem.empty(256, dtype=torch.int32, device=plan.device)
+        flags = symm_mem.empty(512, dtype=torch.int32, device=plan.device)
         ha, hb, hf = (symm_mem.rendezvous(t, group) for t in (xa, xb, flags))
         pa, pb, pf = list(ha.buffer_ptrs), list(hb.buffer_ptrs), list(hf.buffer_ptrs)
     else:
         xa = torch.empty(nfloat, dtype=torch.float32, device=plan.device)
         xb = torch.empty(nfloat, dtype=torch.float32, device=plan.device)
-        flags = torch.empty(256, dtype=torch.int32, device=plan.device)
+        flags = torch.empty(512, dtype=torch.int32, device=plan.device)
         pa, pb, pf = [xa.data_ptr()], [xb.data_ptr()], [flags.data_ptr()]
     flags.zero_()
     plan._check(plan.lib.mrb_qp_plan_init_x(plan.h, C.c_void_p(xa.data_ptr())))
@@ -230,7 +230,7 @@ def solve_fused(ctx, volume, iters=500, band_size=4, timings=None):
         timings["kernel_ms"] = float(plan.lib.mrb_qp_plan_last_kernel_ms(plan.h))
         timings["n_band"] = plan.n_band
         timings["cuts"] = cuts
-    res = (xb if iters % 2 else xa).view(4, plan.Q + 1, 4)
+    res = (xb if iters % 2 else xa)[:16 * (plan.Q + 1)].view(4, plan.Q + 1, 4)
     q0, q1 = int(plan.plane_off[cuts[rank]]), int(plan.plane_off[cuts[rank + 1]])
     x = torch.zeros((4, plan.Q + 1, 4), dtype=torch.float32, device=plan.device)
     x[:, q0:q1, :] = res[:, q0:q1, :]

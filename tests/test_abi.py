@@ -69,7 +69,7 @@ def test_sweep_kernels_keep_the_brick_in_registers():
     seen = 0
     for b in blocks:
         m = re.match(r"'(\S+)'", b)
-        if not m or not any(k in m.group(1) for k in ("k_qp_bricks_tiledILi480", "k_qp_bricks_shardedILi256", "11k_qp_bricksILi256ELi2ELb0")):
+        if not m or not any(k in m.group(1) for k in ("k_qp_bricks_tiledILi480ELi1ELb0", "k_qp_bricks_shardedILi256", "11k_qp_bricksILi256ELi2ELb0")):
             continue
         seen += 1
         assert re.search(r"\b0 bytes stack frame, 0 bytes spill stores, 0 bytes spill loads", b), m.group(1)
