@@ -236,10 +236,11 @@ int  mrb_qp_plan_assemble(mrb_qp_plan* plan, const float* x_dev, float* F_out);
 /* Slab-sharded solve in ONE persistent kernel per GPU: rank `rank` of `world` sweeps the bricks of its brick planes
  * [plane_cuts[rank], plane_cuts[rank+1]) for `iters` sweeps and stores the bricks of its first / last plane
  * directly into the neighbour ranks' iterate buffers over NVLink; per-sweep flags in the neighbours' memory replace
- * a host-driven exchange.  xa_ptrs / xb_ptrs / flag_ptrs: `world` peer-mapped device pointers each (every rank's
- * buffer A, buffer B -- both initialised with mrb_qp_plan_init_x -- and a zeroed block of 256 uint32), e.g. from
- * torch symmetric memory.  All ranks must call this concurrently with the same plan contents.  On return the
- * owned range of buffer A (iters even) or B (iters odd) holds the result. */
+ * a host-driven exchange.  xa_ptrs / xb_ptrs / flag_ptrs: `world` peer-mapped device pointers each, e.g. from torch
+ * symmetric memory: every rank's buffer A and buffer B (16 * (Q + 9) floats each, 128-byte aligned; during the solve
+ * they hold a slab-local layout) and a block of 512 uint32 that the caller zeroes before a barrier across the ranks.
+ * All ranks must call this concurrently with the same plan contents.  On return the owned brick range of buffer A
+ * (iters even) or B (iters odd) holds the result in the plan's layout (four planes of Q + 1 float4). */
 int  mrb_qp_plan_solve_sharded(mrb_qp_plan* plan, int rank, int world, void* const* xa_ptrs, void* const* xb_ptrs,
                                void* const* flag_ptrs, const int* plane_cuts, int iters);
 float mrb_qp_plan_last_kernel_ms(mrb_qp_plan* plan);

@@ -262,3 +262,15 @@ def test_sweep_synchronisation_is_repeatable(ctx, synth):
         for _ in range(12 if n < 256 else 4):
             again = ctx.optimize(v, iters=iters)
             assert np.array_equal(first, again)
+
+
+@pytest.mark.gpu
+def test_pool_of_contexts(ctx, synth):
+    """Pool = several contexts on one GPU, one host thread each: same meshes as one context, input order kept."""
+    import mesh_reconstruction_b200 as mrb
+    vols = [synth.random_object(3000 + i) for i in range(7)]
+    with mrb.Pool(ctx.device if hasattr(ctx, "device") else 0, workers=3) as pool:
+        got = pool.map(vols, iters=60)
+    for v, (verts, faces) in zip(vols, got):
+        v1, f1 = ctx.reconstruct(v, iters=60)
+        assert np.array_equal(faces, f1) and np.array_equal(verts, v1)
