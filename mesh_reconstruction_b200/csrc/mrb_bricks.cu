@@ -693,8 +693,20 @@ struct TiledOrder {
         return ((long long)X * bd.by + Y) * bd.bz + Z;
     }
 };
+// brick activity from the stage-1+2 tile kernel's bitmap: one byte per (brick column, 8 bricks along z)
+struct BrickBitPred {
+    const uint8_t* bits;
+    BrickDims bd;
+    int tz;
+    __device__ bool operator()(size_t p) const {
+        const int Z = (int)(p % bd.bz);
+        const size_t col = p / bd.bz;
+        return (bits[col * tz + (Z >> 3)] >> (Z & 7)) & 1;
+    }
+};
+template <typename Base>
 struct TiledBrickPred {
-    ActiveBrickPred base;
+    Base base;
     TiledOrder ord;
     __device__ bool operator()(size_t i) const {
         const long long p = ord.position(i);
@@ -1009,7 +1021,7 @@ __global__ void __launch_bounds__(256) k_assemble_F_b(const float* __restrict__ 
 // *n_bricks / *closure_err_host are outputs; ev[6], ev[7] bracket the sweep kernel.
 int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_t* flags, const uint8_t* sq, Dims d,
                  int band_size, int iters, int using_features, float* F_dev, float* last_delta_host, int* n_bricks,
-                 int* closure_err_host, int binary_volume) {
+                 int* closure_err_host, int binary_volume, const uint8_t* brick_bits) {
     MRB_TRY(upload_tables(ctx->device));
     BrickDims bd{d.nx, d.ny, d.nz, (d.nx + 1) / 2, (d.ny + 1) / 2, (d.nz + 3) / 4};
     const size_t nb = bd.count();
@@ -1037,7 +1049,9 @@ int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_
     int* blk_nb = nullptr;
     int* tpos = nullptr;
     const TiledOrder ord{bd, tile_T};
-    if (tiled) MRB_TRY(compact(ctx, TiledBrickPred{ActiveBrickPred{flags, bd}, ord}, ord.count(), &tpos, &Q));
+    const BrickBitPred bitpred{brick_bits, bd, (d.nz + 31) / 32};
+    if (tiled && brick_bits) MRB_TRY(compact(ctx, TiledBrickPred<BrickBitPred>{bitpred, ord}, ord.count(), &tpos, &Q));
+    else if (tiled) MRB_TRY(compact(ctx, TiledBrickPred<ActiveBrickPred>{ActiveBrickPred{flags, bd}, ord}, ord.count(), &tpos, &Q));
     else MRB_TRY(compact(ctx, ActiveBrickPred{flags, bd}, nb, &bpos, &Q));
     *n_bricks = Q;
     *closure_err_host = 0;
@@ -1232,7 +1246,8 @@ int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_
 // x-slab of the grid is a contiguous brick range and its one-brick-plane halo is the contiguous range of the
 // neighbouring X plane: ranks that built the plan from the same volume share the numbering and exchange
 // plain sub-ranges of the four SoA planes between sweeps (mesh_reconstruction_b200/slab.py).
-int stage12_binary(mrb_ctx* ctx, const float* vol, Dims d, int W, uint8_t* sq, uint8_t* flags, int* counts, int* binary_out);
+int stage12_binary(mrb_ctx* ctx, const float* vol, Dims d, int W, uint8_t* sq, uint8_t* flags, int* counts, int* binary_out,
+                   uint8_t** brick_bits_out);
 
 __global__ void __launch_bounds__(256) k_qp_bricks_range(const uint2* __restrict__ code, const uint4* __restrict__ fields,
                                                          const int4* __restrict__ nbA, const int2* __restrict__ nbB,
@@ -1574,7 +1589,7 @@ int mrb_qp_plan_create(mrb_ctx* ctx, const float* volume, const int dims[3], int
         int* counts = ctx->d_mail + 32;
         MRB_CUDA(cudaMemsetAsync(counts, 0, 4 * sizeof(int), ctx->stream));
         int binary = 0;
-        MRB_TRY(stage12_binary(ctx, dv, d, band_size, p->sq, p->flags, counts, &binary));
+        MRB_TRY(stage12_binary(ctx, dv, d, band_size, p->sq, p->flags, counts, &binary, nullptr));
         if (!binary) { set_error("mrb_qp_plan_create: the volume must contain only 0 and 1"); return MRB_EINVAL; }
         MRB_CUDA(cudaMemcpyAsync(ctx->h_mail + 32, counts, 4 * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
         p->bd = BrickDims{d.nx, d.ny, d.nz, (d.nx + 1) / 2, (d.ny + 1) / 2, (d.nz + 3) / 4};

@@ -214,7 +214,7 @@ struct TileGeom {
 };
 
 template <int W>
-__global__ void __launch_bounds__(256) k_tile_stage12(const int* __restrict__ tiles, const uint32_t* __restrict__ site, BitDims b,
+__global__ void __launch_bounds__(256) k_tile_stage12(const uint8_t* __restrict__ tile_site, int tile_r, const uint32_t* __restrict__ site, BitDims b,
                                                       uint8_t* __restrict__ sq_out, uint8_t* __restrict__ flags_out,
                                                       int* __restrict__ counts) {
     using G = TileGeom<W>;
@@ -225,7 +225,9 @@ __global__ void __launch_bounds__(256) k_tile_stage12(const int* __restrict__ ti
     uint8_t* s_g2 = s_d1 + G::CX * G::RY * G::RZP;                        // [CX][CY][RZP]
     uint8_t* s_sq = s_g2 + G::CX * G::CY * G::RZP;                        // [CX][CY][CZP]
     uint8_t* s_tg = s_sq + G::CX * G::CY * G::CZP;                        // [UX][UY][UZP]
-    const int tile = tiles[blockIdx.x];
+    // one block per tile of the grid; a tile with no perimeter site within reach is left at the memset values
+    const int tile = blockIdx.x;
+    if (!ActiveTilePred{tile_site, b, tile_r}((size_t)tile)) return;
     const int tz = tile % b.tz, ty = (tile / b.tz) % b.ty, tx = tile / (b.tz * b.ty);
     const int x0 = tx * kTX, y0 = ty * kTY, z0 = tz * 32;
     const int tid = threadIdx.x;
@@ -348,9 +350,9 @@ __global__ void __launch_bounds__(256) k_tile_stage12(const int* __restrict__ ti
 // The squared distance itself is only needed where the final band bit is set (the brick builder reads it there):
 // it is read back from five bit planes built from the exact levels S[u] & ~S[u-1].
 template <int W>
-__global__ void __launch_bounds__(256) k_tile_bits(const int* __restrict__ tiles, const uint32_t* __restrict__ site, BitDims b,
+__global__ void __launch_bounds__(256) k_tile_bits(const uint8_t* __restrict__ tile_site, int tile_r, const uint32_t* __restrict__ site, BitDims b,
                                                    uint8_t* __restrict__ sq_out, uint8_t* __restrict__ flags_out,
-                                                   int* __restrict__ counts) {
+                                                   int* __restrict__ counts, uint8_t* __restrict__ brick_bits) {
     typedef unsigned long long u64;
     constexpr int H = W + 2, W2 = W * W;
     constexpr int RX = kTX + 2 * H, RY = kTY + 2 * H;
@@ -359,7 +361,10 @@ __global__ void __launch_bounds__(256) k_tile_bits(const int* __restrict__ tiles
     __shared__ u64 s_mx[(W + 1) * CX * RY];
     __shared__ u64 s_b0[CX * CY];
     __shared__ u64 s_tg[UX * UY];
-    const int tile = tiles[blockIdx.x];
+    __shared__ unsigned s_colz[kTX * kTY];       // per own column: which of its 8 z-groups of 4 voxels hold a band voxel
+    // one block per tile of the grid; a tile with no perimeter site within reach is left at the memset values
+    const int tile = blockIdx.x;
+    if (!ActiveTilePred{tile_site, b, tile_r}((size_t)tile)) return;
     const int tz = tile % b.tz, ty = (tile / b.tz) % b.ty, tx = tile / (b.tz * b.ty);
     const int x0 = tx * kTX, y0 = ty * kTY, z0 = tz * 32;
     const int tid = threadIdx.x;
@@ -372,6 +377,7 @@ __global__ void __launch_bounds__(256) k_tile_bits(const int* __restrict__ tiles
         if (hi1 > lo1) zint = ((hi1 >= 64 ? ~0ull : ((1ull << hi1) - 1ull)) >> lo1) << lo1;
     }
     const u64 tilebits = 0xffffffffull << H;
+    if (tid < kTX * kTY) s_colz[tid] = 0;
     for (int i = tid; i < RX * RY; i += 256) {
         const int rx = i / RY, ry = i % RY;
         const int x = x0 - H + rx, y = y0 - H + ry;
@@ -459,6 +465,13 @@ __global__ void __launch_bounds__(256) k_tile_bits(const int* __restrict__ tiles
         nt = __popcll(tg);
         if (tg & ~(interior_col ? zint : 0ull)) counts[2] = 1;     // tight voxel on the grid border
         const uint32_t bw = (uint32_t)(band >> H), tw = (uint32_t)(tg >> H);
+        {
+            uint32_t g4 = bw | (bw >> 1) | (bw >> 2) | (bw >> 3);        // bit 4k = any of bits 4k..4k+3
+            uint32_t m8 = 0;
+#pragma unroll
+            for (int k = 0; k < 8; k++) m8 |= ((g4 >> (4 * k)) & 1u) << k;
+            s_colz[(cx - 2) * kTY + (cy - 2)] = m8;
+        }
         const size_t base = ((size_t)gx * b.ny + gy) * b.nz + z0;
         if (bw | tw) {
             if (z0 + 32 <= b.nz && (b.nz & 3) == 0) {
@@ -500,24 +513,38 @@ __global__ void __launch_bounds__(256) k_tile_bits(const int* __restrict__ tiles
             }
         }
     }
+    // bricks (2 x 2 columns x 4 z) with a band voxel: one byte per (brick column, tile z) = its 8 bricks along z
+    if (brick_bits) {
+        __syncthreads();
+        if (tid < (kTX / 2) * (kTY / 2)) {
+            const int bxl = tid / (kTY / 2), byl = tid % (kTY / 2);
+            const unsigned m = s_colz[(2 * bxl) * kTY + 2 * byl] | s_colz[(2 * bxl) * kTY + 2 * byl + 1] |
+                               s_colz[(2 * bxl + 1) * kTY + 2 * byl] | s_colz[(2 * bxl + 1) * kTY + 2 * byl + 1];
+            const int X = tx * (kTX / 2) + bxl, Y = ty * (kTY / 2) + byl;
+            const int bx = (b.nx + 1) / 2, by = (b.ny + 1) / 2;
+            if (X < bx && Y < by && m) brick_bits[((size_t)X * by + Y) * b.tz + tz] = (uint8_t)m;
+        }
+    }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) { nb += __shfl_xor_sync(0xffffffffu, nb, o); nt += __shfl_xor_sync(0xffffffffu, nt, o); }
     if ((threadIdx.x & 31) == 0) { if (nb) atomicAdd(&counts[0], nb); if (nt) atomicAdd(&counts[1], nt); }
 }
 
 template <int W>
-static int launch_tile_stage12(mrb_ctx* ctx, const int* tiles, int ntiles, const uint32_t* site, BitDims b, uint8_t* sq, uint8_t* flags,
-                               int* counts) {
+static int launch_tile_stage12(mrb_ctx* ctx, const uint8_t* tile_site, int tile_r, int ntiles, const uint32_t* site, BitDims b,
+                               uint8_t* sq, uint8_t* flags, int* counts) {
     const size_t smem = TileGeom<W>::bytes;
     if (smem > 48 * 1024) MRB_CUDA(cudaFuncSetAttribute(k_tile_stage12<W>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    MRB_LAUNCH(ctx, k_tile_stage12<W>, ntiles, 256, smem, tiles, site, b, sq, flags, counts);
+    MRB_LAUNCH(ctx, k_tile_stage12<W>, ntiles, 256, smem, tile_site, tile_r, site, b, sq, flags, counts);
     return MRB_OK;
 }
 
 // Stages 1+2 of the fused path for a binary volume.  sq / flags: N^3 bytes each (outputs).  counts: device int[4]
 // (band, tight, border error), zeroed by the caller.  *binary_out = 0 when the volume holds another value than
 // 0 / 1 (nothing usable was produced: the caller runs the general kernels).
-int stage12_binary(mrb_ctx* ctx, const float* vol, Dims d, int W, uint8_t* sq, uint8_t* flags, int* counts, int* binary_out) {
+int stage12_binary(mrb_ctx* ctx, const float* vol, Dims d, int W, uint8_t* sq, uint8_t* flags, int* counts, int* binary_out,
+                   uint8_t** brick_bits_out) {
+    if (brick_bits_out) *brick_bits_out = nullptr;
     BitDims b{d.nx, d.ny, d.nz, (d.nz + 31) / 32, (d.nx + kTX - 1) / kTX, (d.ny + kTY - 1) / kTY, (d.nz + 31) / 32};
     const size_t n = d.count(), nw = b.words(), nt = b.tiles();
     uint32_t *occ = nullptr, *site = nullptr;
@@ -546,33 +573,43 @@ int stage12_binary(mrb_ctx* ctx, const float* vol, Dims d, int W, uint8_t* sq, u
     }
     MRB_CUDA(cudaMemsetAsync(sq, kFar, n, ctx->stream));
     MRB_CUDA(cudaMemsetAsync(flags, 0, n, ctx->stream));
-    int* tiles = nullptr;
-    int ntiles = 0;
     const int r = (W + 1 + kTX - 1) / kTX;          // tiles within band_size + 1 voxels in x / y (z: one 32-voxel tile)
-    MRB_TRY(compact(ctx, ActiveTilePred{tile_site, b, r}, nt, &tiles, &ntiles));    // synchronises the stream
-    *binary_out = ctx->h_mail[52] ? 0 : 1;
-    if (!*binary_out || ntiles == 0) return MRB_OK;
     if (fused) {
+        // one block per tile of the grid, inactive tiles return at once: no tile list, no count to wait for
+        MRB_CUDA(cudaStreamSynchronize(ctx->stream));                   // the "other value than 0 / 1" flag
+        *binary_out = ctx->h_mail[52] ? 0 : 1;
+        if (!*binary_out) return MRB_OK;
+        const int ntl = (int)nt;
         if (W <= 4 && !getenv("MRB_STAGE12_BYTES")) {
+            uint8_t* bits = nullptr;
+            const size_t nbits = (size_t)((d.nx + 1) / 2) * ((d.ny + 1) / 2) * b.tz;
+            MRB_TRY(arena_alloc(ctx, nbits, &bits));
+            MRB_CUDA(cudaMemsetAsync(bits, 0, nbits, ctx->stream));
             switch (W) {
-                case 1: MRB_LAUNCH(ctx, k_tile_bits<1>, ntiles, 256, 0, tiles, site, b, sq, flags, counts); break;
-                case 2: MRB_LAUNCH(ctx, k_tile_bits<2>, ntiles, 256, 0, tiles, site, b, sq, flags, counts); break;
-                case 3: MRB_LAUNCH(ctx, k_tile_bits<3>, ntiles, 256, 0, tiles, site, b, sq, flags, counts); break;
-                default: MRB_LAUNCH(ctx, k_tile_bits<4>, ntiles, 256, 0, tiles, site, b, sq, flags, counts); break;
+                case 1: MRB_LAUNCH(ctx, k_tile_bits<1>, ntl, 256, 0, tile_site, r, site, b, sq, flags, counts, bits); break;
+                case 2: MRB_LAUNCH(ctx, k_tile_bits<2>, ntl, 256, 0, tile_site, r, site, b, sq, flags, counts, bits); break;
+                case 3: MRB_LAUNCH(ctx, k_tile_bits<3>, ntl, 256, 0, tile_site, r, site, b, sq, flags, counts, bits); break;
+                default: MRB_LAUNCH(ctx, k_tile_bits<4>, ntl, 256, 0, tile_site, r, site, b, sq, flags, counts, bits); break;
             }
+            if (brick_bits_out) *brick_bits_out = bits;
             return MRB_OK;
         }
         switch (W) {
-            case 1: return launch_tile_stage12<1>(ctx, tiles, ntiles, site, b, sq, flags, counts);
-            case 2: return launch_tile_stage12<2>(ctx, tiles, ntiles, site, b, sq, flags, counts);
-            case 3: return launch_tile_stage12<3>(ctx, tiles, ntiles, site, b, sq, flags, counts);
-            case 4: return launch_tile_stage12<4>(ctx, tiles, ntiles, site, b, sq, flags, counts);
-            case 5: return launch_tile_stage12<5>(ctx, tiles, ntiles, site, b, sq, flags, counts);
-            case 6: return launch_tile_stage12<6>(ctx, tiles, ntiles, site, b, sq, flags, counts);
-            case 7: return launch_tile_stage12<7>(ctx, tiles, ntiles, site, b, sq, flags, counts);
-            default: return launch_tile_stage12<8>(ctx, tiles, ntiles, site, b, sq, flags, counts);
+            case 1: return launch_tile_stage12<1>(ctx, tile_site, r, ntl, site, b, sq, flags, counts);
+            case 2: return launch_tile_stage12<2>(ctx, tile_site, r, ntl, site, b, sq, flags, counts);
+            case 3: return launch_tile_stage12<3>(ctx, tile_site, r, ntl, site, b, sq, flags, counts);
+            case 4: return launch_tile_stage12<4>(ctx, tile_site, r, ntl, site, b, sq, flags, counts);
+            case 5: return launch_tile_stage12<5>(ctx, tile_site, r, ntl, site, b, sq, flags, counts);
+            case 6: return launch_tile_stage12<6>(ctx, tile_site, r, ntl, site, b, sq, flags, counts);
+            case 7: return launch_tile_stage12<7>(ctx, tile_site, r, ntl, site, b, sq, flags, counts);
+            default: return launch_tile_stage12<8>(ctx, tile_site, r, ntl, site, b, sq, flags, counts);
         }
     }
+    int* tiles = nullptr;
+    int ntiles = 0;
+    MRB_TRY(compact(ctx, ActiveTilePred{tile_site, b, r}, nt, &tiles, &ntiles));    // synchronises the stream
+    *binary_out = ctx->h_mail[52] ? 0 : 1;
+    if (!*binary_out || ntiles == 0) return MRB_OK;
     uint8_t* tight = d1;                              // d1 is dead after pass Y; reuse it for the tight mask
     MRB_LAUNCH(ctx, k_t_edt_x, ntiles, 256, 0, tiles, site, b, W, d1);
     MRB_LAUNCH(ctx, k_t_edt_y, ntiles, 256, 0, tiles, d1, b, W, g2);

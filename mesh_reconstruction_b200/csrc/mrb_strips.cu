@@ -603,10 +603,11 @@ __global__ void __launch_bounds__(256) k_assemble_F_s(const float* __restrict__ 
     }
 }
 
-int stage12_binary(mrb_ctx* ctx, const float* vol, Dims d, int W, uint8_t* sq, uint8_t* flags, int* counts, int* binary_out);
+int stage12_binary(mrb_ctx* ctx, const float* vol, Dims d, int W, uint8_t* sq, uint8_t* flags, int* counts, int* binary_out,
+                   uint8_t** brick_bits_out);
 int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_t* flags, const uint8_t* sq, Dims d,
                  int band_size, int iters, int using_features, float* F_dev, float* last_delta_host, int* n_bricks,
-                 int* closure_err_host, int binary_volume);
+                 int* closure_err_host, int binary_volume, const uint8_t* brick_bits);
 
 // Stages 1-3 on device pointers.  F_dev: N^3 floats.  Records events ev[0..3] (+ ev[6..7] around the sweeps).
 int optimize_strips(mrb_ctx* ctx, const float* vol, const float* fmap, Dims d, int using_features, int band_size,
@@ -627,7 +628,8 @@ int optimize_strips(mrb_ctx* ctx, const float* vol, const float* fmap, Dims d, i
         // binary occupancy grids (the normal case): bit-packed perimeter + tile-sparse passes (mrb_stage12.cu);
         // any other value in the grid -> the general byte-grid kernels below
         int binary = 0;
-        if (!getenv("MRB_STAGE12_GENERAL")) MRB_TRY(stage12_binary(ctx, vol, d, band_size, sq, flags, counts, &binary));
+        uint8_t* brick_bits = nullptr;          // by-product of the bit-sliced tile kernel: which bricks hold a band voxel
+        if (!getenv("MRB_STAGE12_GENERAL")) MRB_TRY(stage12_binary(ctx, vol, d, band_size, sq, flags, counts, &binary, &brick_bits));
         if (binary) {
             MRB_CUDA(cudaEventRecord(ctx->ev[1], ctx->stream));
         } else {
@@ -647,7 +649,7 @@ int optimize_strips(mrb_ctx* ctx, const float* vol, const float* fmap, Dims d, i
             int Q = 0, closure_err = 0;
             float last_delta = 0.0f;
             MRB_TRY(bricks_solve(ctx, vol, fmap, flags, sq, d, band_size, iters, using_features, F_dev,
-                                 stats ? &last_delta : nullptr, &Q, &closure_err, binary));
+                                 stats ? &last_delta : nullptr, &Q, &closure_err, binary, brick_bits));
             MRB_CUDA(cudaEventRecord(ctx->ev[3], ctx->stream));
             MRB_CUDA(cudaStreamSynchronize(ctx->stream));
             if (ctx->h_mail[34] || closure_err) {
