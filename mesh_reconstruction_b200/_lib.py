@@ -8,7 +8,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-SO_PATH = os.path.join(_HERE, "libmrb.so")
+SO_PATH = os.environ.get("MRB_LIBRARY") or os.path.join(_HERE, "libmrb.so")   # MRB_LIBRARY: A/B runs of two builds
 
 c_float_p = C.POINTER(C.c_float)
 c_int_p = C.POINTER(C.c_int)

@@ -26,6 +26,16 @@ static int optimize_dev(mrb_ctx* ctx, const float* vol, const float* fmap, Dims 
     return optimize_strips(ctx, vol, fmap, d, using_features, band_size, iters, F_dev, stats);
 }
 
+// Stages 1-3 when marching cubes follows at `isolevel`: the kernel that writes F also packs its sign bits.
+static int optimize_for_mc(mrb_ctx* ctx, const float* vol, Dims d, int band_size, int iters, float isolevel, float* F_dev,
+                           mrb_qp_stats* stats) {
+    ctx->want_sign_bits = true;
+    ctx->sign_iso = isolevel;
+    const int rc = optimize_strips(ctx, vol, nullptr, d, 0, band_size, iters, F_dev, stats);
+    ctx->want_sign_bits = false;
+    return rc;
+}
+
 }  // namespace mrb
 
 using namespace mrb;
@@ -59,7 +69,7 @@ static int batch_sequential(mrb_ctx* ctx, const float* volumes, Dims d, int ob0,
         MRB_TRY(stage_in(ctx, volumes + (size_t)ob * d.count(), d.count(), &dv));
         float* F = nullptr;
         MRB_TRY(arena_alloc(ctx, d.count(), &F));
-        int rc = optimize_dev(ctx, dv, nullptr, d, 0, o.band_size, o.iters, F, nullptr);
+        int rc = optimize_for_mc(ctx, dv, d, o.band_size, o.iters, o.isolevel, F, nullptr);
         if (rc != MRB_OK) { std::string m = mrb_last_error(); set_error("object %d: %s", ob, m.c_str()); return rc; }
         float* dverts = nullptr;
         int* dfaces = nullptr;
@@ -101,7 +111,7 @@ static int batch_stacked(mrb_ctx* ctx, const float* volumes, Dims d, int ob0, in
     Dims ds{d.nx * n, d.ny, d.nz};
     float* F = nullptr;
     MRB_TRY(arena_alloc(ctx, cnt, &F));
-    if (optimize_dev(ctx, dv, nullptr, ds, 0, o.band_size, o.iters, F, nullptr) != MRB_OK) return MRB_OK;   // sequential run names the object
+    if (optimize_for_mc(ctx, dv, ds, o.band_size, o.iters, o.isolevel, F, nullptr) != MRB_OK) return MRB_OK;   // sequential run names the object
     std::vector<int> foff((size_t)n + 1), voff((size_t)n + 1);
     int seam = 0;
     McStack st{n, d.nx, kstride, foff.data(), voff.data(), &seam};
@@ -195,7 +205,7 @@ int mrb_reconstruct(mrb_ctx* ctx, const float* volume, const int dims[3], const 
     MRB_TRY(stage_in(ctx, volume, d.count(), &dv));
     float* F = nullptr;
     MRB_TRY(arena_alloc(ctx, d.count(), &F));
-    MRB_TRY(optimize_dev(ctx, dv, nullptr, d, 0, o.band_size, o.iters, F, stats));
+    MRB_TRY(optimize_for_mc(ctx, dv, d, o.band_size, o.iters, o.isolevel, F, stats));
     MRB_CUDA(cudaEventRecord(ctx->ev[4], ctx->stream));
     float* verts = nullptr;
     int* faces = nullptr;

@@ -68,6 +68,13 @@ struct mrb_ctx {
     int* d_bar = nullptr;       // 64 ints, device: grid-barrier words (two 128-byte lines)
     char* h_pinned = nullptr;   // grow-only pinned staging buffer for device->host results
     size_t h_pinned_cap = 0;
+    // mrb_reconstruct: the kernel that writes F also packs the "F < isolevel" bits marching cubes starts from
+    // (one read of F less).  want_sign_bits / sign_iso are set by the caller of stages 1-3; sign_bits / sign_F by the
+    // writer; consumed (and cleared) by classify_cells when F and the isolevel match.
+    bool want_sign_bits = false;
+    float sign_iso = 0.0f;
+    const float* sign_F = nullptr;
+    uint32_t* sign_bits = nullptr;
 };
 
 namespace mrb {

@@ -367,12 +367,15 @@ int classify_cells(mrb_ctx* ctx, const float* F, Dims d, float iso, int** cells_
     const size_t nwords = (size_t)d.nx * d.ny * nzw, ncw = (size_t)cd.cx * cd.cy * nzw;
     uint32_t *sb = nullptr, *aw = nullptr;
     int* cnt = nullptr;
-    MRB_TRY(arena_alloc(ctx, nwords, &sb));
+    const bool have_bits = ctx->sign_bits && ctx->sign_F == F && ctx->sign_iso == iso && d.nz % 32 == 0;
+    if (have_bits) sb = ctx->sign_bits;         // packed by the kernel that wrote F (mrb_reconstruct)
+    else MRB_TRY(arena_alloc(ctx, nwords, &sb));
+    ctx->sign_bits = nullptr;
     MRB_TRY(arena_alloc(ctx, ncw, &aw));
     MRB_TRY(arena_alloc(ctx, ncw, &cnt));
     const size_t cap = (size_t)ctx->sm_count * 32;
     size_t want = ((size_t)d.nx * d.ny + 7) / 8;
-    MRB_LAUNCH(ctx, k_sign_bits, (unsigned)(want < cap ? want : cap), 256, 0, F, d, nzw, iso, sb);
+    if (!have_bits) MRB_LAUNCH(ctx, k_sign_bits, (unsigned)(want < cap ? want : cap), 256, 0, F, d, nzw, iso, sb);
     want = (ncw + 255) / 256;
     MRB_LAUNCH(ctx, k_cell_words, (unsigned)(want < cap ? want : cap), 256, 0, sb, cd, nzw, aw, cnt);
     MRB_TRY(scan_exclusive(ctx, cnt, cnt, ncw, ctx->d_mail));
