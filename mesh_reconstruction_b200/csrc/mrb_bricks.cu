@@ -1017,6 +1017,23 @@ __global__ void __launch_bounds__(256) k_assemble_F_b(const float* __restrict__ 
     }
 }
 
+// k_assemble_F_b + the sign bits of F for marching cubes (layout of k_sign_bits: one word per 32 z, nz % 32 == 0):
+// one warp per word, lanes = 32 consecutive z.
+__global__ void __launch_bounds__(256) k_assemble_F_sign(const float* __restrict__ vol, const uint8_t* __restrict__ flags,
+                                                         const int* __restrict__ bid, const float* __restrict__ x, BrickDims bd,
+                                                         size_t P, double scale, float iso, float* __restrict__ F,
+                                                         uint32_t* __restrict__ sb) {
+    const size_t n = (size_t)bd.nx * bd.ny * bd.nz;
+    for (size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x; idx < n; idx += (size_t)gridDim.x * blockDim.x) {
+        float f;
+        if (flags[idx] & 1) f = x[brick_slot(bid, bd, P, idx)];
+        else f = (float)__dmul_rn(__dsub_rn(__dmul_rn(2.0, (double)vol[idx]), 1.0), scale);
+        F[idx] = f;
+        const unsigned m = __ballot_sync(0xffffffffu, f < iso);
+        if ((threadIdx.x & 31) == 0) sb[idx >> 5] = m;
+    }
+}
+
 // Builds the bricks from the stage-2 byte grids, runs `iters` sweeps, applies the feature reset and writes F.
 // *n_bricks / *closure_err_host are outputs; ev[6], ev[7] bracket the sweep kernel.
 int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_t* flags, const uint8_t* sq, Dims d,
@@ -1099,9 +1116,11 @@ int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_
         MRB_CUDA(cudaMemsetAsync(xb, 0, 4 * P * sizeof(float4), ctx->stream));
         MRB_LAUNCH(ctx, k_brick_build, cdiv(Q, 128), 128, 0, vol, sq, flags, bid, bpos, Q, bd, code, fields, xa, nbA, nbB, err, P);
         MRB_CUDA(cudaMemcpyAsync(ctx->h_mail + 24, err, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
-        MRB_CUDA(cudaStreamSynchronize(ctx->stream));
-        *closure_err_host = ctx->h_mail[24];
-        if (*closure_err_host) return MRB_OK;      // caller reports MRB_EBORDER
+        if (!(iters > 0 && tiled)) {
+            MRB_CUDA(cudaStreamSynchronize(ctx->stream));
+            *closure_err_host = ctx->h_mail[24];
+            if (*closure_err_host) return MRB_OK;      // caller reports MRB_EBORDER
+        }
         if (iters > 0 && tiled) {
             unsigned* md = (unsigned*)(ctx->d_mail + 8);
             unsigned* bar = (unsigned*)ctx->d_bar;
@@ -1122,7 +1141,9 @@ int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_
             MRB_LAUNCH(ctx, k_tiled_bitmap, cdiv(Q, 256), 256, 0, nbA, nbB, Q, grid, NW, bitmap);
             MRB_LAUNCH(ctx, k_chunk_lists, cdiv((size_t)grid * 32, 256), 256, 0, bitmap, grid, NW, plist, pcount, ovf);
             int overflow = 0;
-            MRB_TRY(read_int(ctx, ovf, &overflow));
+            MRB_TRY(read_int(ctx, ovf, &overflow));            // one host round trip for this and the closure check above
+            *closure_err_host = ctx->h_mail[24];
+            if (*closure_err_host) return MRB_OK;              // caller reports MRB_EBORDER
             int dbg = getenv("MRB_QP_DEBUG") ? atoi(getenv("MRB_QP_DEBUG")) : 0;
             if (overflow) dbg |= 4;        // a block with more than kChunkListCap neighbour blocks: grid barrier per sweep
             int cap = (Q + grid - 1) / grid + 9;       // block ranges are whole groups of 8 bricks
@@ -1234,6 +1255,17 @@ int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_
         const unsigned g = grid_for(ctx, n, 256);
         MRB_LAUNCH(ctx, k_feat_check_b, g, 256, 0, fmap, flags, n, flag);
         MRB_LAUNCH(ctx, k_feat_apply_b, g, 256, 0, fmap, flags, bid, bd, P, flag, (float*)xres);
+    }
+    ctx->sign_bits = nullptr;
+    if (ctx->want_sign_bits && d.nz % 32 == 0 && n % 256 == 0) {
+        // full warps over whole words: the grid-stride loop keeps every warp on 32 consecutive z of one row
+        uint32_t* sb = nullptr;
+        MRB_TRY(arena_alloc(ctx, n / 32, &sb));
+        MRB_LAUNCH(ctx, k_assemble_F_sign, grid_for(ctx, n, 256), 256, 0, vol, flags, bid, xres, bd, P, (double)band_size + 1.0,
+                   ctx->sign_iso, F_dev, sb);
+        ctx->sign_bits = sb;
+        ctx->sign_F = F_dev;
+        return MRB_OK;
     }
     MRB_LAUNCH(ctx, k_assemble_F_b, grid_for(ctx, n, 256), 256, 0, vol, flags, bid, xres, bd, P, (double)band_size + 1.0,
                F_dev);
