@@ -243,11 +243,16 @@ struct Volume {
 };
 
 // voxelizeData + createGrid + getBinaryVolume (voxelize.cpp:6-51,87-101; grid.cpp:84-121,213-265,314-334)
+// res_factor <= 0: no fillGrid (the m_cubes executable builds its grid without it, m_cubes.cpp:71)
+inline Volume voxelize_leaf(const std::vector<P3>& cloud, float leaf, int res_factor);
 inline Volume voxelize(const std::vector<P3>& cloud, int res_factor) {
     double dt; int cnt;
     nn_stats(cloud, dt, cnt);
     float leaf = 2.0 * (float)dt / (float)cnt;
     std::cout << "Leaf size is " << leaf << std::endl;
+    return voxelize_leaf(cloud, leaf, res_factor);
+}
+inline Volume voxelize_leaf(const std::vector<P3>& cloud, float leaf, int res_factor) {
     std::cout << "PointCloud before filtering: " << cloud.size() << " data points" << std::endl;
     float mn[3] = {1e30f, 1e30f, 1e30f}, mx[3] = {-1e30f, -1e30f, -1e30f};
     for (auto& p : cloud) { mn[0] = std::min(mn[0], p.x); mn[1] = std::min(mn[1], p.y); mn[2] = std::min(mn[2], p.z);
@@ -283,7 +288,7 @@ inline Volume voxelize(const std::vector<P3>& cloud, int res_factor) {
     for (int a = 0; a < 3; a++) { g.shift[a] = lo[a]; g.scale[a] = (hi[a] - lo[a]) / ((float)div[a]); }
     // fillGrid (grid.cpp:213-265): close the first gap of every z column if it is narrower than res_factor+1
     const int max_width = res_factor + 1;
-    for (int i = 0; i < g.dims[0]; i++)
+    for (int i = 0; i < (res_factor > 0 ? g.dims[0] : 0); i++)
         for (int j = 0; j < g.dims[1]; j++) {
             float* col = &conf[((size_t)i * g.dims[1] + j) * g.dims[2]];
             int num_gap = 0;

@@ -86,3 +86,39 @@ def test_cli_feature_detection(cli, synth, tmp_path):
     assert "Using feature detection" in r.stdout and "Feature threshold is 0.8" in r.stdout
     lines = out.read_text().splitlines()
     assert lines[0] == "ply" and int(lines[2].split()[-1]) > 1000 and int(lines[6].split()[-1]) > 2000
+
+
+def test_m_cubes_usage(cli):
+    exe = os.path.join(os.path.dirname(cli), "m_cubes")
+    r = subprocess.run([exe], capture_output=True, text=True)
+    assert r.returncode == 1 and "Usage: <pcd filename> <output filename (.ply)> [optional]leaf_size" in r.stderr
+
+
+@pytest.mark.gpu
+def test_m_cubes_meshes_a_point_cloud(cli, ctx, synth, tmp_path):
+    """m_cubes (m_cubes.cpp:18-81): voxelise a pcd at the given leaf size, marching cubes at isolevel 0.5.  The mesh must be
+    what mrb_mcubes gives on the same occupancy grid (rebuilt here from the same points with numpy)."""
+    exe = os.path.join(os.path.dirname(cli), "m_cubes")
+    rng = np.random.default_rng(5)
+    pts = rng.normal(size=(40000, 3))
+    pts = pts / np.linalg.norm(pts, axis=1, keepdims=True) * rng.uniform(0.0, 1.0, (40000, 1)) ** (1 / 3) * 0.5
+    pts = (np.round(pts * 128) / 128).astype(np.float32)       # k / 128: exact in fp32 and in the "%.7g" text of the pcd
+    pcd = str(tmp_path / "ball.pcd")
+    synth.write_pcd_ascii(pcd, pts)
+    out = tmp_path / "ball.ply"
+    leaf = 0.02
+    r = subprocess.run([exe, pcd, str(out), str(leaf)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "Running Standard Marching Cubes" in r.stdout and "Leaf size is 0.02" in r.stdout
+    lines = out.read_text().splitlines()
+    nv, nf = int(lines[2].split()[-1]), int(lines[6].split()[-1])
+    # the same occupancy grid: one voxel per occupied leaf of size 2 * leaf, pad 6 (voxelize.cpp / grid.cpp)
+    inv = np.float32(1.0) / np.float32(2 * leaf)
+    ijk = np.floor(pts * inv).astype(np.int64)
+    mn = np.floor(pts.min(axis=0) * inv).astype(np.int64)
+    div = np.floor(pts.max(axis=0) * inv).astype(np.int64) - mn + 1
+    vol = np.zeros(tuple(div + 12), np.float32)
+    q = ijk - mn + 6
+    vol[q[:, 0], q[:, 1], q[:, 2]] = 1.0
+    verts, faces = ctx.mcubes(vol, 0.5)
+    assert (nv, nf) == (len(verts), len(faces)) and nf > 1000
