@@ -241,3 +241,11 @@ def solve_fused(ctx, volume, iters=500, band_size=4, timings=None):
     F = plan.assemble(x)
     plan.close()
     return F
+
+
+def reconstruct_fused(ctx, volume, iters=500, band_size=4, isolevel=0.0, timings=None):
+    """The whole path for ONE grid on several GPUs: stages 1-2 on every rank (they are a few per cent of a step),
+    stage 3 slab-sharded in the fused NVLink kernel, then marching cubes + vertex de-dup of the assembled embedding.
+    Every rank returns the same (verts, faces): stage 4 is not sharded, it runs on every rank's copy of F."""
+    F = solve_fused(ctx, volume, iters=iters, band_size=band_size, timings=timings)
+    return ctx.mcubes(F, isolevel)

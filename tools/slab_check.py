@@ -27,6 +27,11 @@ else:
     F = slab.solve_fused(ctx, vt, iters=iters, timings=t)
     t["solve_ms"] = t["kernel_ms"]
 ok = bool(torch.equal(F, F_ref))
+if mode != "nccl" and ok:
+    # the whole path: mesh of the sharded run == mesh of the single-GPU run
+    v1, f1 = ctx.reconstruct(vt, iters=iters)
+    v2, f2 = slab.reconstruct_fused(ctx, vt, iters=iters)
+    ok = bool(np.array_equal(np.asarray(f1), np.asarray(f2)) and np.array_equal(np.asarray(v1), np.asarray(v2)))
 if not ok and dist.get_rank() == 0:
     bad = (F != F_ref).nonzero()
     print("mismatch voxels", len(bad), "x range", int(bad[:, 0].min()), int(bad[:, 0].max()), "cuts", t.get("cuts"),
