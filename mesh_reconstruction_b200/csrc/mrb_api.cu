@@ -31,6 +31,7 @@ static int optimize_for_mc(mrb_ctx* ctx, const float* vol, Dims d, int band_size
                            mrb_qp_stats* stats) {
     ctx->want_sign_bits = true;
     ctx->sign_iso = isolevel;
+    ctx->sign_bits = nullptr;            // never a leftover of an earlier call
     const int rc = optimize_strips(ctx, vol, nullptr, d, 0, band_size, iters, F_dev, stats);
     ctx->want_sign_bits = false;
     return rc;
