@@ -828,7 +828,9 @@ __global__ void __launch_bounds__(Threads, MinBlocks) k_qp_bricks_tiled(const ui
                                                                         int expanded, size_t P, TShard sh) {
     __shared__ float s_sqrt[256];
     __shared__ float s_inv[32];
-    for (int i = threadIdx.x; i < 256; i += Threads) s_sqrt[i] = c_brick_sqrt[i];
+    // Threads is the launch bound; the block may be launched with fewer threads (grids that do not fill the GPU)
+    const int nthreads = (int)blockDim.x;
+    for (int i = threadIdx.x; i < 256; i += nthreads) s_sqrt[i] = c_brick_sqrt[i];
     if (threadIdx.x < 32) s_inv[threadIdx.x] = c_brick_invdg[threadIdx.x];
     const int q_begin = tiled_begin(blockIdx.x, Q, gridDim.x);
     const int q_end = tiled_begin(blockIdx.x + 1, Q, gridDim.x);
@@ -848,7 +850,7 @@ __global__ void __launch_bounds__(Threads, MinBlocks) k_qp_bricks_tiled(const ui
     if (expanded) { s_na = (int4*)(s_pred + cap); s_nz = (int2*)(s_na + cap); }
     const bool smem_consts = cap > 0;
     if (smem_consts)
-        for (int q = q_begin + threadIdx.x; q < q_end; q += Threads) {
+        for (int q = q_begin + threadIdx.x; q < q_end; q += nthreads) {
             const int l = q - q_begin;
             s_na[l] = __ldg(nbA + q); s_nz[l] = __ldg(nbB + q);
             if (expanded) {
@@ -871,7 +873,7 @@ __global__ void __launch_bounds__(Threads, MinBlocks) k_qp_bricks_tiled(const ui
     unsigned* mine = progress + (size_t)blockIdx.x * kProgressStride;
     // Work order inside a sweep: interior bricks first, dealt from warp 0 up; rim bricks second, dealt from the last warp
     // down, so that warp 0 (which publishes and polls) has the least to do.
-    constexpr int W = Threads / 32;
+    const int W = nthreads / 32;
     const int rtid = (W - 1 - (int)(threadIdx.x >> 5)) * 32 + (int)(threadIdx.x & 31);
     __shared__ unsigned s_seen;              // number of sweeps whose neighbour flags have all been observed
     __shared__ int s_nrem[2];                // slots to wait for in the lower / upper neighbour's flag rows
@@ -939,14 +941,14 @@ __global__ void __launch_bounds__(Threads, MinBlocks) k_qp_bricks_tiled(const ui
             __syncwarp();
             if (threadIdx.x == 0) asm volatile("st.release.cta.shared.u32 [%0], %1;" ::"r"(s_seen_addr), "r"((unsigned)it) : "memory");
         }
-        for (int q = q_int + threadIdx.x; q < q_end; q += Threads) dmax = fmaxf(dmax, tiled_update(tc, q, P, in, out, last));
+        for (int q = q_int + threadIdx.x; q < q_end; q += nthreads) dmax = fmaxf(dmax, tiled_update(tc, q, P, in, out, last));
         if (it > 0 && flags_on && q_begin + rtid < q_int) {
             unsigned v;
             do {
                 asm volatile("ld.acquire.cta.shared.u32 %0, [%1];" : "=r"(v) : "r"(s_seen_addr) : "memory");
             } while (v < (unsigned)it);
         }
-        for (int q = q_begin + rtid; q < q_int; q += Threads) {
+        for (int q = q_begin + rtid; q < q_int; q += nthreads) {
             dmax = fmaxf(dmax, tiled_update(tc, q, P, in, out, last));
             if (Sharded && !last && (my_lo >= 0 || my_hi >= 0)) {
                 // first / last plane of the slab: the same values go into the neighbour's halo slot over NVLink
@@ -1081,7 +1083,18 @@ int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_
         if (t_fit < 1) { set_error("k_qp_bricks_tiled does not fit on an SM"); return MRB_ECUDA; }
         t_grid = t_fit * ctx->sm_count;
         const int need = (Q + t_threads - 1) / t_threads;
-        if (t_grid > need) t_grid = need;
+        if (t_grid > need) {
+            // Fewer bricks than threads: spread them over all SMs with smaller blocks instead of leaving SMs idle; a
+            // sweep's length is then set by fewer warps per SM queueing on the L1 data pipe.
+            t_grid = need;
+            if (t_threads == 480 && !getenv("MRB_QP_BRICK_THREADS")) {
+                const int per_sm = (Q + t_fit * ctx->sm_count - 1) / (t_fit * ctx->sm_count);
+                int th = (per_sm + 31) / 32 * 32;
+                const int th_min = getenv("MRB_QP_MIN_THREADS") ? atoi(getenv("MRB_QP_MIN_THREADS")) : 352;   // measured 120^3..200^3
+                if (th < th_min) th = th_min;
+                if (th < t_threads) { t_threads = th; t_grid = std::min(t_fit * ctx->sm_count, (Q + th - 1) / th); }
+            }
+        }
         int *bid1 = nullptr, *sb = nullptr;
         MRB_TRY(arena_alloc(ctx, nb, &bid1));
         MRB_TRY(arena_alloc(ctx, (size_t)Q + 1, &sb));

@@ -644,10 +644,10 @@ int optimize_strips(mrb_ctx* ctx, const float* vol, const float* fmap, Dims d, i
         }
         // Layout of stage 3: 2x2x4 bricks (mrb_bricks.cu) for grids that fill the GPU; small grids are latency-bound (one
         // brick update per thread and sweep is a 2 us dependency chain), there the z-strip kernel with four times as many,
-        // four times lighter threads finishes a sweep sooner (92^3: 1.4 ms against 2.1 ms per 500 sweeps; 172^3: 2.5
-        // against 2.3).  MRB_QP_LAYOUT=strips|bricks overrides.
+        // four times lighter threads finishes a sweep sooner (500 sweeps, strips / bricks: 92^3 1.4 / 2.1 ms, 128^3 1.8 / 2.0,
+        // 144^3 1.9 / 2.0, 160^3 2.4 / 2.0, 172^3 2.5 / 2.0).  MRB_QP_LAYOUT=strips|bricks overrides.
         const char* layout = getenv("MRB_QP_LAYOUT");
-        const bool use_strips = layout ? strcmp(layout, "strips") == 0 : n <= (size_t)112 * 112 * 112;
+        const bool use_strips = layout ? strcmp(layout, "strips") == 0 : n <= (size_t)150 * 150 * 150;
         if (!use_strips) {
             // default: 2x2x4 bricks (mrb_bricks.cu)
             MRB_CUDA(cudaMemcpyAsync(ctx->h_mail + 32, counts, 4 * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));

@@ -4,7 +4,8 @@ import numpy as np, torch
 import mesh_reconstruction_b200 as mrb
 from mesh_reconstruction_b200 import synth
 ctx = mrb.Context(0)
-for n, r in ((52, 17.0), (92, 34.0), (172, 70.0)):
+sizes = [int(a) for a in sys.argv[1:]] or [52, 92, 172]
+for n, r in [(n, n / 2.0 - 16.0) for n in sizes]:
     v = torch.from_numpy(synth.sphere(n, r)).cuda()
     for _ in range(3): ctx.reconstruct(v, return_stats=True)
     torch.cuda.synchronize(); t0 = time.perf_counter()
