@@ -108,6 +108,97 @@ __global__ void __launch_bounds__(32) k_flip_edges(MrbFeatCell* cellsv, const in
     if (lane == 0) *nnew_out = nnew;
 }
 
+// flipEdges in dependency order instead of list order.  A step (feature cell f against its feature neighbours) reads and
+// rewrites only f's cell and those neighbours, so two steps whose cells are more than two cell-steps apart commute.  One
+// warp per feature cell: it takes its place in the list from a ticket counter (so every earlier cell's warp is already
+// running), waits until the earlier feature cells within Manhattan distance 2 are done, runs the reference's step, and
+// marks itself done.  Triangles the reference would append to its global list go into a slot per (cell, neighbour)
+// and are emitted in (cell, neighbour) order afterwards, which is the reference's append order.  The result is the
+// sequential one bit for bit; the critical path is the longest run of adjacent feature cells (an edge of the object),
+// not the number of feature cells (172^3 box + sphere: 14.9 ms -> see profiles).
+static const int kFlipSlot = 8;       // new triangles per (cell, neighbour) step; more -> *err = 3, the caller runs k_flip_edges
+__global__ void k_findex(const int* __restrict__ fcells, int nf, int* __restrict__ findex) {
+    int f = blockIdx.x * blockDim.x + threadIdx.x;
+    if (f < nf) findex[fcells[f]] = f;
+}
+__global__ void __launch_bounds__(128) k_flip_edges_par(MrbFeatCell* cellsv, const int* __restrict__ cells, const int* __restrict__ fcells,
+                                                        int nf, const int* __restrict__ cellmap, const int* __restrict__ findex, Dims d,
+                                                        MrbTri* __restrict__ slots, int* __restrict__ slot_cnt, unsigned* done,
+                                                        unsigned* ticket, int* __restrict__ err) {
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int cx = d.nx - 1, cy = d.ny - 1, cz = d.nz - 1;
+    __shared__ int s_si_all[4][MRB_FEAT_MAX_TRI * MRB_FEAT_MAX_TRI], s_sj_all[4][MRB_FEAT_MAX_TRI * MRB_FEAT_MAX_TRI];
+    __shared__ unsigned char s_flag_all[4][MRB_FEAT_MAX_TRI * MRB_FEAT_MAX_TRI];
+    int* s_si = s_si_all[w];
+    int* s_sj = s_sj_all[w];
+    unsigned char* s_flag = s_flag_all[w];
+    int f = 0;
+    if (lane == 0) f = (int)atomicAdd(ticket, 1u);
+    f = __shfl_sync(0xffffffffu, f, 0);
+    if (f >= nf) return;
+    const int a = fcells[f];
+    MrbFeatCell* c = cellsv + a;
+    const int id = cells[a];
+    const int z = id % cz, y = (id / cz) % cy, x = id / (cz * cy);
+    // earlier feature cells within Manhattan distance 2: 6 at distance 1, 6 straight + 12 diagonal at distance 2
+    if (lane < 24) {
+        int dx = 0, dy = 0, dz = 0;
+        if (lane < 6) { const int ax = lane >> 1, sg = (lane & 1) ? 1 : -1; (ax == 0 ? dx : ax == 1 ? dy : dz) = sg; }
+        else if (lane < 12) { const int ax = (lane - 6) >> 1, sg = (lane & 1) ? 2 : -2; (ax == 0 ? dx : ax == 1 ? dy : dz) = sg; }
+        else {
+            const int k = lane - 12, pair = k >> 2, s1 = (k & 1) ? 1 : -1, s2 = (k & 2) ? 1 : -1;      // pairs: xy, xz, yz
+            if (pair == 0) { dx = s1; dy = s2; } else if (pair == 1) { dx = s1; dz = s2; } else { dy = s1; dz = s2; }
+        }
+        const int xx = x + dx, yy = y + dy, zz = z + dz;
+        if (xx >= 0 && xx < cx && yy >= 0 && yy < cy && zz >= 0 && zz < cz) {
+            const int b = cellmap[(xx * cy + yy) * cz + zz];
+            const int fp = b >= 0 ? findex[b] : -1;
+            if (fp >= 0 && fp < f) {
+                unsigned v, spins = 0;
+                do {
+                    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(done + fp) : "memory");
+                    if (++spins == (1u << 26)) __trap();
+                } while (v == 0);
+            }
+        }
+    }
+    __syncwarp();
+    if (c->feature != 0) {
+        int nb[6], nn = 0;
+        if (x != 0) nb[nn++] = id - cy * cz;
+        if (x != cx - 1) nb[nn++] = id + cy * cz;
+        if (y != 0) nb[nn++] = id - cz;
+        if (y != cy - 1) nb[nn++] = id + cz;
+        if (z != 0) nb[nn++] = id - 1;
+        if (z != cz - 1) nb[nn++] = id + 1;
+        for (int q = 0; q < nn; q++) {
+            const int b = cellmap[nb[q]];
+            if (b < 0) continue;                       // not a surface cell
+            MrbFeatCell* n = cellsv + b;
+            if (n->feature == 0) continue;
+            const int nc = c->ntri, nnb = n->ntri, np = nc * nnb;
+            for (int p = lane; p < np; p += 32) s_flag[p] = (unsigned char)mrb_flip_shared(c, n, p / nnb, p % nnb);
+            __syncwarp();
+            if (lane == 0) {
+                int ns = 0;
+                for (int p = 0; p < np; p++)
+                    if (s_flag[p]) { s_si[ns] = p / nnb; s_sj[ns] = p % nnb; ns++; }
+                if (ns > 0) {
+                    if (2 * ns > kFlipSlot) *err = 3;
+                    else slot_cnt[f * 6 + q] = mrb_flip_apply(c, n, s_si, s_sj, ns, slots + (size_t)(f * 6 + q) * kFlipSlot, kFlipSlot);
+                }
+            }
+            __threadfence();
+            __syncwarp();
+        }
+    }
+    __threadfence();
+    __syncwarp();
+    if (lane == 0) asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(done + f), "r"(1u) : "memory");
+}
+__global__ void k_feat_emit_slots(const MrbTri* __restrict__ slots, const int* __restrict__ off, int nsteps, int first,
+                                  float* __restrict__ soup, unsigned long long* __restrict__ keys, int ny, int nz);
+
 __global__ void k_feat_counts(const MrbFeatCell* __restrict__ c, int n, int* __restrict__ cnt) {
     int a = blockIdx.x * blockDim.x + threadIdx.x;
     if (a < n) cnt[a] = c[a].ntri;
@@ -125,6 +216,13 @@ __device__ __forceinline__ void put_tri(const MrbTri& t, size_t tri, float* __re
         soup[tri * 9 + v * 3 + 0] = t.p[v].x; soup[tri * 9 + v * 3 + 1] = t.p[v].y; soup[tri * 9 + v * 3 + 2] = t.p[v].z;
         keys[tri * 3 + v] = hash_p3(t.p[v], ny, nz);
     }
+}
+__global__ void k_feat_emit_slots(const MrbTri* __restrict__ slots, const int* __restrict__ off, int nsteps, int first,
+                                  float* __restrict__ soup, unsigned long long* __restrict__ keys, int ny, int nz) {
+    int st = blockIdx.x * blockDim.x + threadIdx.x;
+    if (st >= nsteps) return;
+    const int n = off[st + 1] - off[st];
+    for (int i = 0; i < n; i++) put_tri(slots[(size_t)st * kFlipSlot + i], (size_t)first + off[st] + i, soup, keys, ny, nz);
 }
 __global__ void k_feat_emit(const MrbFeatCell* __restrict__ c, int n, const int* __restrict__ off, float* __restrict__ soup,
                             unsigned long long* __restrict__ keys, int ny, int nz) {
@@ -174,21 +272,59 @@ extern "C" int mrb_mcubes_features(mrb_ctx* ctx, const float* F, const float* su
     int* fcells = nullptr;
     int nf = 0;
     MRB_TRY(compact(ctx, FeaturePred{fc}, (size_t)ncells, &fcells, &nf));
-    MrbTri* new_tris = nullptr;
-    const int ncap = nf > 0 ? nf * 24 : 1;                 // every feature cell shares edges with a few neighbours
-    MRB_TRY(arena_alloc(ctx, (size_t)ncap, &new_tris));
-    int* nnew_dev = ctx->d_mail + 55;
-    if (nf > 0) MRB_LAUNCH(ctx, k_flip_edges, 1, 32, 0, fc, cells, fcells, nf, cellmap, d, new_tris, ncap, nnew_dev, err);
-    int* tri_off = nullptr;
+    // flipEdges: dependency-ordered on many warps (k_flip_edges_par); if a step needs more slots than kFlipSlot the cells
+    // are rebuilt and the one-warp kernel in list order runs instead (MRB_FLIP_SEQUENTIAL=1 forces that).
+    MrbTri *new_tris = nullptr, *slots = nullptr;
+    int *slot_off = nullptr, *tri_off = nullptr;
     MRB_TRY(arena_alloc(ctx, (size_t)ncells, &tri_off));
-    MRB_LAUNCH(ctx, k_feat_counts, cdiv(ncells, 256), 256, 0, fc, ncells, tri_off);
-    MRB_TRY(scan_exclusive(ctx, tri_off, tri_off, (size_t)ncells, ctx->d_mail));
-    MRB_CUDA(cudaMemcpyAsync(ctx->h_mail, ctx->d_mail, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
-    MRB_CUDA(cudaMemcpyAsync(ctx->h_mail + 54, err, 2 * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
-    MRB_TRY(sync(ctx));
-    if (ctx->h_mail[54] == 1) { set_error("mrb_mcubes_features: surface map refers to a normal index outside [0, nnormals)"); return MRB_EINVAL; }
-    if (ctx->h_mail[54] == 2) { set_error("mrb_mcubes_features: flipped-triangle buffer overflow"); return MRB_ECAPACITY; }
-    const int ntri_cells = ctx->h_mail[0], nnew = nf > 0 ? ctx->h_mail[55] : 0, ntri = ntri_cells + nnew;
+    int* nnew_dev = ctx->d_mail + 55;
+    bool par = nf > 0 && !getenv("MRB_FLIP_SEQUENTIAL");
+    int ntri_cells = 0, nnew = 0;
+    for (int attempt = 0; attempt < 2; attempt++) {
+        const int nsteps = nf * 6;
+        if (par) {
+            int* findex = nullptr;
+            unsigned* done = nullptr;
+            MRB_TRY(arena_alloc(ctx, (size_t)ncells, &findex));
+            MRB_TRY(arena_alloc(ctx, (size_t)nsteps * kFlipSlot, &slots));
+            MRB_TRY(arena_alloc(ctx, (size_t)nsteps + 1, &slot_off));
+            MRB_TRY(arena_alloc(ctx, (size_t)nf + 1, &done));
+            MRB_LAUNCH(ctx, k_fill_i32f, cdiv(ncells, 256), 256, 0, findex, (size_t)ncells, -1);
+            MRB_LAUNCH(ctx, k_findex, cdiv(nf, 256), 256, 0, fcells, nf, findex);
+            MRB_CUDA(cudaMemsetAsync(slot_off, 0, ((size_t)nsteps + 1) * sizeof(int), ctx->stream));
+            MRB_CUDA(cudaMemsetAsync(done, 0, ((size_t)nf + 1) * sizeof(unsigned), ctx->stream));
+            MRB_LAUNCH(ctx, k_flip_edges_par, cdiv(nf, 4), 128, 0, fc, cells, fcells, nf, cellmap, findex, d, slots, slot_off, done,
+                       done + nf, err);
+            MRB_TRY(scan_exclusive(ctx, slot_off, slot_off, (size_t)nsteps, slot_off + nsteps));
+            MRB_CUDA(cudaMemcpyAsync(ctx->h_mail + 55, slot_off + nsteps, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+        } else {
+            const int ncap = nf > 0 ? nf * 24 : 1;             // every feature cell shares edges with a few neighbours
+            MRB_TRY(arena_alloc(ctx, (size_t)ncap, &new_tris));
+            if (nf > 0) {
+                MRB_LAUNCH(ctx, k_flip_edges, 1, 32, 0, fc, cells, fcells, nf, cellmap, d, new_tris, ncap, nnew_dev, err);
+                MRB_CUDA(cudaMemcpyAsync(ctx->h_mail + 55, nnew_dev, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+            }
+        }
+        MRB_LAUNCH(ctx, k_feat_counts, cdiv(ncells, 256), 256, 0, fc, ncells, tri_off);
+        MRB_TRY(scan_exclusive(ctx, tri_off, tri_off, (size_t)ncells, ctx->d_mail));
+        MRB_CUDA(cudaMemcpyAsync(ctx->h_mail, ctx->d_mail, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+        MRB_CUDA(cudaMemcpyAsync(ctx->h_mail + 54, err, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+        MRB_TRY(sync(ctx));
+        if (ctx->h_mail[54] == 1) { set_error("mrb_mcubes_features: surface map refers to a normal index outside [0, nnormals)"); return MRB_EINVAL; }
+        if (ctx->h_mail[54] == 2) { set_error("mrb_mcubes_features: flipped-triangle buffer overflow"); return MRB_ECAPACITY; }
+        if (ctx->h_mail[54] == 3 && par) {
+            // a step with more than kFlipSlot new triangles: rebuild the cells and flip in list order
+            par = false;
+            MRB_CUDA(cudaMemsetAsync(err, 0, 2 * sizeof(int), ctx->stream));
+            MRB_LAUNCH(ctx, k_feat_polygonise, cdiv(ncells, 64), 64, 0, dF, dm, dn, nnormals, d, cells, ncells, isolevel, feat_thresh,
+                       corner_thresh, fc, err);
+            continue;
+        }
+        ntri_cells = ctx->h_mail[0];
+        nnew = nf > 0 ? ctx->h_mail[55] : 0;
+        break;
+    }
+    const int ntri = ntri_cells + nnew;
     if (ntri == 0) return MRB_OK;
     float* soup = nullptr;
     unsigned long long* keys = nullptr;
@@ -197,7 +333,8 @@ extern "C" int mrb_mcubes_features(mrb_ctx* ctx, const float* F, const float* su
     MRB_TRY(arena_alloc(ctx, (size_t)ntri * 3, &keys));
     MRB_TRY(arena_alloc(ctx, (size_t)ntri * 3, &faces));
     MRB_LAUNCH(ctx, k_feat_emit, cdiv(ncells, 128), 128, 0, fc, ncells, tri_off, soup, keys, d.ny, d.nz);
-    if (nnew > 0) MRB_LAUNCH(ctx, k_feat_emit_new, cdiv(nnew, 128), 128, 0, new_tris, nnew, ntri_cells, soup, keys, d.ny, d.nz);
+    if (nnew > 0 && par) MRB_LAUNCH(ctx, k_feat_emit_slots, cdiv(nf * 6, 128), 128, 0, slots, slot_off, nf * 6, ntri_cells, soup, keys, d.ny, d.nz);
+    else if (nnew > 0) MRB_LAUNCH(ctx, k_feat_emit_new, cdiv(nnew, 128), 128, 0, new_tris, nnew, ntri_cells, soup, keys, d.ny, d.nz);
     float* verts = nullptr;
     int nv = 0;
     MRB_TRY(dev_dedup(ctx, soup, keys, ntri * 3, faces, &verts, &nv));
