@@ -164,20 +164,20 @@ static int reconstruct_with_features(mrb_ctx* ctx, const float* volume, const in
     MRB_CUDA(cudaSetDevice(ctx->device));
     memset(out, 0, sizeof(*out));
     const size_t n = (size_t)dims[0] * dims[1] * dims[2];
-    float *vol = nullptr, *smap = nullptr, *fmap = nullptr, *F = nullptr, *normals = nullptr;
-    int* surf = nullptr;
     int rc = MRB_OK, ns = 0;
-    auto fail = [&](int code) { cudaFree(vol); cudaFree(smap); cudaFree(fmap); cudaFree(F); cudaFree(normals); cudaFree(surf); return code; };
-    if (cudaMalloc((void**)&vol, n * 4) != cudaSuccess || cudaMalloc((void**)&smap, n * 4) != cudaSuccess ||
-        cudaMalloc((void**)&fmap, n * 4) != cudaSuccess || cudaMalloc((void**)&F, n * 4) != cudaSuccess) {
-        cudaGetLastError(); set_error("mrb_reconstruct: cudaMalloc failed"); return fail(MRB_ENOMEM);
-    }
+    auto fail = [&](int code) { return code; };
+    // intermediates live in the context's side buffers (grow-only, reused by the next call), not in the arena
+    char* s0 = nullptr;
+    const size_t gbytes = (n * 4 + 255) / 256 * 256;
+    MRB_TRY(side_reserve(ctx, 0, 4 * gbytes, &s0));
+    float *vol = (float*)s0, *smap = (float*)(s0 + gbytes), *fmap = (float*)(s0 + 2 * gbytes), *F = (float*)(s0 + 3 * gbytes);
     if ((rc = mrb_copy(ctx, vol, volume, n * 4)) != MRB_OK) return fail(rc);
     if ((rc = mrb_get_surface(ctx, vol, dims, nullptr, 0, &ns)) != MRB_OK) return fail(rc);
-    if (cudaMalloc((void**)&surf, (size_t)(ns > 0 ? ns : 1) * 4) != cudaSuccess ||
-        cudaMalloc((void**)&normals, (size_t)(ns > 0 ? ns : 1) * 12) != cudaSuccess) {
-        cudaGetLastError(); set_error("mrb_reconstruct: cudaMalloc failed"); return fail(MRB_ENOMEM);
-    }
+    char* s1 = nullptr;
+    const size_t sbytes = ((size_t)(ns > 0 ? ns : 1) * 4 + 255) / 256 * 256;
+    MRB_TRY(side_reserve(ctx, 1, 4 * sbytes, &s1));
+    int* surf = (int*)s1;
+    float* normals = (float*)(s1 + sbytes);
     if (ns > 0 && (rc = mrb_get_surface(ctx, vol, dims, surf, ns, &ns)) != MRB_OK) return fail(rc);
     if ((rc = mrb_index_map(ctx, dims, surf, ns, smap)) != MRB_OK) return fail(rc);
     if ((rc = mrb_surface_normals(ctx, vol, dims, surf, ns, normals)) != MRB_OK) return fail(rc);

@@ -86,9 +86,24 @@ void Arena::release() {
     blocks.clear();
 }
 
+int side_reserve(mrb_ctx* ctx, int which, size_t bytes, char** out) {
+    if (bytes > ctx->side_cap[which]) {
+        if (ctx->side[which]) cudaFree(ctx->side[which]);
+        ctx->side[which] = nullptr;
+        ctx->side_cap[which] = 0;
+        const size_t cap = bytes + bytes / 8;
+        cudaError_t e = cudaMalloc((void**)&ctx->side[which], cap);
+        if (e != cudaSuccess) { cudaGetLastError(); set_error("side buffer: cudaMalloc(%zu) failed", cap); return MRB_ENOMEM; }
+        ctx->side_cap[which] = cap;
+    }
+    *out = ctx->side[which];
+    return MRB_OK;
+}
+
 int pinned_reserve(mrb_ctx* ctx, size_t bytes, char** out) {
     if (bytes > ctx->h_pinned_cap) {
         if (ctx->h_pinned) cudaFreeHost(ctx->h_pinned);
+    for (int w = 0; w < 2; w++) if (ctx->side[w]) cudaFree(ctx->side[w]);
         ctx->h_pinned = nullptr;
         size_t cap = bytes + (bytes >> 2) + (1u << 20);
         cudaError_t e = cudaMallocHost((void**)&ctx->h_pinned, cap);
@@ -256,6 +271,7 @@ void mrb_ctx_destroy(mrb_ctx* ctx) {
     if (ctx->d_mail) cudaFree(ctx->d_mail);
     if (ctx->d_bar) cudaFree(ctx->d_bar);
     if (ctx->h_pinned) cudaFreeHost(ctx->h_pinned);
+    for (int w = 0; w < 2; w++) if (ctx->side[w]) cudaFree(ctx->side[w]);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }

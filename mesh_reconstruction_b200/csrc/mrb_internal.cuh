@@ -71,6 +71,10 @@ struct mrb_ctx {
     // mrb_reconstruct: the kernel that writes F also packs the "F < isolevel" bits marching cubes starts from
     // (one read of F less).  want_sign_bits / sign_iso are set by the caller of stages 1-3; sign_bits / sign_F by the
     // writer; consumed (and cleared) by classify_cells when F and the isolevel match.
+    // grow-only device buffers outside the arena (which every entry point resets): intermediates of calls that are
+    // composed from several entry points (mrb_reconstruct with features)
+    char* side[2] = {nullptr, nullptr};
+    size_t side_cap[2] = {0, 0};
     bool want_sign_bits = false;
     float sign_iso = 0.0f;
     const float* sign_F = nullptr;
@@ -81,6 +85,8 @@ namespace mrb {
 
 // Pinned host staging of at least `bytes` (grow-only; contents valid until the next reserve).
 int pinned_reserve(mrb_ctx* ctx, size_t bytes, char** out);
+// Device side buffer `which` (0 / 1) of at least `bytes` (grow-only; contents valid until the next reserve of the same buffer).
+int side_reserve(mrb_ctx* ctx, int which, size_t bytes, char** out);
 
 // True when p is device-accessible memory (device or managed).
 bool is_device_ptr(const void* p);
