@@ -12,6 +12,8 @@
 //                 reference's order.  Only feature cells take part (a few thousand on sharp-edged shapes).
 //   4. emit       remaining per-cell triangles in cell order, then the flipped triangles; hashXYZ keys; de-dup.
 #include "mrb_internal.cuh"
+#include <algorithm>
+#include <vector>
 #include "mrb_compact.cuh"
 #include "mc_tables.h"
 #include "../../include/mrb_feature_mc.h"
@@ -116,6 +118,40 @@ __global__ void __launch_bounds__(32) k_flip_edges(MrbFeatCell* cellsv, const in
 // and are emitted in (cell, neighbour) order afterwards, which is the reference's append order.  The result is the
 // sequential one bit for bit; the critical path is the longest run of adjacent feature cells (an edge of the object),
 // not the number of feature cells (172^3 box + sphere: 14.9 ms -> see profiles).
+// mrb_flip_shared without the square roots: sameEdge compares (double)sqrtf(d) < 0.00001 for two squared distances d;
+// sqrtf is monotone, so that is d <= D with D the largest float whose root passes (found once on the host by bisection
+// over the float bit patterns).  Same booleans as mrb_flip_shared, about a third of the instructions.
+static float same_edge_threshold() {
+    uint32_t lo = 0u, hi = 0x7f800000u;            // passes(lo), !passes(hi)
+    while (hi - lo > 1u) {
+        const uint32_t mid = lo + (hi - lo) / 2u;
+        float dd;
+        memcpy(&dd, &mid, 4);
+        if ((double)sqrtf(dd) < 0.00001) lo = mid; else hi = mid;
+    }
+    float out;
+    memcpy(&out, &lo, 4);
+    return out;
+}
+__device__ __forceinline__ float p3_sqdist(const MrbP3& l, const MrbP3& r) {       // the sum inside mrb_p3_dist, same operation order
+    float dd = __fmul_rn(__fsub_rn(r.x, l.x), __fsub_rn(r.x, l.x));
+    dd = __fadd_rn(dd, __fmul_rn(__fsub_rn(r.y, l.y), __fsub_rn(r.y, l.y)));
+    dd = __fadd_rn(dd, __fmul_rn(__fsub_rn(r.z, l.z), __fsub_rn(r.z, l.z)));
+    return dd;
+}
+__device__ __forceinline__ bool flip_shared_fast(const MrbFeatCell* c, const MrbFeatCell* nb, int i, int j, float D) {
+    for (int n = 0; n < 3; n++) {
+        MrbP3 a0 = c->tri[i].p[n], a1 = c->tri[i].p[(n + 1) % 3];
+        if (mrb_p3_less(a1, a0)) { MrbP3 t = a0; a0 = a1; a1 = t; }
+        for (int m = 0; m < 3; m++) {
+            MrbP3 b0 = nb->tri[j].p[m], b1 = nb->tri[j].p[(m + 1) % 3];
+            if (mrb_p3_less(b1, b0)) { MrbP3 t = b0; b0 = b1; b1 = t; }
+            if (p3_sqdist(a0, b0) <= D && p3_sqdist(a1, b1) <= D) return true;
+        }
+    }
+    return false;
+}
+
 static const int kFlipSlot = 8;       // new triangles per (cell, neighbour) step; more -> *err = 3, the caller runs k_flip_edges
 __global__ void k_findex(const int* __restrict__ fcells, int nf, int* __restrict__ findex) {
     int f = blockIdx.x * blockDim.x + threadIdx.x;
@@ -124,23 +160,27 @@ __global__ void k_findex(const int* __restrict__ fcells, int nf, int* __restrict
 __global__ void __launch_bounds__(128) k_flip_edges_par(MrbFeatCell* cellsv, const int* __restrict__ cells, const int* __restrict__ fcells,
                                                         int nf, const int* __restrict__ cellmap, const int* __restrict__ findex, Dims d,
                                                         MrbTri* __restrict__ slots, int* __restrict__ slot_cnt, unsigned* done,
-                                                        unsigned* ticket, int* __restrict__ err) {
+                                                        unsigned* ticket, int* __restrict__ err, int chunk, long long* __restrict__ prof, float sqD) {
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int cx = d.nx - 1, cy = d.ny - 1, cz = d.nz - 1;
     __shared__ int s_si_all[4][MRB_FEAT_MAX_TRI * MRB_FEAT_MAX_TRI], s_sj_all[4][MRB_FEAT_MAX_TRI * MRB_FEAT_MAX_TRI];
-    __shared__ unsigned char s_flag_all[4][MRB_FEAT_MAX_TRI * MRB_FEAT_MAX_TRI];
     int* s_si = s_si_all[w];
     int* s_sj = s_sj_all[w];
-    unsigned char* s_flag = s_flag_all[w];
-    int f = 0;
-    if (lane == 0) f = (int)atomicAdd(ticket, 1u);
-    f = __shfl_sync(0xffffffffu, f, 0);
-    if (f >= nf) return;
+    // a warp takes `chunk` consecutive cells of the list: cells that follow each other in the list are usually adjacent in
+    // z, and inside one warp their order costs no flag hand-over
+    int t = 0;
+    if (lane == 0) t = (int)atomicAdd(ticket, 1u);
+    t = __shfl_sync(0xffffffffu, t, 0);
+    const int f_begin = t * chunk;
+    const long long t_start = prof ? clock64() : 0;
+    for (int f = f_begin; f < min(nf, f_begin + chunk); f++) {
     const int a = fcells[f];
+    unsigned depth = 0;          // done[f] = 1 + the longest chain of earlier steps this one waited for (a statistic, and the flag)
     MrbFeatCell* c = cellsv + a;
     const int id = cells[a];
     const int z = id % cz, y = (id / cz) % cy, x = id / (cz * cy);
     // earlier feature cells within Manhattan distance 2: 6 at distance 1, 6 straight + 12 diagonal at distance 2
+    int fp = -1;                 // the earlier feature cell this lane has to wait for
     if (lane < 24) {
         int dx = 0, dy = 0, dz = 0;
         if (lane < 6) { const int ax = lane >> 1, sg = (lane & 1) ? 1 : -1; (ax == 0 ? dx : ax == 1 ? dy : dz) = sg; }
@@ -152,17 +192,39 @@ __global__ void __launch_bounds__(128) k_flip_edges_par(MrbFeatCell* cellsv, con
         const int xx = x + dx, yy = y + dy, zz = z + dz;
         if (xx >= 0 && xx < cx && yy >= 0 && yy < cy && zz >= 0 && zz < cz) {
             const int b = cellmap[(xx * cy + yy) * cz + zz];
-            const int fp = b >= 0 ? findex[b] : -1;
-            if (fp >= 0 && fp < f) {
-                unsigned v, spins = 0;
-                do {
-                    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(done + fp) : "memory");
-                    if (++spins == (1u << 26)) __trap();
-                } while (v == 0);
-            }
+            const int fq = b >= 0 ? findex[b] : -1;
+            if (fq >= 0 && fq < f_begin) fp = fq;          // earlier cells of this warp's own chunk are done by construction
         }
     }
+    // Poll the latest predecessor first (the others have usually finished by then), with relaxed loads and a short sleep:
+    // 1800 warps polling 24 flags each with acquire loads slow every other warp's L2 round trip down several times.
+    int fmax = fp;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) fmax = max(fmax, __shfl_xor_sync(0xffffffffu, fmax, o));
+    for (int pass = 0; pass < 2; pass++) {
+        if (fp >= 0 && (pass == 1 || fp == fmax)) {
+            unsigned v, spins = 0;
+            for (;;) {
+                asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(done + fp) : "memory");
+                if (v != 0) break;
+                __nanosleep(200);
+                if (++spins == (1u << 24)) __trap();
+            }
+            depth = max(depth, v);
+        }
+        __syncwarp();
+    }
+    asm volatile("fence.acq_rel.gpu;" ::: "memory");        // the flags were read relaxed: order the cell reads after them
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) depth = max(depth, __shfl_xor_sync(0xffffffffu, depth, o));
     __syncwarp();
+    const long long t_waited = prof ? clock64() : 0;
+    // The cell and its (up to six) feature neighbours are fetched into shared memory in ONE round of loads, worked on
+    // there, and the changed ones written back: the step itself is a chain of dependent accesses by one lane, far too
+    // slow against L2, and fetching the neighbours one after the other would pay the L2 latency six times.
+    __shared__ MrbFeatCell s_cell[4][7];
+    MrbFeatCell* sc = &s_cell[w][0];
+    constexpr int kWords = (int)(sizeof(MrbFeatCell) / 4);
     if (c->feature != 0) {
         int nb[6], nn = 0;
         if (x != 0) nb[nn++] = id - cy * cz;
@@ -171,30 +233,79 @@ __global__ void __launch_bounds__(128) k_flip_edges_par(MrbFeatCell* cellsv, con
         if (y != cy - 1) nb[nn++] = id + cz;
         if (z != 0) nb[nn++] = id - 1;
         if (z != cz - 1) nb[nn++] = id + 1;
-        for (int q = 0; q < nn; q++) {
-            const int b = cellmap[nb[q]];
-            if (b < 0) continue;                       // not a surface cell
-            MrbFeatCell* n = cellsv + b;
-            if (n->feature == 0) continue;
-            const int nc = c->ntri, nnb = n->ntri, np = nc * nnb;
-            for (int p = lane; p < np; p += 32) s_flag[p] = (unsigned char)mrb_flip_shared(c, n, p / nnb, p % nnb);
-            __syncwarp();
-            if (lane == 0) {
-                int ns = 0;
-                for (int p = 0; p < np; p++)
-                    if (s_flag[p]) { s_si[ns] = p / nnb; s_sj[ns] = p % nnb; ns++; }
-                if (ns > 0) {
-                    if (2 * ns > kFlipSlot) *err = 3;
-                    else slot_cnt[f * 6 + q] = mrb_flip_apply(c, n, s_si, s_sj, ns, slots + (size_t)(f * 6 + q) * kFlipSlot, kFlipSlot);
-                }
-            }
-            __threadfence();
-            __syncwarp();
+        // lane q looks up neighbour q (two dependent loads), the slots are then shared by shuffles
+        int myb = -1;
+        if (lane < nn) {
+            const int b = cellmap[nb[lane]];
+            if (b >= 0 && cellsv[b].feature != 0) myb = b;           // a surface cell that is a feature cell
         }
+        MrbFeatCell* gsrc[7];
+        gsrc[0] = c;
+#pragma unroll
+        for (int q = 0; q < 6; q++) {
+            const int b = __shfl_sync(0xffffffffu, myb, q);
+            gsrc[q + 1] = b >= 0 ? cellsv + b : nullptr;
+        }
+        // all loads first (independent, one L2 round trip), then the shared-memory stores: interleaved, every generic load
+        // would have to wait for the store before it
+        constexpr int kPer = (kWords + 31) / 32;
+        uint32_t regs[7][kPer];
+#pragma unroll
+        for (int k2 = 0; k2 < 7; k2++)
+#pragma unroll
+            for (int i = 0; i < kPer; i++) {
+                const int wi = lane + 32 * i;
+                regs[k2][i] = (gsrc[k2] && wi < kWords) ? __ldcg((const uint32_t*)gsrc[k2] + wi) : 0u;
+            }
+#pragma unroll
+        for (int k2 = 0; k2 < 7; k2++)
+#pragma unroll
+            for (int i = 0; i < kPer; i++) {
+                const int wi = lane + 32 * i;
+                if (gsrc[k2] && wi < kWords) ((uint32_t*)&s_cell[w][k2])[wi] = regs[k2][i];
+            }
+        __syncwarp();
+        const long long t_loaded = prof ? clock64() : 0;
+        if (prof && lane == 0) prof[4 * f + 1] = t_loaded - t_waited;
+        unsigned dirty = 0;
+#pragma unroll
+        for (int q = 0; q < 6; q++) {
+            if (!gsrc[q + 1]) continue;
+            MrbFeatCell* sn = &s_cell[w][q + 1];
+            const int nc = sc->ntri, nnb = sn->ntri, np = nc * nnb;
+            int ns = 0;                                 // (i, j) pairs that share an edge, in (i, j) order: lane 0 collects them
+            for (int base = 0; base < np; base += 32) {
+                const int p = base + lane;
+                const bool fl = p < np && flip_shared_fast(sc, sn, p / nnb, p % nnb, sqD);
+                unsigned m = __ballot_sync(0xffffffffu, fl);
+                if (lane == 0)
+                    while (m) {
+                        const int pp = base + __ffs(m) - 1;
+                        m &= m - 1;
+                        s_si[ns] = pp / nnb; s_sj[ns] = pp % nnb; ns++;
+                    }
+            }
+            if (lane == 0 && ns > 0) {
+                if (2 * ns > kFlipSlot) *err = 3;
+                else slot_cnt[f * 6 + q] = mrb_flip_apply(sc, sn, s_si, s_sj, ns, slots + (size_t)(f * 6 + q) * kFlipSlot, kFlipSlot);
+            }
+            ns = __shfl_sync(0xffffffffu, ns, 0);       // (also orders lane 0's shared-memory writes before the next reads)
+            if (ns > 0) dirty |= 1u | (2u << q);
+        }
+#pragma unroll
+        for (int k2 = 0; k2 < 7; k2++)
+            if (gsrc[k2] && ((dirty >> k2) & 1u)) {
+                const uint32_t* s32 = (const uint32_t*)&s_cell[w][k2];
+                uint32_t* d32 = (uint32_t*)gsrc[k2];
+                for (int i = lane; i < kWords; i += 32) d32[i] = s32[i];
+            }
     }
-    __threadfence();
     __syncwarp();
-    if (lane == 0) asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(done + f), "r"(1u) : "memory");
+    if (prof && lane == 0) { prof[4 * f + 0] = t_waited - t_start; prof[4 * f + 2] = clock64() - t_waited; }
+    // one release per cell: it orders every lane's writes of this step (made cumulative by the __syncwarp) before the flag
+    if (lane == 0) asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(done + f), "r"(depth + 1u) : "memory");
+    if (prof && lane == 0) prof[4 * f + 3] = clock64() - t_start;
+    }
 }
 __global__ void k_feat_emit_slots(const MrbTri* __restrict__ slots, const int* __restrict__ off, int nsteps, int first,
                                   float* __restrict__ soup, unsigned long long* __restrict__ keys, int ny, int nz);
@@ -293,8 +404,28 @@ extern "C" int mrb_mcubes_features(mrb_ctx* ctx, const float* F, const float* su
             MRB_LAUNCH(ctx, k_findex, cdiv(nf, 256), 256, 0, fcells, nf, findex);
             MRB_CUDA(cudaMemsetAsync(slot_off, 0, ((size_t)nsteps + 1) * sizeof(int), ctx->stream));
             MRB_CUDA(cudaMemsetAsync(done, 0, ((size_t)nf + 1) * sizeof(unsigned), ctx->stream));
-            MRB_LAUNCH(ctx, k_flip_edges_par, cdiv(nf, 4), 128, 0, fc, cells, fcells, nf, cellmap, findex, d, slots, slot_off, done,
-                       done + nf, err);
+            const int chunk = getenv("MRB_FLIP_CHUNK") ? std::max(1, atoi(getenv("MRB_FLIP_CHUNK"))) : 1;
+            long long* prof = nullptr;
+            if (getenv("MRB_FLIP_STATS")) { MRB_TRY(arena_alloc(ctx, (size_t)nf * 4, &prof)); MRB_CUDA(cudaMemsetAsync(prof, 0, (size_t)nf * 32, ctx->stream)); }
+            MRB_LAUNCH(ctx, k_flip_edges_par, cdiv(cdiv(nf, chunk), 4), 128, 0, fc, cells, fcells, nf, cellmap, findex, d, slots, slot_off, done,
+                       done + nf, err, chunk, prof, same_edge_threshold());
+            if (prof) {
+                std::vector<long long> hp((size_t)nf * 4);
+                MRB_CUDA(cudaMemcpyAsync(hp.data(), prof, hp.size() * 8, cudaMemcpyDeviceToHost, ctx->stream));
+                MRB_CUDA(cudaStreamSynchronize(ctx->stream));
+                double sum[4] = {0, 0, 0, 0}; long long mx[4] = {0, 0, 0, 0};
+                for (int i = 0; i < nf; i++) for (int j = 0; j < 4; j++) { sum[j] += (double)hp[(size_t)i * 4 + j]; mx[j] = std::max(mx[j], hp[(size_t)i * 4 + j]); }
+                fprintf(stderr, "[mrb] flip cycles avg (max): wait %.0f (%lld), load %.0f (%lld), step %.0f (%lld), total %.0f (%lld)\n",
+                        sum[0] / nf, mx[0], sum[1] / nf, mx[1], sum[2] / nf, mx[2], sum[3] / nf, mx[3]);
+            }
+            if (getenv("MRB_FLIP_STATS")) {
+                std::vector<unsigned> h((size_t)nf);
+                MRB_CUDA(cudaMemcpyAsync(h.data(), done, (size_t)nf * sizeof(unsigned), cudaMemcpyDeviceToHost, ctx->stream));
+                MRB_CUDA(cudaStreamSynchronize(ctx->stream));
+                unsigned mx = 0;
+                for (unsigned v : h) mx = std::max(mx, v);
+                fprintf(stderr, "[mrb] flipEdges: %d feature cells of %d surface cells, longest dependency chain %u\n", nf, ncells, mx);
+            }
             MRB_TRY(scan_exclusive(ctx, slot_off, slot_off, (size_t)nsteps, slot_off + nsteps));
             MRB_CUDA(cudaMemcpyAsync(ctx->h_mail + 55, slot_off + nsteps, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
         } else {
