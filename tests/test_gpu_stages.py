@@ -141,8 +141,12 @@ def test_optimize_sync_and_layout_variants(ctx, O, synth, monkeypatch):
     """Every selectable stage-3 variant (tuning knobs) must give the same bits as the default."""
     v = synth.torus(56, 14.0, 5.0)
     F_ref = O.optimize(v, iters=60)
-    for env in ({"MRB_QP_SYNC": "flow"}, {"MRB_QP_LAYOUT": "strips"}, {"MRB_QP_BRICK_THREADS": "512"},
-                {"MRB_QP_BRICK_THREADS": "128"}, {"MRB_QP_BRICK_NOSMEM": "1"},
+    B = {"MRB_QP_LAYOUT": "bricks"}          # grids this small default to the strip kernel
+    X = dict(B, MRB_QP_ORDER="xyz")          # the older (X,Y,Z)-ordered brick kernel
+    for env in (B, dict(B, MRB_QP_BRICK_THREADS="512"), dict(B, MRB_QP_BRICK_THREADS="256"), dict(B, MRB_QP_BRICK_COMPACT="1"),
+                dict(B, MRB_QP_BRICK_NOSMEM="1"), dict(B, MRB_QP_TILE="3"), dict(B, MRB_QP_MIN_THREADS="128"),
+                X, dict(X, MRB_QP_SYNC="flow"), dict(X, MRB_QP_BRICK_THREADS="512"), dict(X, MRB_QP_BRICK_THREADS="128"),
+                dict(X, MRB_QP_BRICK_NOSMEM="1"), {"MRB_QP_LAYOUT": "strips"},
                 {"MRB_QP_LAYOUT": "strips", "MRB_QP_VARIANT": "0:1024"}, {"MRB_QP_LAYOUT": "strips", "MRB_QP_VARIANT": "2:512"}):
         for k, val in env.items():
             monkeypatch.setenv(k, val)
@@ -241,10 +245,12 @@ def test_device_pointers(ctx, O, synth):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("layout", ["bricks", "strips"])
 @pytest.mark.parametrize("band_size", [1, 2, 3, 4, 5, 6, 7, 8, 9])
-def test_fused_stages_every_band_size(ctx, O, synth, band_size):
+def test_fused_stages_every_band_size(ctx, O, synth, band_size, layout, monkeypatch):
     """The fused stage-1+2 tile kernels are instantiated per band_size (bit-sliced <= 4, byte arrays <= 8, global
     passes above): each against the oracle, on a grid whose dims are not multiples of the 8 x 8 x 32 tile."""
+    monkeypatch.setenv("MRB_QP_LAYOUT", layout)
     v = synth.random_spheres((70, 61, 75), 4, 9, 14, seed=100 + band_size, pad=band_size + 3)
     F_ref, info = O.optimize(v, band_size=band_size, iters=12, brute_edt=False, return_info=True)
     F, st = ctx.optimize(v, band_size=band_size, iters=12, return_stats=True)
@@ -256,6 +262,15 @@ def test_fused_stages_every_band_size(ctx, O, synth, band_size):
 def test_sweep_synchronisation_is_repeatable(ctx, synth):
     """The persistent sweep kernel synchronises blocks with flags in global memory: a lost wait would show up as a
     run-to-run difference.  Many short runs (different grid sizes -> different block / neighbour-list shapes)."""
+    import os
+    os.environ["MRB_QP_LAYOUT"] = "bricks"        # the flag-synchronised kernel, also on the small grids
+    try:
+        _repeat(ctx, synth)
+    finally:
+        del os.environ["MRB_QP_LAYOUT"]
+
+
+def _repeat(ctx, synth):
     for n, r, iters in ((96, 30.0, 40), (160, 60.0, 30), (256, 110.0, 12)):
         v = synth.sphere(n, r)
         first = ctx.optimize(v, iters=iters)
