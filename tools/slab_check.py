@@ -31,7 +31,8 @@ if mode != "nccl" and ok:
     # the whole path: mesh of the sharded run == mesh of the single-GPU run
     v1, f1 = ctx.reconstruct(vt, iters=iters)
     v2, f2 = slab.reconstruct_fused(ctx, vt, iters=iters)
-    ok = bool(np.array_equal(np.asarray(f1), np.asarray(f2)) and np.array_equal(np.asarray(v1), np.asarray(v2)))
+    host = lambda a: a.cpu().numpy() if torch.is_tensor(a) else np.asarray(a)
+    ok = bool(np.array_equal(host(f1), host(f2)) and np.array_equal(host(v1), host(v2)))
 if not ok and dist.get_rank() == 0:
     bad = (F != F_ref).nonzero()
     print("mismatch voxels", len(bad), "x range", int(bad[:, 0].min()), int(bad[:, 0].max()), "cuts", t.get("cuts"),
