@@ -489,8 +489,11 @@ __global__ void __launch_bounds__(256) k_tile_bits(const uint8_t* __restrict__ t
             }
         }
         if (bw) {
-            // squared distance of the band voxels from five bit planes of the exact levels
-            u64 pl[5] = {0, 0, 0, 0, 0};
+            // squared distance of the band voxels from the bit planes of the exact levels (values up to W^2)
+            constexpr int NPL = W2 < 32 ? 5 : 7;
+            u64 pl[NPL];
+#pragma unroll
+            for (int k = 0; k < NPL; k++) pl[k] = 0;
             u64 prev = 0;
 #pragma unroll
             for (int u = 0; u <= W2; u++) {
@@ -498,7 +501,7 @@ __global__ void __launch_bounds__(256) k_tile_bits(const uint8_t* __restrict__ t
                 const u64 exact = S & ~prev;
                 prev = S;
 #pragma unroll
-                for (int k = 0; k < 5; k++)
+                for (int k = 0; k < NPL; k++)
                     if ((u >> k) & 1) pl[k] |= exact;
             }
             uint32_t m = bw;
@@ -506,9 +509,9 @@ __global__ void __launch_bounds__(256) k_tile_bits(const uint8_t* __restrict__ t
                 const int k = __ffs(m) - 1;
                 m &= m - 1;
                 const int i = k + H;
-                const uint32_t v = (uint32_t)((pl[0] >> i) & 1ull) | ((uint32_t)((pl[1] >> i) & 1ull) << 1) |
-                                   ((uint32_t)((pl[2] >> i) & 1ull) << 2) | ((uint32_t)((pl[3] >> i) & 1ull) << 3) |
-                                   ((uint32_t)((pl[4] >> i) & 1ull) << 4);
+                uint32_t v = 0;
+#pragma unroll
+                for (int q = 0; q < NPL; q++) v |= (uint32_t)((pl[q] >> i) & 1ull) << q;
                 sq_out[base + k] = (uint8_t)v;
             }
         }
@@ -580,7 +583,8 @@ int stage12_binary(mrb_ctx* ctx, const float* vol, Dims d, int W, uint8_t* sq, u
         *binary_out = ctx->h_mail[52] ? 0 : 1;
         if (!*binary_out) return MRB_OK;
         const int ntl = (int)nt;
-        if (W <= 4 && !getenv("MRB_STAGE12_BYTES")) {
+        const int bits_max = getenv("MRB_STAGE12_BITS_MAX") ? atoi(getenv("MRB_STAGE12_BITS_MAX")) : 8;
+        if (W <= bits_max && !getenv("MRB_STAGE12_BYTES")) {
             uint8_t* bits = nullptr;
             const size_t nbits = (size_t)((d.nx + 1) / 2) * ((d.ny + 1) / 2) * b.tz;
             MRB_TRY(arena_alloc(ctx, nbits, &bits));
@@ -589,7 +593,11 @@ int stage12_binary(mrb_ctx* ctx, const float* vol, Dims d, int W, uint8_t* sq, u
                 case 1: MRB_LAUNCH(ctx, k_tile_bits<1>, ntl, 256, 0, tile_site, r, site, b, sq, flags, counts, bits); break;
                 case 2: MRB_LAUNCH(ctx, k_tile_bits<2>, ntl, 256, 0, tile_site, r, site, b, sq, flags, counts, bits); break;
                 case 3: MRB_LAUNCH(ctx, k_tile_bits<3>, ntl, 256, 0, tile_site, r, site, b, sq, flags, counts, bits); break;
-                default: MRB_LAUNCH(ctx, k_tile_bits<4>, ntl, 256, 0, tile_site, r, site, b, sq, flags, counts, bits); break;
+                case 4: MRB_LAUNCH(ctx, k_tile_bits<4>, ntl, 256, 0, tile_site, r, site, b, sq, flags, counts, bits); break;
+                case 5: MRB_LAUNCH(ctx, k_tile_bits<5>, ntl, 256, 0, tile_site, r, site, b, sq, flags, counts, bits); break;
+                case 6: MRB_LAUNCH(ctx, k_tile_bits<6>, ntl, 256, 0, tile_site, r, site, b, sq, flags, counts, bits); break;
+                case 7: MRB_LAUNCH(ctx, k_tile_bits<7>, ntl, 256, 0, tile_site, r, site, b, sq, flags, counts, bits); break;
+                default: MRB_LAUNCH(ctx, k_tile_bits<8>, ntl, 256, 0, tile_site, r, site, b, sq, flags, counts, bits); break;
             }
             if (brick_bits_out) *brick_bits_out = bits;
             return MRB_OK;
