@@ -3,6 +3,8 @@
 Integer / index / topology outputs must be bit-exact; the margin and the QP iterate are compared
 with tolerance 0 as well (design target: bit-exact), the documented bound being 1e-4 voxel units.
 """
+import os
+
 import numpy as np
 import pytest
 
@@ -289,3 +291,31 @@ def test_pool_of_contexts(ctx, synth):
     for v, (verts, faces) in zip(vols, got):
         v1, f1 = ctx.reconstruct(v, iters=60)
         assert np.array_equal(faces, f1) and np.array_equal(verts, v1)
+
+
+@pytest.mark.gpu
+def test_degenerate_volumes_through_the_fused_path(ctx, O, synth):
+    """Empty, full, one-voxel and tiny grids: the tile / brick machinery must cope and agree with the oracle."""
+    for shape in ((9, 9, 9), (33, 17, 40), (64, 64, 64)):
+        for fill in (0.0, 1.0):
+            v = np.full(shape, fill, np.float32)
+            F_ref = O.optimize(v, iters=5)
+            F, st = ctx.optimize(v, iters=5, return_stats=True)
+            assert st["n_band"] == 0 and np.array_equal(F, F_ref), (shape, fill)
+            verts, faces = ctx.reconstruct(v, iters=5)
+            assert len(verts) == 0 and len(faces) == 0
+    v = np.zeros((40, 40, 40), np.float32)
+    v[20, 20, 20] = 1.0                                     # a single voxel, far from every border
+    F_ref = O.optimize(v, iters=30)
+    assert np.array_equal(ctx.optimize(v, iters=30), F_ref)
+    vr, fr = O.mcubes(F_ref, 0.0)
+    verts, faces = ctx.reconstruct(v, iters=30)
+    assert np.array_equal(faces, fr) and np.array_equal(verts, vr)
+    v = np.zeros((40, 41, 37), np.float32)
+    v[12:20, 14:29, 11:17] = 1.0                            # non-cubic grid, box
+    for layout in ("bricks", "strips"):
+        os.environ["MRB_QP_LAYOUT"] = layout
+        try:
+            assert np.array_equal(ctx.optimize(v, iters=40), O.optimize(v, iters=40)), layout
+        finally:
+            del os.environ["MRB_QP_LAYOUT"]
