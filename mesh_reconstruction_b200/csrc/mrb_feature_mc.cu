@@ -179,6 +179,23 @@ __global__ void __launch_bounds__(128) k_flip_edges_par(MrbFeatCell* cellsv, con
     MrbFeatCell* c = cellsv + a;
     const int id = cells[a];
     const int z = id % cz, y = (id / cz) % cy, x = id / (cz * cy);
+    // Which neighbours take part does not change during the kernel (feature flags and the cell map are read-only here):
+    // looked up BEFORE the wait, lane q for neighbour q (two dependent loads), shared by shuffles after it.
+    const bool is_feature = c->feature != 0;
+    int myb = -1;
+    {
+        int nb[6], nn = 0;
+        if (x != 0) nb[nn++] = id - cy * cz;
+        if (x != cx - 1) nb[nn++] = id + cy * cz;
+        if (y != 0) nb[nn++] = id - cz;
+        if (y != cy - 1) nb[nn++] = id + cz;
+        if (z != 0) nb[nn++] = id - 1;
+        if (z != cz - 1) nb[nn++] = id + 1;
+        if (lane < nn) {
+            const int b = cellmap[nb[lane]];
+            if (b >= 0 && cellsv[b].feature != 0) myb = b;           // a surface cell that is a feature cell
+        }
+    }
     // earlier feature cells within Manhattan distance 2: 6 at distance 1, 6 straight + 12 diagonal at distance 2
     int fp = -1;                 // the earlier feature cell this lane has to wait for
     if (lane < 24) {
@@ -225,20 +242,7 @@ __global__ void __launch_bounds__(128) k_flip_edges_par(MrbFeatCell* cellsv, con
     __shared__ MrbFeatCell s_cell[4][7];
     MrbFeatCell* sc = &s_cell[w][0];
     constexpr int kWords = (int)(sizeof(MrbFeatCell) / 4);
-    if (c->feature != 0) {
-        int nb[6], nn = 0;
-        if (x != 0) nb[nn++] = id - cy * cz;
-        if (x != cx - 1) nb[nn++] = id + cy * cz;
-        if (y != 0) nb[nn++] = id - cz;
-        if (y != cy - 1) nb[nn++] = id + cz;
-        if (z != 0) nb[nn++] = id - 1;
-        if (z != cz - 1) nb[nn++] = id + 1;
-        // lane q looks up neighbour q (two dependent loads), the slots are then shared by shuffles
-        int myb = -1;
-        if (lane < nn) {
-            const int b = cellmap[nb[lane]];
-            if (b >= 0 && cellsv[b].feature != 0) myb = b;           // a surface cell that is a feature cell
-        }
+    if (is_feature) {
         MrbFeatCell* gsrc[7];
         gsrc[0] = c;
 #pragma unroll
