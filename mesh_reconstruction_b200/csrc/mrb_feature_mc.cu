@@ -408,7 +408,7 @@ extern "C" int mrb_mcubes_features(mrb_ctx* ctx, const float* F, const float* su
             MRB_LAUNCH(ctx, k_findex, cdiv(nf, 256), 256, 0, fcells, nf, findex);
             MRB_CUDA(cudaMemsetAsync(slot_off, 0, ((size_t)nsteps + 1) * sizeof(int), ctx->stream));
             MRB_CUDA(cudaMemsetAsync(done, 0, ((size_t)nf + 1) * sizeof(unsigned), ctx->stream));
-            const int chunk = getenv("MRB_FLIP_CHUNK") ? std::max(1, atoi(getenv("MRB_FLIP_CHUNK"))) : 1;
+            const int chunk = 1;          // several consecutive cells per warp were measured slower (9.5 ms at 2, 30 ms at 16)
             long long* prof = nullptr;
             if (getenv("MRB_FLIP_STATS")) { MRB_TRY(arena_alloc(ctx, (size_t)nf * 4, &prof)); MRB_CUDA(cudaMemsetAsync(prof, 0, (size_t)nf * 32, ctx->stream)); }
             MRB_LAUNCH(ctx, k_flip_edges_par, cdiv(cdiv(nf, chunk), 4), 128, 0, fc, cells, fcells, nf, cellmap, findex, d, slots, slot_off, done,
