@@ -225,7 +225,7 @@ __global__ void __launch_bounds__(128) k_flip_edges_par(MrbFeatCell* cellsv, con
                 asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(done + fp) : "memory");
                 if (v != 0) break;
                 __nanosleep(200);
-                if (++spins == (1u << 24)) __trap();
+                if (++spins == (1u << 26)) __trap();     // ~15 s: a lost predecessor must not hang the GPU
             }
             depth = max(depth, v);
         }
