@@ -171,12 +171,14 @@ typedef struct mrb_mesh {
     int*    faces;     /* nfaces * 3 vertex ids, reference triangle order */
     int     nverts;
     int     nfaces;
-    int     on_device; /* 1: verts/faces are device pointers owned by the ctx arena (valid until next call) */
+    int     on_device; /* where verts/faces live = the device_out the call was made with:
+                        * 0 malloc'd host arrays owned by the caller (mrb_mesh_free);
+                        * 1 device memory of the context's arena, 2 pinned host memory of the context (no extra host copy):
+                        *   both owned by the context and valid until the next call on it; mrb_mesh_free only clears the struct */
 } mrb_mesh;
 
 /* mcubes (mcubes.cpp:592-662) without the PLY write, default (non-feature) path:
- * getGridCells + Polygonise + pointHashmap.  Result arrays are malloc'd host memory
- * (release with mrb_mesh_free) unless device_out != 0. */
+ * getGridCells + Polygonise + pointHashmap.  device_out: see mrb_mesh.on_device (0, 1 or 2). */
 int  mrb_mcubes(mrb_ctx* ctx, const float* F, const int dims[3], float isolevel,
                 int device_out, mrb_mesh* out);
 void mrb_mesh_free(mrb_mesh* mesh);

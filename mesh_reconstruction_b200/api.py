@@ -227,7 +227,7 @@ class Context:
     # ---- stage 4 (mcubes.h:354, hasher.h:84-106) ---------------------------------------------------
     def _take_mesh(self, m, like):
         nv, nf = m.nverts, m.nfaces
-        if m.on_device:
+        if m.on_device == 1:
             import torch
             verts = torch.empty((nv, 3), dtype=torch.float32, device=like.device)
             faces = torch.empty((nf, 3), dtype=torch.int32, device=like.device)
@@ -236,6 +236,7 @@ class Context:
             if nf:
                 self._check(self.lib.mrb_copy(self.h, faces.data_ptr(), C.cast(m.faces, C.c_void_p), nf * 12))
             return verts, faces
+        # on_device == 0: malloc'd arrays (freed below); 2: the context's pinned staging (valid until the next call): copy out
         verts = np.ctypeslib.as_array(m.verts, shape=(max(nv, 1), 3))[:nv].copy()
         faces = np.ctypeslib.as_array(m.faces, shape=(max(nf, 1), 3))[:nf].copy()
         self.lib.mrb_mesh_free(C.byref(m))
@@ -245,7 +246,7 @@ class Context:
         """mcubes.h:354 default path; returns (verts [V,3] grid coords, faces [F,3]); writes the PLY if filename."""
         kF, pF, shape, like = self._in(F)
         m = L.Mesh()
-        self._check(self.lib.mrb_mcubes(self.h, pF, self._dims(shape), float(isolevel), 1 if like is not None else 0,
+        self._check(self.lib.mrb_mcubes(self.h, pF, self._dims(shape), float(isolevel), 1 if like is not None else 2,
                                         C.byref(m)))
         verts, faces = self._take_mesh(m, like)
         if filename is not None:
@@ -259,7 +260,7 @@ class Context:
         kn, pn, nshape, _ = self._in(normals)
         m = L.Mesh()
         self._check(self.lib.mrb_mcubes_features(self.h, pF, pm, pn, int(nshape[0]), self._dims(shape), float(isolevel),
-                                                 float(feat_thresh), float(corner_thresh), 1 if like is not None else 0,
+                                                 float(feat_thresh), float(corner_thresh), 1 if like is not None else 2,
                                                  C.byref(m)))
         return self._take_mesh(m, like)
 
@@ -293,7 +294,7 @@ class Context:
         m = L.Mesh()
         st = L.QPStats()
         self._check(self.lib.mrb_reconstruct(self.h, pv, self._dims(shape), C.byref(opt),
-                                             1 if like is not None else 0, C.byref(m), C.byref(st)))
+                                             1 if like is not None else 2, C.byref(m), C.byref(st)))
         verts, faces = self._take_mesh(m, like)
         if return_stats:
             return verts, faces, _stats(st)

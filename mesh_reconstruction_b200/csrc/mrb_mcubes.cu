@@ -451,10 +451,21 @@ __global__ void k_hash_points(const float* __restrict__ xyz, int n, int ny, int 
 int export_mesh(mrb_ctx* ctx, float* verts_dev, int* faces_dev, int nverts, int nfaces, int device_out, mrb_mesh* out) {
     out->nverts = nverts;
     out->nfaces = nfaces;
-    out->on_device = device_out ? 1 : 0;
-    if (device_out) {
+    out->on_device = device_out == 2 ? 2 : (device_out ? 1 : 0);
+    if (device_out && device_out != 2) {
         out->verts = verts_dev;
         out->faces = faces_dev;
+        return sync(ctx);
+    }
+    if (device_out == 2) {
+        // the context's pinned staging itself: full PCIe rate and no second host copy
+        const size_t vb2 = (sizeof(float) * 3 * (size_t)nverts + 255) / 256 * 256, fb2 = sizeof(int) * 3 * (size_t)nfaces;
+        char* pin2 = nullptr;
+        MRB_TRY(pinned_reserve(ctx, vb2 + fb2 + 256, &pin2));
+        if (nverts > 0) MRB_CUDA(cudaMemcpyAsync(pin2, verts_dev, sizeof(float) * 3 * (size_t)nverts, cudaMemcpyDeviceToHost, ctx->stream));
+        if (nfaces > 0) MRB_CUDA(cudaMemcpyAsync(pin2 + vb2, faces_dev, fb2, cudaMemcpyDeviceToHost, ctx->stream));
+        out->verts = (float*)pin2;
+        out->faces = (int*)(pin2 + vb2);
         return sync(ctx);
     }
     out->verts = (float*)malloc(sizeof(float) * 3 * (size_t)(nverts > 0 ? nverts : 1));
@@ -495,7 +506,7 @@ int mrb_mcubes(mrb_ctx* ctx, const float* F, const int dims[3], float isolevel, 
 
 void mrb_mesh_free(mrb_mesh* mesh) {
     if (!mesh) return;
-    if (!mesh->on_device) { free(mesh->verts); free(mesh->faces); }
+    if (mesh->on_device == 0) { free(mesh->verts); free(mesh->faces); }     // 1, 2: owned by the context
     mesh->verts = nullptr; mesh->faces = nullptr; mesh->nverts = 0; mesh->nfaces = 0;
 }
 
