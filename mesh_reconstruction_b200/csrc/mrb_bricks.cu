@@ -1178,12 +1178,9 @@ int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_
             MRB_CUDA(cudaEventRecord(ctx->ev[7], ctx->stream));
             ctx->launches++;
             xres = (iters % 2) ? (const float*)xb : (const float*)xa;
-            if (last_delta_host) {
-                MRB_CUDA(cudaMemcpyAsync(ctx->h_mail + 8, md, sizeof(unsigned), cudaMemcpyDeviceToHost, ctx->stream));
-                MRB_CUDA(cudaStreamSynchronize(ctx->stream));
-                unsigned bits = (unsigned)ctx->h_mail[8];
-                memcpy(last_delta_host, &bits, sizeof(float));
-            }
+            // the residual travels to h_mail[8] with the stream; the caller reads it after its own synchronisation
+            // (no host round trip of its own between the sweeps and the F assembly)
+            if (last_delta_host) MRB_CUDA(cudaMemcpyAsync(ctx->h_mail + 8, md, sizeof(unsigned), cudaMemcpyDeviceToHost, ctx->stream));
         } else if (iters > 0) {
             unsigned* md = (unsigned*)(ctx->d_mail + 8);
             unsigned* bar = (unsigned*)ctx->d_bar;

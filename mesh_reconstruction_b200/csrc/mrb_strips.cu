@@ -653,10 +653,12 @@ int optimize_strips(mrb_ctx* ctx, const float* vol, const float* fmap, Dims d, i
             MRB_CUDA(cudaMemcpyAsync(ctx->h_mail + 32, counts, 4 * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
             int Q = 0, closure_err = 0;
             float last_delta = 0.0f;
+            ctx->h_mail[8] = 0;
             MRB_TRY(bricks_solve(ctx, vol, fmap, flags, sq, d, band_size, iters, using_features, F_dev,
                                  stats ? &last_delta : nullptr, &Q, &closure_err, binary, brick_bits));
             MRB_CUDA(cudaEventRecord(ctx->ev[3], ctx->stream));
             MRB_CUDA(cudaStreamSynchronize(ctx->stream));
+            if (stats && last_delta == 0.0f) memcpy(&last_delta, &ctx->h_mail[8], sizeof(float));     // tiled kernel: copied with the stream
             if (ctx->h_mail[34] || closure_err) {
                 set_error("narrow band touches the grid border (tight-band voxel on the border or with a neighbour outside "
                           "the band); the reference exits here (grid.cpp:20-37 via primeqp.cpp:40-75)");

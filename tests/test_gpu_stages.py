@@ -143,6 +143,7 @@ def test_optimize_sync_and_layout_variants(ctx, O, synth, monkeypatch):
     """Every selectable stage-3 variant (tuning knobs) must give the same bits as the default."""
     v = synth.torus(56, 14.0, 5.0)
     F_ref = O.optimize(v, iters=60)
+    deltas = []
     B = {"MRB_QP_LAYOUT": "bricks"}          # grids this small default to the strip kernel
     X = dict(B, MRB_QP_ORDER="xyz")          # the older (X,Y,Z)-ordered brick kernel
     for env in (B, dict(B, MRB_QP_BRICK_THREADS="512"), dict(B, MRB_QP_BRICK_THREADS="256"), dict(B, MRB_QP_BRICK_COMPACT="1"),
@@ -152,7 +153,11 @@ def test_optimize_sync_and_layout_variants(ctx, O, synth, monkeypatch):
                 {"MRB_QP_LAYOUT": "strips", "MRB_QP_VARIANT": "0:1024"}, {"MRB_QP_LAYOUT": "strips", "MRB_QP_VARIANT": "2:512"}):
         for k, val in env.items():
             monkeypatch.setenv(k, val)
-        assert np.array_equal(ctx.optimize(v, iters=60), F_ref), env
+        F, st = ctx.optimize(v, iters=60, return_stats=True)
+        assert np.array_equal(F, F_ref), env
+        # the residual of the last sweep (max |x_60 - x_59|) is the same number whichever kernel reduced it
+        deltas.append(st["last_max_delta"])
+        assert 0.0 < deltas[-1] < 1.0 and deltas[-1] == deltas[0], env
         for k in env:
             monkeypatch.delenv(k)
 
