@@ -971,7 +971,9 @@ __global__ void __launch_bounds__(Threads, MinBlocks) k_qp_bricks_tiled(const ui
             if ((threadIdx.x & 31) == 0) atomicMax(maxdelta_bits, __float_as_uint(dmax));
         } else if (!(dbg & 1)) {
             __syncthreads();        // the block's stores of this sweep are issued; its reads of the neighbours' bricks are done
-            if (flags_on && threadIdx.x == 0) {
+            // Published by the LAST warp's first lane (MRB_QP_DEBUG=32: by thread 0): the release waits for the block's
+            // stores to be visible, and warp 0 should already be polling the neighbours' flags during that time.
+            if (flags_on && (int)threadIdx.x == ((dbg & 32) ? 0 : nthreads - 32)) {
                 if (Sharded && (my_lo >= 0 || my_hi >= 0)) {
                     // one system-scope fence covers the stores into the neighbour GPUs (made cumulative by the barrier)
                     asm volatile("fence.acq_rel.sys;" ::: "memory");
@@ -1158,6 +1160,9 @@ int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_
             *closure_err_host = ctx->h_mail[24];
             if (*closure_err_host) return MRB_OK;              // caller reports MRB_EBORDER
             int dbg = getenv("MRB_QP_DEBUG") ? atoi(getenv("MRB_QP_DEBUG")) : 0;
+            // who publishes a block's sweep: the last warp when the grid fills the GPU (warp 0 polls meanwhile: 2.69 -> 2.66 ms at
+            // 256^3), thread 0 when the blocks were shrunk (there the last warp is first in line for rim bricks: 172^3 2.19 vs 1.99 ms)
+            if (t_threads < 480) dbg |= 32;
             if (overflow) dbg |= 4;        // a block with more than kChunkListCap neighbour blocks: grid barrier per sweep
             int cap = (Q + grid - 1) / grid + 9;       // block ranges are whole groups of 8 bricks
             // expanded constants (168 B per brick) for binary volumes if one block's share fits, else the 64-byte form
@@ -1885,7 +1890,7 @@ static int solve_sharded_tiled(mrb_qp_plan* plan, int rank, int world, void* con
         if (getenv("MRB_QP_BRICK_COMPACT") || smem > (size_t)220 * 1024 / (size_t)fit) { expanded = 0; smem = (size_t)cap * 64; }
         if (!expanded && smem > 96 * 1024 / (size_t)fit) { cap = 0; smem = 0; }
         if (smem > 48 * 1024) MRB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        int its = iters, QQ = Qo, dbg = 0;
+        int its = iters, QQ = Qo, dbg = 32;      // thread 0 publishes (the configuration the multi-GPU runs were validated with)
         size_t PP = P;
         void* args[] = {(void*)&code, (void*)&fields, (void*)&nbA, (void*)&nbB, (void*)&xa, (void*)&xb, (void*)&QQ, (void*)&its,
                         (void*)&md, (void*)&bar, (void*)&dbg, (void*)&blk_nb, (void*)&progress, (void*)&cap, (void*)&plist, (void*)&pcount,
