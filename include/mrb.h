@@ -25,6 +25,11 @@
  *    (The reference prints and exit(1)s -- the compat shim reproduces that.)
  *  - One mrb_ctx per host thread / per GPU; calls on one ctx are serialised on
  *    its stream and are synchronous on return unless stated otherwise.
+ *  - Dead-man switch: the persistent sweep kernels (stage 3, single- and multi-GPU) and the flipEdges
+ *    kernel wait on progress flags of other blocks / peer GPUs in spin loops that execute a trap after
+ *    about 2^26 polls (a lost peer or predecessor).  The call then fails with MRB_ECUDA and the error is
+ *    STICKY: the CUDA context of the whole process is unusable afterwards (every mrb_ctx and every other
+ *    CUDA library in it); the process has to be restarted or its primary context reset with cudaDeviceReset.
  */
 #ifndef MRB_H
 #define MRB_H

@@ -103,7 +103,6 @@ int side_reserve(mrb_ctx* ctx, int which, size_t bytes, char** out) {
 int pinned_reserve(mrb_ctx* ctx, size_t bytes, char** out) {
     if (bytes > ctx->h_pinned_cap) {
         if (ctx->h_pinned) cudaFreeHost(ctx->h_pinned);
-    for (int w = 0; w < 2; w++) if (ctx->side[w]) cudaFree(ctx->side[w]);
         ctx->h_pinned = nullptr;
         size_t cap = bytes + (bytes >> 2) + (1u << 20);
         cudaError_t e = cudaMallocHost((void**)&ctx->h_pinned, cap);

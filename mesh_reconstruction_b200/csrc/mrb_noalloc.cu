@@ -30,6 +30,8 @@ static const int kMaxDevices = 64;
 static int* g_scratch_addr[kMaxDevices] = {nullptr};   // per-device address of g_noalloc_scratch
 
 // Looks the array's device address up the first time a given GPU is used (that GPU must be current).
+// The cache is filled without a lock: two threads making their first call on the same GPU at the same
+// time both look the symbol up and both store the same value, so the race is harmless.
 static int noalloc_scratch(int device, int** out) {
     if (device < 0 || device >= kMaxDevices) { set_error("mrb_find_indexes_noalloc: device %d not supported", device); return MRB_EINVAL; }
     if (g_scratch_addr[device] == nullptr) {
@@ -123,6 +125,21 @@ int mrb_find_indexes_noalloc(const float* grid_dev, const int dims[3], int* idx_
     cudaStream_t stream = (cudaStream_t)stream_v;
     int device = 0;
     MRB_CUDA(cudaGetDevice(&device));
+    // The kernels run on the current GPU with the current GPU's scratch array: buffers that live on another
+    // GPU would fault or be reached through peer access with the wrong scratch, so they are refused.
+    {
+        cudaPointerAttributes pa;
+        const void* ptrs[2] = {grid_dev, idx_out_dev};
+        for (int i = 0; i < 2; i++) {
+            if (!ptrs[i]) continue;
+            if (cudaPointerGetAttributes(&pa, ptrs[i]) != cudaSuccess) { cudaGetLastError(); continue; }
+            if (pa.type == cudaMemoryTypeDevice && pa.device != device) {
+                set_error("mrb_find_indexes_noalloc: %s lives on GPU %d but GPU %d is current",
+                          i == 0 ? "grid" : "idx_out", pa.device, device);
+                return MRB_EINVAL;
+            }
+        }
+    }
     int* scratch = nullptr;
     MRB_TRY(noalloc_scratch(device, &scratch));     // first call on this GPU resolves the array's address
 
