@@ -6,12 +6,17 @@
 // only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs
 // may load it.  libmrb.so never links or calls it.
 //
-// Parity pin: the reference ships no tests, golden vectors or fixtures for this path
-//  and cannot be compiled here (Eigen, PCL and Boost are absent),
-// so for the default path this oracle *is* the pin; it is itself pinned by hand-derived
-// known-answer tests (tests/test_oracle_*.py: 5^3 cube of distance_fields/main.cpp:5-23,
-// single voxel, O(N^6) brute-force EDT, closed-form H matrix) and the committed
-// tests/golden/ fixtures.  PARITY UNPINNED against a compiled reference.
+// Parity pin: the reference ships no tests, golden vectors or fixtures for this path (SURVEY.md
+// section 4 / 8c).  The oracle is pinned against the REFERENCE'S OWN CODE: oracle/build_ref.sh
+// compiles the reference's hot-path translation units unmodified from /root/reference (stand-in
+// headers for the absent Eigen / Boost / PCL, oracle/ref_stubs/) into oracle/_ref/libmrb_ref.so, and
+// tests/test_ref_pin.py requires this file to equal it bit for bit on every stage, the whole default
+// path (F, mesh, PLY bytes), the feature path and the edge cases, live and through committed
+// fixtures generated from it (tests/golden/ref_golden.*).  NOT pinned by that build, and bounded
+// by tolerance tests instead: the floating-point path inside Eigen's eigen-solver / JacobiSVD
+// (feature sub-path only; our definition is include/mrb_eig3.h) and the assumption that Eigen's
+// sparse product returns row indexes ascending inside each column (values are exact integers).
+// Also kept: hand-derived known answers (tests/test_oracle_*.py) and tests/golden/ (oracle-made).
 //
 // Build: g++ -O2 -ffp-contract=off -fno-fast-math -fopenmp -shared -fPIC (oracle/Makefile).
 // fp32 everywhere, no FMA contraction (the reference is a Debug x86-64 build, CMakeLists.txt:3).
