@@ -12,8 +12,17 @@ e2e     = the same through the reference-facing C-ABI call with HOST buffers (pi
           host mesh out; H2D / D2H copies inside the timed region)
 N > 1   = object-parallel: one independent object per GPU (weak scaling, no data-path collective).
 
-`--impl reference` times the reference's CPU path (the oracle restatement: the reference itself cannot
-be compiled here) on the host cores for the same metric.
+Two more records ride on the same JSON line (they do not change metric / value / config.workload):
+  slab   (N > 1) the SAME 256^3 grid (BASELINE config 3) slab-sharded over the N GPUs -- stage 3 in one persistent kernel
+         per GPU with the halo exchange over NVLink peer memory -- and, at N = 8, the 512^3 grid of config 4: solve and
+         whole-step device times, voxel-updates/s, and `bit_identical` computed IN THE RUN against every rank's own
+         single-GPU mrb_reconstruct (F, vertices, faces);
+  batch  BASELINE config 5: 1024 objects of 52^3 split over the N ranks (dist.shard_objects), each rank's share through
+         mrb_reconstruct_batch from pinned host memory to host meshes: meshes/s end to end.
+
+`--impl reference` times the reference's CPU path for the same metric on the same 256^3 workload at every N: the oracle
+restatement (pinned bit for bit to the reference's own sources, oracle/_ref) with OpenMP over all host cores -- the
+reference itself is single-threaded; its 1-core time is reported beside it as `cpu_baseline_1core`.
 """
 import argparse
 import json
@@ -100,84 +109,177 @@ def measured_peak():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
-def cpu_baseline(volume, band_size, iters, budget_s=30.0):
-    """Oracle (restated reference CPU path) on the host cores; bounded sample of the same workload."""
+def base_config(workload, band_size, iters, B, world):
+    """The `config` object: identical in the GPU arm and the reference arm."""
+    return {"workload": workload, "band_size": band_size, "sweeps": iters, "band_voxels": int(B),
+            "objects_per_step": "one per GPU (GPU arm, object-parallel x%d); one (CPU arm, rank 0 only)" % world,
+            "l2": "GPU arm: explicit 256 MiB flush write between timed iterations; CPU arm: 64 MiB input > any host cache"}
+
+
+def cpu_worker(args):
+    """Child process of the CPU legs (thread count fixed by OMP_NUM_THREADS in its environment, optionally pinned to
+    one core): times whole steps of the oracle on the requested grid and prints one JSON object."""
+    if args.pin_one_core:
+        cpus = sorted(os.sched_getaffinity(0))
+        os.sched_setaffinity(0, {cpus[len(cpus) // 2]})
     from oracle import oracle as O
-    from mesh_reconstruction_b200 import synth
     O.build()
-    cores = len(os.sched_getaffinity(0))
-    small = synth.sphere(128, 46.0)
-    t0 = time.perf_counter()
-    F, info = O.optimize(small, band_size=band_size, iters=iters, brute_edt=True, return_info=True)
-    O.mcubes(F, 0.0)
-    t_small = time.perf_counter() - t0
-    val = info["n_band"] * iters / t_small
-    sample = "128^3 sphere R=46 (1/8 of the workload's voxels), full pipeline, %d sweeps, %.2f s" % (iters, t_small)
-    # the full 256^3 step costs ~8x (QP, MC) .. 16x (brute-force EDT) the 128^3 one
-    if volume.shape[0] == 256 and t_small * 14.0 <= budget_s:
+    volume, _ = make_volume(args.size, args.band_size)
+
+    def step():
         t0 = time.perf_counter()
-        F, info = O.optimize(volume, band_size=band_size, iters=iters, brute_edt=True, return_info=True)
+        F, info = O.optimize(volume, band_size=args.band_size, iters=args.iters, brute_edt=True, return_info=True)
         O.mcubes(F, 0.0)
-        t_full = time.perf_counter() - t0
-        val = info["n_band"] * iters / t_full
-        sample = "the full workload once (256^3, %d sweeps), %.2f s" % (iters, t_full)
-    return {"value": val, "unit": UNIT, "cores": cores, "kind": "port",
-            "sample": sample + "; oracle = restated reference CPU path, OpenMP over independent rows/lines "
-                               "(the reference itself is single-threaded)"}
+        return time.perf_counter() - t0, info
+    t_first, info = step()
+    # always the requested grid; fewer steps when the budget is short: the first step is the warm-up when at least one
+    # more fits, otherwise it is the (single) timed step
+    fit = int((args.budget_s - t_first) / max(t_first, 1e-9))
+    times = []
+    if fit >= 1:
+        warm_extra = min(max(args.warmup - 1, 0), max(fit - args.steps, 0))
+        for _ in range(warm_extra):
+            step()
+        for _ in range(max(1, min(args.steps, fit - warm_extra))):
+            times.append(step()[0])
+        warmed = 1 + warm_extra
+    else:
+        times.append(t_first)
+        warmed = 0
+    print(json.dumps({"ms_per_step": 1000.0 * sum(times) / len(times), "n_band": info["n_band"], "steps_timed": len(times),
+                      "warmup_done": warmed, "threads": int(os.environ.get("OMP_NUM_THREADS", "0")),
+                      "stages_ms": {k: info[k] for k in ("ms_dfield", "ms_band", "ms_prime", "ms_qp")}}))
+
+
+def run_cpu_leg(args, threads, steps, warmup, budget_s, pin_one_core=False):
+    """Runs cpu_worker in a child with the thread count set by us (torchrun exports OMP_NUM_THREADS=1)."""
+    env = dict(os.environ)
+    env["OMP_NUM_THREADS"] = str(threads)
+    env.pop("OMP_PROC_BIND", None)
+    cmd = [sys.executable, os.path.abspath(__file__), "--cpu-worker", "--size", str(args.size), "--band-size", str(args.band_size),
+           "--iters", str(args.iters), "--steps", str(steps), "--warmup", str(warmup), "--budget-s", str(budget_s)]
+    if pin_one_core:
+        cmd.append("--pin-one-core")
+    out = subprocess.run(cmd, env=env, stdout=subprocess.PIPE, text=True, check=True).stdout
+    return json.loads(out.strip().splitlines()[-1])
+
+
+def cpu_model():
+    try:
+        for ln in open("/proc/cpuinfo"):
+            if ln.startswith("model name"):
+                return ln.split(":", 1)[1].strip()
+    except Exception:
+        pass
+    return "unknown"
+
+
+def cpu_baseline(args):
+    """The restated reference CPU path on the host cores, on the workload itself (one timed 256^3 step per leg):
+    all cores (OpenMP over independent rows / lines; NOT the reference, which is single-threaded) and 1 pinned core
+    (the reference's own configuration)."""
+    cores = len(os.sched_getaffinity(0))
+    r = run_cpu_leg(args, cores, steps=1, warmup=1, budget_s=45.0)
+    val = r["n_band"] * args.iters / (r["ms_per_step"] / 1000.0)
+    what = "the full workload (%d^3, %d sweeps, brute-force EDT), %d timed step(s) of %.2f s" % (
+        args.size, args.iters, r["steps_timed"], r["ms_per_step"] / 1000.0)
+    all_cores = {"value": val, "unit": UNIT, "cores": cores, "kind": "port",
+                 "sample": what + "; oracle port of the reference CPU path with OpenMP on all %d host cores -- not the "
+                                  "reference's configuration (it is single-threaded); host CPU: %s" % (cores, cpu_model())}
+    one = None
+    if not args.no_cpu_1core:
+        r1 = run_cpu_leg(args, 1, steps=1, warmup=0, budget_s=0.0, pin_one_core=True)
+        one = {"value": r1["n_band"] * args.iters / (r1["ms_per_step"] / 1000.0), "unit": UNIT, "cores": 1, "kind": "port",
+               "ms_per_step": r1["ms_per_step"], "stages_ms": r1["stages_ms"],
+               "sample": "the full workload once (%d^3, %d sweeps, brute-force EDT) on 1 core pinned with sched_setaffinity "
+                         "(BASELINE.md section 2), %.1f s" % (args.size, args.iters, r1["ms_per_step"] / 1000.0)}
+    return all_cores, one
 
 
 def run_reference(args):
-    """Reference arm: the CPU path on all host threads, same metric/config."""
+    """Reference arm: the CPU path on all host threads, same metric, same 256^3 workload at every N (rank 0 only)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    from oracle import oracle as O
-    from mesh_reconstruction_b200 import synth
-    O.build()
     cores = len(os.sched_getaffinity(0))
-    volume, workload = make_volume(args.size, args.band_size)
-    budget = 200.0
-    total_steps = args.steps + args.warmup
-    # choose the largest sample whose estimated run time fits the budget
-    probe = synth.sphere(64, 14.0)
-    t0 = time.perf_counter()
-    F, _ = O.optimize(probe, band_size=args.band_size, iters=args.iters, return_info=True)
-    O.mcubes(F, 0.0)
-    t64 = time.perf_counter() - t0
-    choice = None
-    for size in (args.size, 192, 128, 96, 64):
-        if size > args.size:
-            continue
-        scale = (size / 64.0) ** 3 * (1.0 + 0.5 * (size / 64.0))     # N^3 stages + the O(N^4) EDT
-        if t64 * scale * total_steps <= budget or size == 64:
-            choice = size
-            break
-    vol = volume if choice == args.size else synth.sphere(choice, choice / 2.0 - 18.0)
-    times, nb = [], 0
-    for s in range(total_steps):
-        t0 = time.perf_counter()
-        F, info = O.optimize(vol, band_size=args.band_size, iters=args.iters, brute_edt=True, return_info=True)
-        O.mcubes(F, 0.0)
-        dt = time.perf_counter() - t0
-        nb = info["n_band"]
-        if s >= args.warmup:
-            times.append(dt)
-    ms = 1000.0 * sum(times) / max(len(times), 1)
-    val = nb * args.iters / (ms / 1000.0)
-    sample = ("whole step (EDT brute force + band + primeQP + %d sweeps + MC) on a %d^3 sphere, B=%d"
-              % (args.iters, choice, nb))
-    if choice != args.size:
-        sample += " -- bounded sample of the %d^3 workload chosen to fit the time budget" % args.size
+    _, workload = make_volume(args.size, args.band_size)
+    r = run_cpu_leg(args, cores, steps=args.steps, warmup=args.warmup, budget_s=150.0)
+    ms = r["ms_per_step"]
+    val = r["n_band"] * args.iters / (ms / 1000.0)
+    sample = ("whole step (brute-force EDT + band + primeQP + %d sweeps + MC) on the workload itself (%d^3, B=%d): "
+              "%d timed step(s) after %d warm-up step(s) -- fewer than --steps/--warmup when they would not fit 150 s; "
+              "oracle port of the reference CPU path (pinned bit for bit to the reference's own sources, oracle/_ref) "
+              "with OpenMP on all %d host cores (the reference is single-threaded); host CPU: %s"
+              % (args.iters, args.size, r["n_band"], r["steps_timed"], r["warmup_done"], cores, cpu_model()))
     line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": workload, "band_size": args.band_size, "sweeps": args.iters,
-                       "reference_impl": "oracle port of the reference CPU path (reference not buildable here: "
-                                         "Eigen/PCL/Boost absent)"},
+            "config": base_config(workload, args.band_size, args.iters, r["n_band"], args.gpus),
+            "steps_timed": r["steps_timed"], "stages_ms": r["stages_ms"],
             "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line))
+
+
+def slab_records(ctx, args, world, local):
+    """N > 1: the slab-sharded whole path on the same 256^3 grid (config 3) and, at N = 8, on config 4 (512^3)."""
+    import torch
+    from mesh_reconstruction_b200 import slab, synth
+    dev = torch.device("cuda", local)
+    out = {}
+    cases = [("config3_256", 3)] + ([("config4_512", 4)] if world >= 8 else [])
+    solver = slab.FusedSolver(ctx, slab.max_bricks_for((512,) * 3 if world >= 8 else (256,) * 3) // 4)
+    for name, cfg in cases:
+        vol = synth.config_volume_t(cfg, device=dev)
+        out[name] = slab.check_against_single_gpu(ctx, solver, vol, iters=args.iters, band_size=args.band_size, reps=3)
+        del vol
+    out["note"] = ("one grid on N GPUs: stages 1-2 and 4 on every rank, stage 3 slab-sharded along x in one persistent "
+                   "kernel per GPU, halo bricks stored into the neighbours' buffers over NVLink peer memory, per-sweep flags")
+    return out
+
+
+def batch_record(ctx, args, world, rank, local):
+    """BASELINE config 5: 1024 objects of 52^3, object-parallel: a contiguous block of objects per rank through
+    mrb_reconstruct_batch, pinned host volumes in, host meshes out (wall clock between barriers, max over ranks)."""
+    import torch
+    import torch.distributed as dist
+    from mesh_reconstruction_b200 import synth
+    from mesh_reconstruction_b200.dist import shard_objects, max_over_ranks
+    n_total = args.batch_objects
+    mine = shard_objects(n_total, world, rank)
+    stack = torch.empty((len(mine), 52, 52, 52), dtype=torch.float32).pin_memory()
+    host = stack.numpy()
+    for i, oid in enumerate(mine):
+        host[i] = synth.random_object(1000 + oid)
+    kw = dict(band_size=args.band_size, iters=args.iters)
+
+    def sync():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+    ctx.reconstruct_batch(host[:min(8, len(mine))], **kw)
+    meshes = ctx.reconstruct_batch(host, **kw)                       # warm-up at full size (arena growth)
+    v0, f0 = ctx.reconstruct(host[0], **kw)
+    ok = bool(np.array_equal(meshes[0][0], v0) and np.array_equal(meshes[0][1], f0))
+    times = []
+    for _ in range(3):
+        sync()
+        t0 = time.perf_counter()
+        meshes = ctx.reconstruct_batch(host, **kw)
+        torch.cuda.synchronize()
+        times.append(time.perf_counter() - t0)
+    sync()
+    dt, = max_over_ranks([float(np.mean(times))], device=torch.device("cuda", local))
+    flag = torch.tensor([1 if ok else 0], device=torch.device("cuda", local))
+    if world > 1:
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    return {"workload": "%d x 52^3 random objects (BASELINE config 5, seed 1000+id), %d sweeps" % (n_total, args.iters),
+            "objects": n_total, "objects_per_gpu": len(shard_objects(n_total, world, 0)), "meshes_per_s": n_total / dt,
+            "ms_total": 1000.0 * dt, "path": "mrb_reconstruct_batch per rank, pinned host volumes -> host meshes",
+            "h2d_bytes": int(n_total) * 52 ** 3 * 4, "first_object_equals_single_call": bool(int(flag)),
+            "faces_rank0": int(sum(len(m[1]) for m in meshes))}
 
 
 def main():
@@ -190,7 +292,16 @@ def main():
     ap.add_argument("--band-size", type=int, default=4)
     ap.add_argument("--iters", type=int, default=500)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-cpu-1core", action="store_true", help="skip the 1-core CPU leg (about a minute)")
+    ap.add_argument("--no-extras", action="store_true", help="skip the slab / batch records (profiling runs)")
+    ap.add_argument("--batch-objects", type=int, default=1024)
+    ap.add_argument("--cpu-worker", action="store_true", help=argparse.SUPPRESS)
+    ap.add_argument("--pin-one-core", action="store_true", help=argparse.SUPPRESS)
+    ap.add_argument("--budget-s", type=float, default=150.0, help=argparse.SUPPRESS)
     args = ap.parse_args()
+    if args.cpu_worker:
+        cpu_worker(args)
+        return
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = max(args.warmup, 1)   # contract asks W >= 3; honoured by default, not forced for debugging
 
@@ -307,10 +418,9 @@ def main():
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": workload, "band_voxels": B, "tight_voxels": stats[-1]["n_tight"],
-                       "sweeps": args.iters, "objects_per_step": world, "parallelism": "object-parallel x%d" % world,
-                       "l2": "explicit 256 MiB flush write between timed iterations",
-                       "mesh": {"verts": int(len(verts)), "faces": int(len(faces))}},
+            "config": base_config(workload, args.band_size, args.iters, B, world),
+            "parallelism": "object-parallel x%d" % world, "tight_voxels": stats[-1]["n_tight"],
+            "mesh": {"verts": int(len(verts)), "faces": int(len(faces))},
             "meshes_per_s": world / (ms_per_step / 1000.0),
             "stages_ms": {k: float(np.mean([s[k] for s in stats])) for k in ("ms_dfield", "ms_band", "ms_qp", "ms_mc")},
             # SURVEY 8d algorithmic bytes per stage / stage time / measured peak (stage 2's time includes the brick build)
@@ -339,7 +449,18 @@ def main():
             except Exception:
                 pass
         if world == 1 and not args.no_cpu_baseline:
-            line["cpu_baseline"] = cpu_baseline(volume, args.band_size, args.iters)
+            line["cpu_baseline"], one = cpu_baseline(args)
+            if one is not None:
+                line["cpu_baseline_1core"] = one
+    if not args.no_extras:
+        if world > 1:
+            rec = slab_records(ctx, args, world, local)
+            if rank == 0:
+                line["slab"] = rec
+        rec = batch_record(ctx, args, world, rank, local)
+        if rank == 0:
+            line["batch"] = rec
+    if rank == 0:
         print(json.dumps(line))
     ctx.close()
     if world > 1:

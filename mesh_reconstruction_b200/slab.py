@@ -190,62 +190,154 @@ def balanced_cuts(plane_off, world):
     return cuts
 
 
-def solve_fused(ctx, volume, iters=500, band_size=4, timings=None):
-    """Slab-sharded solve with the halo exchange INSIDE the persistent kernel: every rank's iterate buffers and a
+class FusedSolver:
+    """Slab-sharded stage 3 with the halo exchange INSIDE the persistent kernel.  Every rank's two iterate buffers and a
     small flag block live in torch symmetric memory (peer-mapped over NVLink); mrb_qp_plan_solve_sharded stores the
-    boundary brick planes straight into the neighbours' buffers and synchronises with per-sweep flags.
-    Works with world size 1 (no process group needed).  Every rank returns the full F."""
-    import torch
-    import torch.distributed as dist
-    distributed = dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
-    world = dist.get_world_size() if distributed else 1
-    rank = dist.get_rank() if distributed else 0
+    boundary brick planes straight into the neighbours' buffers (plain stores, no TMA) and synchronises with per-sweep
+    flags.  The symmetric buffers are allocated once for `max_bricks` bricks and reused by every solve (the rendezvous
+    costs milliseconds).  Works with world size 1 (no process group needed)."""
+
+    def __init__(self, ctx, max_bricks):
+        import torch
+        import torch.distributed as dist
+        self.ctx = ctx
+        self.device = torch.device("cuda", ctx.device)
+        self.distributed = dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
+        self.world = dist.get_world_size() if self.distributed else 1
+        self.rank = dist.get_rank() if self.distributed else 0
+        self.max_bricks = int(max_bricks)
+        nfloat = 16 * (self.max_bricks + 9)          # slab-local layout: plane stride rounded up to 8 bricks
+        if self.distributed:
+            import torch.distributed._symmetric_memory as symm_mem
+            group = dist.group.WORLD.group_name
+            self.xa = symm_mem.empty(nfloat, dtype=torch.float32, device=self.device)
+            self.xb = symm_mem.empty(nfloat, dtype=torch.float32, device=self.device)
+            self.flags = symm_mem.empty(512, dtype=torch.int32, device=self.device)
+            ha, hb, hf = (symm_mem.rendezvous(t, group) for t in (self.xa, self.xb, self.flags))
+            self._handles = (ha, hb, hf)
+            self.pa, self.pb, self.pf = list(ha.buffer_ptrs), list(hb.buffer_ptrs), list(hf.buffer_ptrs)
+        else:
+            self.xa = torch.empty(nfloat, dtype=torch.float32, device=self.device)
+            self.xb = torch.empty(nfloat, dtype=torch.float32, device=self.device)
+            self.flags = torch.empty(512, dtype=torch.int32, device=self.device)
+            self.pa, self.pb, self.pf = [self.xa.data_ptr()], [self.xb.data_ptr()], [self.flags.data_ptr()]
+
+    def solve_plan(self, plan, iters=500, timings=None):
+        """Runs the sharded solve on an existing plan; returns the full iterate x [4, Q+1, 4] on every rank."""
+        import torch
+        import torch.distributed as dist
+        if plan.Q > self.max_bricks:
+            raise ValueError("plan has %d bricks, the solver's buffers hold %d" % (plan.Q, self.max_bricks))
+        world, rank = self.world, self.rank
+        cuts = balanced_cuts(plan.plane_off, world)
+        self.flags.zero_()
+        plan._check(plan.lib.mrb_qp_plan_init_x(plan.h, C.c_void_p(self.xa.data_ptr())))
+        plan._check(plan.lib.mrb_qp_plan_init_x(plan.h, C.c_void_p(self.xb.data_ptr())))
+        torch.cuda.current_stream().synchronize()
+        if self.distributed:
+            dist.barrier()                           # every rank's flags are zero and its buffers initialised
+            torch.cuda.current_stream().synchronize()
+        VP = C.c_void_p * world
+        ccuts = (C.c_int * (world + 1))(*cuts)
+        plan._check(plan.lib.mrb_qp_plan_solve_sharded(plan.h, rank, world, VP(*self.pa), VP(*self.pb), VP(*self.pf),
+                                                       ccuts, int(iters)))
+        if timings is not None:
+            timings["kernel_ms"] = float(plan.lib.mrb_qp_plan_last_kernel_ms(plan.h))
+            timings["n_band"] = plan.n_band
+            timings["cuts"] = cuts
+        res = (self.xb if iters % 2 else self.xa)[:16 * (plan.Q + 1)].view(4, plan.Q + 1, 4)
+        q0, q1 = int(plan.plane_off[cuts[rank]]), int(plan.plane_off[cuts[rank + 1]])
+        x = torch.zeros((4, plan.Q + 1, 4), dtype=torch.float32, device=self.device)
+        x[:, q0:q1, :] = res[:, q0:q1, :]
+        if self.distributed:
+            dist.barrier()                           # nobody reuses peer-mapped buffers while a neighbour still runs
+            dist.all_reduce(x)                       # disjoint supports: x + 0 is exact
+        torch.cuda.current_stream().synchronize()    # the library works on its own stream: x must be complete
+        return x
+
+    def solve(self, volume, iters=500, band_size=4, timings=None):
+        """Every rank returns the full F."""
+        plan = Plan(self.ctx, volume, band_size)
+        try:
+            x = self.solve_plan(plan, iters, timings)
+            return plan.assemble(x)
+        finally:
+            plan.close()
+
+    def reconstruct(self, volume, iters=500, band_size=4, isolevel=0.0, timings=None):
+        """The whole path for ONE grid on several GPUs: stages 1-2 on every rank, stage 3 slab-sharded in the fused
+        NVLink kernel, then marching cubes + vertex de-dup of the assembled embedding on every rank's copy of F."""
+        F = self.solve(volume, iters=iters, band_size=band_size, timings=timings)
+        return self.ctx.mcubes(F, isolevel), F
+
+
+def max_bricks_for(shape):
+    """Upper bound of the brick count of a grid (every 2x2x4 brick active), for sizing a FusedSolver."""
+    nx, ny, nz = shape
+    return ((nx + 1) // 2) * ((ny + 1) // 2) * ((nz + 3) // 4)
+
+
+def solve_fused(ctx, volume, iters=500, band_size=4, timings=None):
+    """One-shot convenience wrapper around FusedSolver (allocates the symmetric buffers for this one solve)."""
     plan = Plan(ctx, volume, band_size)
-    cuts = balanced_cuts(plan.plane_off, world)
-    nfloat = 16 * (plan.Q + 9)                       # slab-local layout: plane stride rounded up to 8 bricks
-    if distributed:
-        import torch.distributed._symmetric_memory as symm_mem
-        group = dist.group.WORLD.group_name
-        xa = symm_mem.empty(nfloat, dtype=torch.float32, device=plan.device)
-        xb = symm_mem.empty(nfloat, dtype=torch.float32, device=plan.device)
-        flags = symm_mem.empty(512, dtype=torch.int32, device=plan.device)
-        ha, hb, hf = (symm_mem.rendezvous(t, group) for t in (xa, xb, flags))
-        pa, pb, pf = list(ha.buffer_ptrs), list(hb.buffer_ptrs), list(hf.buffer_ptrs)
-    else:
-        xa = torch.empty(nfloat, dtype=torch.float32, device=plan.device)
-        xb = torch.empty(nfloat, dtype=torch.float32, device=plan.device)
-        flags = torch.empty(512, dtype=torch.int32, device=plan.device)
-        pa, pb, pf = [xa.data_ptr()], [xb.data_ptr()], [flags.data_ptr()]
-    flags.zero_()
-    plan._check(plan.lib.mrb_qp_plan_init_x(plan.h, C.c_void_p(xa.data_ptr())))
-    plan._check(plan.lib.mrb_qp_plan_init_x(plan.h, C.c_void_p(xb.data_ptr())))
-    torch.cuda.synchronize()
-    if distributed:
-        dist.barrier()
-        torch.cuda.synchronize()
-    VP = C.c_void_p * world
-    ccuts = (C.c_int * (world + 1))(*cuts)
-    plan._check(plan.lib.mrb_qp_plan_solve_sharded(plan.h, rank, world, VP(*pa), VP(*pb), VP(*pf), ccuts, int(iters)))
-    if timings is not None:
-        timings["kernel_ms"] = float(plan.lib.mrb_qp_plan_last_kernel_ms(plan.h))
-        timings["n_band"] = plan.n_band
-        timings["cuts"] = cuts
-    res = (xb if iters % 2 else xa)[:16 * (plan.Q + 1)].view(4, plan.Q + 1, 4)
-    q0, q1 = int(plan.plane_off[cuts[rank]]), int(plan.plane_off[cuts[rank + 1]])
-    x = torch.zeros((4, plan.Q + 1, 4), dtype=torch.float32, device=plan.device)
-    x[:, q0:q1, :] = res[:, q0:q1, :]
-    if distributed:
-        dist.barrier()                               # nobody frees peer-mapped buffers while a neighbour still runs
-        dist.all_reduce(x)
-    torch.cuda.synchronize()                         # the library works on its own stream: x must be complete
-    F = plan.assemble(x)
-    plan.close()
-    return F
+    try:
+        solver = FusedSolver(ctx, plan.Q)
+        x = solver.solve_plan(plan, iters, timings)
+        return plan.assemble(x)
+    finally:
+        plan.close()
 
 
 def reconstruct_fused(ctx, volume, iters=500, band_size=4, isolevel=0.0, timings=None):
-    """The whole path for ONE grid on several GPUs: stages 1-2 on every rank (they are a few per cent of a step),
-    stage 3 slab-sharded in the fused NVLink kernel, then marching cubes + vertex de-dup of the assembled embedding.
-    Every rank returns the same (verts, faces): stage 4 is not sharded, it runs on every rank's copy of F."""
+    """One-shot whole path on several GPUs (see FusedSolver.reconstruct); every rank returns the same (verts, faces)."""
     F = solve_fused(ctx, volume, iters=iters, band_size=band_size, timings=timings)
     return ctx.mcubes(F, isolevel)
+
+
+def check_against_single_gpu(ctx, solver, volume, iters=500, band_size=4, reps=3):
+    """Runs the slab-sharded whole path `reps` times and compares it, in the run, with this rank's own single-GPU
+    mrb_reconstruct / mrb_optimize of the same volume (F, vertices and faces, bit for bit; AND over the ranks).
+    Times are device times (CUDA events on the context's stream, which is made torch's current stream so that the
+    NCCL gather of the iterate is ordered on it too), max over ranks.  Returns a dict for bench.py's `slab` record."""
+    import torch
+    import torch.distributed as dist
+    from .dist import max_over_ranks
+    stream = torch.cuda.ExternalStream(ctx.stream, device=solver.device)
+    host = lambda a: a.cpu().numpy() if torch.is_tensor(a) else np.asarray(a)
+    with torch.cuda.stream(stream):
+        F1, st = ctx.optimize(volume, band_size=band_size, iters=iters, return_stats=True)
+        v1, f1 = ctx.reconstruct(volume, band_size=band_size, iters=iters)
+        t = {}
+        (v2, f2), F2 = solver.reconstruct(volume, iters=iters, band_size=band_size, timings=t)      # warm-up + check
+        ok = bool(torch.equal(F1, F2) and np.array_equal(host(f1), host(f2)) and np.array_equal(host(v1), host(v2)))
+        step_ms, solve_ms = [], []
+        for _ in range(reps):
+            torch.cuda.synchronize()
+            if solver.distributed:
+                dist.barrier()
+            e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            (v2, f2), F2 = solver.reconstruct(volume, iters=iters, band_size=band_size, timings=t)
+            e1.record(stream)
+            torch.cuda.synchronize()
+            ok = ok and bool(torch.equal(F1, F2) and np.array_equal(host(f1), host(f2)))
+            step_ms.append(e0.elapsed_time(e1))
+            solve_ms.append(t["kernel_ms"])
+        # single-GPU step for the speed-up
+        torch.cuda.synchronize()
+        e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        ctx.reconstruct(volume, band_size=band_size, iters=iters)
+        e1.record(stream)
+        torch.cuda.synchronize()
+        single_ms = e0.elapsed_time(e1)
+    flag = torch.tensor([1 if ok else 0], device=solver.device)
+    if solver.distributed:
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    step, solve, single = max_over_ranks([float(np.mean(step_ms)), float(np.mean(solve_ms)), single_ms], device=solver.device)
+    B = int(st["n_band"])
+    return {"grid": list(volume.shape), "band_voxels": B, "sweeps": int(iters), "world": solver.world,
+            "bit_identical": bool(int(flag)), "compared": "F, vertices, faces vs this rank's single-GPU mrb_reconstruct, every rank",
+            "solve_ms": solve, "step_ms": step, "single_gpu_step_ms": single, "single_gpu_solve_ms": float(st["ms_qp_kernel"]),
+            "voxel_updates_per_s": B * iters / (step / 1000.0), "speedup_vs_single_gpu_step": single / step,
+            "plane_cuts": t.get("cuts"), "reps": reps}

@@ -167,3 +167,39 @@ def cli_inputs(dirpath, n=40, radius=12.0):
     pts = np.stack([xx[m] + c / n, yy[m] + c / n, np.sqrt(rr[m]) + c / n], 1)
     write_pcd_ascii(pcd, pts)
     return bv, pcd
+
+
+# ---- the same generators on a torch device (the 512^3 volume takes numpy tens of seconds on a busy host) ----------
+def sphere_t(n, radius, center=None, device="cpu"):
+    """synth.sphere evaluated with torch on `device`: the same fp32 operations in the same order, hence the same voxels."""
+    import torch
+    if isinstance(n, int):
+        n = (n, n, n)
+    if center is None:
+        center = [(s - 1) / 2.0 for s in n]
+    ax = [torch.arange(s, dtype=torch.float32, device=device) for s in n]
+    dx = (ax[0] - np.float32(center[0]).item()) ** 2
+    dy = (ax[1] - np.float32(center[1]).item()) ** 2
+    dz = (ax[2] - np.float32(center[2]).item()) ** 2
+    d2 = (dx[:, None, None] + dy[None, :, None]) + dz[None, None, :]
+    return (d2 <= np.float32(radius * radius).item()).to(torch.float32)
+
+
+def config_volume_t(cfg, device="cpu"):
+    """config_volume(cfg) for the sphere-built configs (1, 3, 4) as a torch tensor on `device`."""
+    import torch
+    if cfg == 1:
+        return sphere_t(52, 17.0, device=device)
+    if cfg == 3:
+        return sphere_t(256, 110.0, device=device)
+    if cfg == 4:
+        v = sphere_t(512, 220.0, device=device)
+        rng = np.random.default_rng(4)
+        for _ in range(8):
+            r = rng.uniform(20, 40)
+            u = rng.normal(size=3); u /= np.linalg.norm(u)
+            c = [255.5 + 215.0 * u[i] for i in range(3)]
+            c = [min(max(ci, 6 + r + 1), 512 - 6 - r - 2) for ci in c]
+            v = torch.maximum(v, sphere_t(512, r, c, device=device))
+        return v
+    raise ValueError(cfg)

@@ -82,3 +82,43 @@ def test_reconstruct_with_feature_detection(ctx, O, synth):
     verts_ref, faces_ref = O.mcubes_features(F, smap, n, 0.0, 0.75, 0.8)
     verts, faces = ctx.reconstruct(v, using_features=True)
     assert np.array_equal(faces, faces_ref) and np.array_equal(verts, verts_ref)
+
+
+def test_config2_feature_detection_172(ctx, O, synth):
+    """BASELINE config 2 as stated: 172^3 rotated box + sphere WITH --feature-detection (thresholds 0.75 / 0.8), the
+    whole pipeline of mesh_reconstruction.cpp:123-134 in one call == the oracle's composition, bit for bit."""
+    v = synth.config_volume(2)
+    assert v.shape == (172, 172, 172)
+    s = O.get_surface(v)
+    n = O.surface_normals(v, s)
+    smap = O.index_map(v.shape, s)
+    fm = O.feature_map(v, smap, n, 0.75)
+    assert fm.sum() > 1000                                             # the box edges are detected
+    F = O.optimize(v, fm, using_features=True, brute_edt=False)        # (fast exact EDT == brute force, test_oracle_dfield)
+    verts_ref, faces_ref = O.mcubes_features(F, smap, n, 0.0, 0.75, 0.8)
+    assert np.array_equal(ctx.getSurface(v), s) and np.array_equal(ctx.getSurfaceNormals(v, s), n)
+    assert np.array_equal(ctx.getFeatureMap(v, smap, n, 0.75), fm)
+    assert np.array_equal(ctx.optimize(v, fm, True), F)
+    verts, faces = ctx.reconstruct(v, using_features=True, feature_threshold=0.75, corner_threshold=0.8)
+    assert np.array_equal(faces, faces_ref) and np.array_equal(verts, verts_ref)
+    v0, f0 = ctx.reconstruct(v)                                        # and the default path differs (features are real here)
+    assert len(f0) != len(faces)
+
+
+def test_repeated_feature_calls_on_one_context(synth, O):
+    """Host-buffer feature calls that grow the pinned staging must not invalidate the side buffers (regression:
+    pinned_reserve once freed them): small mesh, then larger meshes, then the first again, all on ONE context."""
+    import mesh_reconstruction_b200 as mrb
+    shapes_ = [synth.box(40, (8, 6, 5), None, 0.0, 0.0), synth.box(56, (13, 10, 8), None, 20.0, 35.0),
+               synth.union(synth.box(64, (18, 14, 10), None, 20.0, 35.0), synth.sphere(64, 14.0))]
+    refs = []
+    for v in shapes_:
+        s = O.get_surface(v)
+        n = O.surface_normals(v, s)
+        smap = O.index_map(v.shape, s)
+        F = O.optimize(v, O.feature_map(v, smap, n, 0.75), using_features=True)
+        refs.append(O.mcubes_features(F, smap, n, 0.0, 0.75, 0.8))
+    with mrb.Context(0) as c:
+        for i in (0, 1, 2, 2, 1, 0, 2):
+            verts, faces = c.reconstruct(shapes_[i], using_features=True)
+            assert np.array_equal(faces, refs[i][1]) and np.array_equal(verts, refs[i][0]), i
