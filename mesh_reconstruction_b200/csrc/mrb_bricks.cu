@@ -19,6 +19,9 @@
 #include "mrb_internal.cuh"
 #include "mrb_compact.cuh"
 
+#include <vector>
+#include <algorithm>
+
 namespace mrb {
 
 #define MRB_VOXEL_LOOP(idx, n) \
@@ -680,9 +683,32 @@ __host__ __device__ __forceinline__ size_t tiled_stride(int Q) { return ((size_t
 struct TiledOrder {
     BrickDims bd;
     int T;
-    __host__ __device__ size_t count() const { return (size_t)((bd.bx + T - 1) / T) * T * bd.by * bd.bz; }
-    // traversal index -> linear brick-grid position (X*by + Y)*bz + Z, or -1 in the padding of the last slab
+    // Morton mode (mx > 0): the brick grid is cut into tiles of mx x my x mz bricks; the tiles are visited in Morton
+    // (Z-curve) order of their coordinates (nbx / nby / nbz bits per axis, interleaved from the least significant bit while
+    // an axis has bits left), the bricks of a tile in (x, y, z) order with z fastest.  A contiguous range of this order
+    // is a compact 3-D patch whatever the orientation of the surface, so the blocks of the sweep kernel have about the
+    // same share of rim bricks everywhere (x-slab order: 33 % in the median, 61 % where the surface is tangent to z).
+    int mx, my, mz, nbx, nby, nbz;
+    __host__ __device__ size_t count() const {
+        if (mx > 0) return ((size_t)1 << (nbx + nby + nbz)) * (size_t)(mx * my * mz);
+        return (size_t)((bd.bx + T - 1) / T) * T * bd.by * bd.bz;
+    }
+    // traversal index -> linear brick-grid position (X*by + Y)*bz + Z, or -1 in the padding
     __host__ __device__ long long position(size_t i) const {
+        if (mx > 0) {
+            const int per = mx * my * mz;
+            const int w = (int)(i % per);
+            size_t m = i / per;
+            int tx = 0, ty = 0, tz = 0;
+            for (int b = 0; b < 16; b++) {
+                if (b < nbx) { tx |= (int)(m & 1) << b; m >>= 1; }
+                if (b < nby) { ty |= (int)(m & 1) << b; m >>= 1; }
+                if (b < nbz) { tz |= (int)(m & 1) << b; m >>= 1; }
+            }
+            const int X = tx * mx + w / (my * mz), Y = ty * my + (w / mz) % my, Z = tz * mz + w % mz;
+            if (X >= bd.bx || Y >= bd.by || Z >= bd.bz) return -1;
+            return ((long long)X * bd.by + Y) * bd.bz + Z;
+        }
         const int Z = (int)(i % bd.bz);
         size_t t = i / bd.bz;
         const int x = (int)(t % T);
@@ -693,6 +719,19 @@ struct TiledOrder {
         return ((long long)X * bd.by + Y) * bd.bz + Z;
     }
 };
+static int bits_for(int n) { int b = 0; while ((1 << b) < n) b++; return b; }
+static TiledOrder make_order(const BrickDims& bd, int tile_T) {
+    TiledOrder o{bd, tile_T, 0, 0, 0, 0, 0, 0};
+    const char* e = getenv("MRB_QP_ORDER");
+    if (e && strncmp(e, "morton", 6) == 0) {
+        int mx = 4, my = 4, mz = 8;
+        if (e[6] == ':') sscanf(e + 7, "%d,%d,%d", &mx, &my, &mz);
+        if (mx < 1) mx = 1; if (my < 1) my = 1; if (mz < 1) mz = 1;
+        o.mx = mx; o.my = my; o.mz = mz;
+        o.nbx = bits_for((bd.bx + mx - 1) / mx); o.nby = bits_for((bd.by + my - 1) / my); o.nbz = bits_for((bd.bz + mz - 1) / mz);
+    }
+    return o;
+}
 // brick activity from the stage-1+2 tile kernel's bitmap: one byte per (brick column, 8 bricks along z)
 struct BrickBitPred {
     const uint8_t* bits;
@@ -987,6 +1026,332 @@ __global__ void __launch_bounds__(Threads, MinBlocks) k_qp_bricks_tiled(const ui
     }
 }
 
+// ---- on-chip sweep kernel: the block's iterate lives in shared memory for all sweeps ----------------------------------
+// k_qp_bricks_tiled above reads the iterate through L1/L2 every sweep (20 LDG.128 + 8 LDG.64 per brick update, L1 hit
+// rate 56 %) and pays, per sweep, a block barrier -> release fence (0.9 us) -> flag hop -> acquire poll chain in front of
+// its rim bricks (measured timeline: profiles/r02_summary.md).  Here
+//   * a block keeps BOTH ping-pong copies of its own bricks in shared memory (2 x 64 B per brick), a copy of the foreign
+//     bricks its rim reads (the HALO, 64 B each) and the constants (signed margins as floats, one predicate byte per
+//     voxel, six 16-bit neighbour slots: 92 B per brick): every load of a sweep is an LDS;
+//   * the only thing other blocks need, the RIM bricks (a neighbour in another block), travels through an exchange buffer
+//     in global memory (L2) in which every 64-bit word carries one fp32 value and the number of the sweep that produced
+//     it.  A 64-bit store is single-copy atomic, so a consumer that reads the expected sweep number has the value too:
+//     no fence, no flag, no release/acquire pair, and the dependency is per brick instead of per block;
+//   * a sweep updates the rim bricks FIRST and sends them at once; while a thread updates its second (interior) brick, its
+//     loads of ONE halo brick for the next sweep are in flight (the producers sent it one interior phase ago); the halo is
+//     put into shared memory between the two block barriers that end the sweep.
+// invdg is not stored: d = 12 T(v) + (number of tight neighbours) is recomputed from the predicate byte (popc) and looked
+// up in the 32-entry table (a conflict-free LDS: distinct entries sit in distinct banks).
+// Write-after-read on the two exchange parities is safe because a producer can only reach sweep s+2 after its neighbours
+// have produced sweep s+1, i.e. after they have consumed sweep s.
+// Shared-memory planes (k = dx*2+dy), S = 2*(CAP+1) + CAPH float4 each:  [buffer 0: own slots 0..CAP][halo][buffer 1,
+// own slots in REVERSE order].  Neighbour slot r (own brick, CAP' = the all-zero dummy brick, CAP+1+h = halo brick h)
+// is element r of a plane in even sweeps and element S-1-r in odd sweeps (the halo is written in that order too), so a
+// sweep addresses everything as base + step * r with step = +-16 bytes and the plane offsets are immediates.
+static const int kTraceFirst = 200, kTraceSweeps = 32;
+static const int kOcCap = 848, kOcHalo = 608, kOcThreadsMax = 480;
+__device__ __forceinline__ unsigned long long gtimer() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+__device__ __forceinline__ unsigned long long ll_pack(float v, unsigned tag) {
+    return (unsigned long long)__float_as_uint(v) | ((unsigned long long)tag << 32);
+}
+__device__ __forceinline__ void ll_store2(ulonglong2* dst, float a, float b, unsigned tag) {
+    asm volatile("st.global.cg.v2.u64 [%0], {%1, %2};" ::"l"(dst), "l"(ll_pack(a, tag)), "l"(ll_pack(b, tag)) : "memory");
+}
+__device__ __forceinline__ ulonglong2 ll_load2(const ulonglong2* src) {
+    ulonglong2 v;
+    asm volatile("ld.global.cg.v2.u64 {%0, %1}, [%2];" : "=l"(v.x), "=l"(v.y) : "l"(src) : "memory");
+    return v;
+}
+__device__ __forceinline__ bool ll_valid(const ulonglong2 (&v)[8], unsigned tag) {
+    bool ok = true;
+#pragma unroll
+    for (int i = 0; i < 8; i++) ok = ok && (unsigned)(v[i].x >> 32) == tag && (unsigned)(v[i].y >> 32) == tag;
+    return ok;
+}
+// Waiting for a late producer: poll ONE word with a pause between the attempts (a waiting warp leaves the SM's issue slots
+// and the L2 to the warps that have work), then load the brick again.
+__device__ __forceinline__ void ll_wait_reload(const ulonglong2* src, unsigned tag, ulonglong2 (&v)[8]) {
+    unsigned spins = 0;
+    for (;;) {
+        unsigned long long w;
+        asm volatile("ld.global.cg.u64 %0, [%1];" : "=l"(w) : "l"(src) : "memory");
+        if ((unsigned)(w >> 32) == tag) {
+#pragma unroll
+            for (int i = 0; i < 8; i++) v[i] = ll_load2(src + i);
+            if (ll_valid(v, tag)) return;
+        }
+        if (++spins == (1u << 22)) __trap();               // a lost producer must not hang the GPU
+        __nanosleep(200);
+    }
+}
+
+// For every brick g and direction d (0 x-, 1 x+, 2 y-, 3 y+, 4 z-, 5 z+) whose neighbour lives in another block o: g is
+// halo brick number hslot[g*6+d] of block o (one number per distinct o), listed in hgid[o*caph + number].
+__global__ void k_onchip_halo(const int4* __restrict__ nbA, const int2* __restrict__ nbB, int Q, int G, int caph,
+                              int* __restrict__ hcount, int* __restrict__ hgid, unsigned short* __restrict__ hslot,
+                              int* __restrict__ hmax) {
+    const int g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= Q) return;
+    const int own = tiled_owner(g, Q, G);
+    const int4 a = nbA[g];
+    const int2 z = nbB[g];
+    const int n[6] = {a.x, a.y, a.z, a.w, z.x, z.y};
+    int o[6], sl[6];
+#pragma unroll
+    for (int d = 0; d < 6; d++) {
+        o[d] = n[d] < Q ? tiled_owner(n[d], Q, G) : own;
+        sl[d] = -1;
+        if (o[d] != own) {
+            for (int e = 0; e < d; e++) if (o[e] == o[d]) sl[d] = sl[e];
+            if (sl[d] < 0) {
+                sl[d] = atomicAdd(&hcount[o[d]], 1);
+                if (sl[d] < caph) hgid[(size_t)o[d] * caph + sl[d]] = g;
+                atomicMax(hmax, sl[d] + 1);
+            }
+        }
+        hslot[(size_t)g * 6 + d] = (unsigned short)(sl[d] < 0 ? 0 : sl[d]);
+    }
+}
+
+template <int CAP, int CAPH>
+struct OnchipLayout {
+    static constexpr int CAPX = CAP + 1;                    // own slots + the dummy brick
+    static constexpr int S = 2 * CAPX + CAPH;               // float4 per plane
+    static constexpr size_t kIterBytes = (size_t)4 * S * 16;
+    static constexpr size_t kBytes = kIterBytes + (size_t)CAP * (64 + 16 + 8 + 4);
+};
+
+// One brick update out of shared memory: slot l, neighbour slots from s_na / s_nz; `cb` = byte address (shared window) of
+// element 0 of plane 0 as the current sweep sees it, `cs` = +-16; `nb` / `ns` the same for the buffer being written.
+template <int CAP, int CAPH>
+__device__ __forceinline__ float onchip_update(int l, unsigned cb, int cs, unsigned nb, int ns, const float4* __restrict__ s_sm,
+                                               const uint4* __restrict__ s_pred,
+                                               const uint2* __restrict__ s_na, const unsigned* __restrict__ s_nz,
+                                               const char* __restrict__ s_inv_bytes, bool rim, ulonglong2* ex_out, unsigned tag_out,
+                                               float4* gout, size_t P, int q, bool to_global, bool want_delta) {
+    using L = OnchipLayout<CAP, CAPH>;
+    constexpr unsigned PS = (unsigned)L::S * 16u;            // plane stride in bytes
+    BrickRegs r;
+    const uint2 na = s_na[l];
+    const unsigned nz = s_nz[l];
+    auto lds4 = [](unsigned addr) {
+        float4 v;
+        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+        return v;
+    };
+    auto lds2 = [](unsigned addr) {
+        float2 v;
+        asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(addr));
+        return v;
+    };
+    const unsigned a_own = cb + (unsigned)(cs * l);
+    const unsigned a_xm = cb + (unsigned)(cs * (int)(na.x & 0xffffu)), a_xp = cb + (unsigned)(cs * (int)(na.x >> 16));
+    const unsigned a_ym = cb + (unsigned)(cs * (int)(na.y & 0xffffu)), a_yp = cb + (unsigned)(cs * (int)(na.y >> 16));
+    const unsigned a_zl = cb + (unsigned)(cs * (int)(nz & 0xffffu)) + 8u, a_zh = cb + (unsigned)(cs * (int)(nz >> 16));
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        put4(r.own[k], lds4(a_own + k * PS));
+        put4(r.xm[k], lds4(a_xm + k * PS));
+        put4(r.xp[k], lds4(a_xp + k * PS));
+        put4(r.ym[k], lds4(a_ym + k * PS));
+        put4(r.yp[k], lds4(a_yp + k * PS));
+        const float2 lo = lds2(a_zl + k * PS), hi = lds2(a_zh + k * PS);
+        r.zl[k][0] = lo.x; r.zl[k][1] = lo.y;
+        r.zh[k][0] = hi.x; r.zh[k][1] = hi.y;
+    }
+    const uint4 pw = s_pred[l];
+    // invdg of the four voxels of a strip: byte j of w = predicate byte (bit 0 T(v), bits 1..6 the six neighbours' T)
+    auto inv4 = [&](uint32_t w) {
+        auto one = [&](uint32_t pb) {
+            const uint32_t d4 = __popc(pb & 0x7eu) * 4u + (pb & 1u) * 48u;       // 4 * (12 T(v) + tight neighbours)
+            return *reinterpret_cast<const float*>(s_inv_bytes + d4);
+        };
+        return make_float4(one(w & 0xffu), one((w >> 8) & 0xffu), one((w >> 16) & 0xffu), one(w >> 24));
+    };
+    const float4 o0 = brick_strip_x<0>(r, pw.x, s_sm[l], inv4(pw.x));
+    const float4 o1 = brick_strip_x<1>(r, pw.y, s_sm[CAP + l], inv4(pw.y));
+    const float4 o2 = brick_strip_x<2>(r, pw.z, s_sm[2 * CAP + l], inv4(pw.z));
+    const float4 o3 = brick_strip_x<3>(r, pw.w, s_sm[3 * CAP + l], inv4(pw.w));
+    if (rim && !to_global) {
+        ulonglong2* dst = ex_out + (size_t)q * 8;
+        ll_store2(dst + 0, o0.x, o0.y, tag_out); ll_store2(dst + 1, o0.z, o0.w, tag_out);
+        ll_store2(dst + 2, o1.x, o1.y, tag_out); ll_store2(dst + 3, o1.z, o1.w, tag_out);
+        ll_store2(dst + 4, o2.x, o2.y, tag_out); ll_store2(dst + 5, o2.z, o2.w, tag_out);
+        ll_store2(dst + 6, o3.x, o3.y, tag_out); ll_store2(dst + 7, o3.z, o3.w, tag_out);
+    }
+    auto sts4 = [](unsigned addr, const float4 v) {
+        asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+    };
+    const unsigned a_out = nb + (unsigned)(ns * l);
+    sts4(a_out, o0); sts4(a_out + PS, o1); sts4(a_out + 2 * PS, o2); sts4(a_out + 3 * PS, o3);
+    if (to_global) { gout[q] = o0; gout[P + q] = o1; gout[2 * P + q] = o2; gout[3 * P + q] = o3; }
+    float dmax = 0.0f;
+    if (want_delta) {
+        const float4 os[4] = {o0, o1, o2, o3};
+#pragma unroll
+        for (int k = 0; k < 4; k++)
+            dmax = fmaxf(fmaxf(dmax, fmaxf(fabsf(os[k].x - r.own[k][0]), fabsf(os[k].y - r.own[k][1]))),
+                         fmaxf(fabsf(os[k].z - r.own[k][2]), fabsf(os[k].w - r.own[k][3])));
+    }
+    return dmax;
+}
+
+// ex: exchange buffer, 2 parities x Q bricks x 16 words of {fp32 value, sweep number}; zeroed by the host before the launch
+// (sweep numbers start at 1, so nothing stale can match).  Sweep `it` consumes number it + 1 (staged into the halo before
+// the sweep starts) and produces number it + 2 into parity it & 1; the set-up publishes the initial iterate as number 1.
+template <int Threads, int CAP, int CAPH, bool Trace>
+__global__ void __launch_bounds__(Threads, 1) k_qp_bricks_onchip(const uint2* __restrict__ code, const uint4* __restrict__ fields,
+                                                                 const int4* __restrict__ nbA, const int2* __restrict__ nbB,
+                                                                 float4* xa, float4* xb, int Q, int iters,
+                                                                 unsigned* __restrict__ maxdelta_bits, const int* __restrict__ blk_nb,
+                                                                 size_t P, ulonglong2* ex, const int* __restrict__ hcount,
+                                                                 const int* __restrict__ hgid, const unsigned short* __restrict__ hslot,
+                                                                 unsigned long long* trace) {
+    using L = OnchipLayout<CAP, CAPH>;
+    constexpr int CAPX = L::CAPX, S = L::S;
+    constexpr unsigned PS = (unsigned)S * 16u;
+    __shared__ float s_sqrt[256];
+    __shared__ float s_inv[32];
+    const int nthreads = (int)blockDim.x;
+    for (int i = threadIdx.x; i < 256; i += nthreads) s_sqrt[i] = c_brick_sqrt[i];
+    if (threadIdx.x < 32) s_inv[threadIdx.x] = c_brick_invdg[threadIdx.x];
+    const int q_begin = tiled_begin(blockIdx.x, Q, gridDim.x);
+    const int q_end = tiled_begin(blockIdx.x + 1, Q, gridDim.x);
+    const int q_int = q_begin + blk_nb[blockIdx.x];          // first interior brick; [q_begin, q_int) are the rim bricks
+    const int nloc = q_end - q_begin;                        // slot nloc = dummy brick (all zero in both buffers)
+    extern __shared__ uint4 s_dyn[];
+    float4* s_x = (float4*)s_dyn;                            // [4][S]
+    float4* s_sm = s_x + 4 * S;                              // [4][CAP]
+    uint4* s_pred = (uint4*)(s_sm + 4 * CAP);
+    uint2* s_na = (uint2*)(s_pred + CAP);
+    unsigned* s_nz = (unsigned*)(s_na + CAP);
+    ulonglong2* ex0 = ex;                                    // parity 0 / 1
+    ulonglong2* ex1 = ex + (size_t)Q * 8;
+    const unsigned xbase = (unsigned)__cvta_generic_to_shared(s_x);
+    __syncthreads();
+    for (int q = q_begin + threadIdx.x; q < q_end; q += nthreads) {
+        const int l = q - q_begin;
+        const int4 a = __ldg(nbA + q);
+        const int2 z = __ldg(nbB + q);
+        const int n[6] = {a.x, a.y, a.z, a.w, z.x, z.y};
+        unsigned sl[6];
+#pragma unroll
+        for (int d = 0; d < 6; d++)
+            sl[d] = (n[d] >= q_begin && n[d] < q_end) ? (unsigned)(n[d] - q_begin)
+                    : (n[d] >= Q ? (unsigned)nloc : (unsigned)(CAPX + hslot[(size_t)n[d] * 6 + (d ^ 1)]));
+        s_na[l] = make_uint2(sl[0] | (sl[1] << 16), sl[2] | (sl[3] << 16));
+        s_nz[l] = sl[4] | (sl[5] << 16);
+        const uint4 f0 = __ldg(fields + q), f1 = __ldg(fields + (size_t)Q + q);
+        const BrickConstsX x = brick_expand(__ldg(code + q), f0, f1, s_sqrt, s_inv);
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            s_sm[k * CAP + l] = x.sm[k];
+            const float4 xv = xa[k * P + q];
+            s_x[k * S + l] = xv;                                        // buffer 0: forward order
+            s_x[k * S + S - 1 - l] = make_float4(0.f, 0.f, 0.f, 0.f);   // buffer 1: reverse order
+            if (q < q_int) {                                            // rim brick: its initial values are "sweep number 1"
+                ll_store2(ex1 + (size_t)q * 8 + 2 * k, xv.x, xv.y, 1u);
+                ll_store2(ex1 + (size_t)q * 8 + 2 * k + 1, xv.z, xv.w, 1u);
+            }
+        }
+        s_pred[l] = x.pred;
+    }
+    if (threadIdx.x < 8) {
+        const int k = threadIdx.x & 3;
+        s_x[k * S + ((threadIdx.x < 4) ? nloc : S - 1 - nloc)] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    // The halo bricks this thread brings in every sweep: brick h = threadIdx.x while it updates its second brick, and --
+    // only threads WITHOUT a second brick (there are nthreads - (nloc - nthreads) of them: checked by the host) -- brick
+    // nthreads + (threadIdx.x - first such thread) in the time the others spend on theirs.
+    const int nh = hcount[blockIdx.x];
+    const bool stager = (int)threadIdx.x < nh;
+    const int first_free = nloc > nthreads ? nloc - nthreads : 0;      // threads >= first_free have one brick at most
+    const int h2 = nthreads + (int)threadIdx.x - first_free;
+    const bool stager2 = (int)threadIdx.x >= first_free && h2 < nh;
+    const int hg = stager ? hgid[(size_t)blockIdx.x * CAPH + threadIdx.x] : 0;
+    const int hg2 = stager2 ? hgid[(size_t)blockIdx.x * CAPH + h2] : 0;
+    auto halo_put = [&](int parity, int h, const ulonglong2 (&v)[8]) {     // halo brick h as the sweep of that parity sees it
+        const int e = parity ? S - 1 - (CAPX + h) : CAPX + h;
+#pragma unroll
+        for (int k = 0; k < 4; k++)
+            s_x[k * S + e] = make_float4(__uint_as_float((unsigned)v[2 * k].x), __uint_as_float((unsigned)v[2 * k].y),
+                                         __uint_as_float((unsigned)v[2 * k + 1].x), __uint_as_float((unsigned)v[2 * k + 1].y));
+    };
+    if (stager) {
+        ulonglong2 hv[8];
+        ll_wait_reload(ex1 + (size_t)hg * 8, 1u, hv);
+        halo_put(0, threadIdx.x, hv);
+    }
+    if (stager2) {
+        ulonglong2 hv[8];
+        ll_wait_reload(ex1 + (size_t)hg2 * 8, 1u, hv);
+        halo_put(0, h2, hv);
+    }
+    const char* s_inv_bytes = reinterpret_cast<const char*>(s_inv);
+    __syncthreads();
+    for (int it = 0; it < iters; it++) {
+        const bool last = it == iters - 1;
+        const int par = it & 1;
+        // element r of the buffer read / written by this sweep: base + step * r
+        const unsigned cb = par ? xbase + (unsigned)(S - 1) * 16u : xbase;
+        const int cs = par ? -16 : 16;
+        const unsigned nb = par ? xbase : xbase + (unsigned)(S - 1) * 16u;
+        const int ns = -cs;
+        float4* gout = par ? xa : xb;
+        ulonglong2* ex_out = par ? ex1 : ex0;                   // this sweep's rim results: number it + 2
+        const unsigned tag_out = (unsigned)it + 2u;
+        float dmax = 0.0f;
+        const bool tr = Trace && it >= kTraceFirst && it < kTraceFirst + kTraceSweeps;
+        unsigned long long* trow = Trace ? trace + ((size_t)blockIdx.x * kTraceSweeps + (it - kTraceFirst)) * 8 : nullptr;
+        if (tr && threadIdx.x == 0) trow[0] = gtimer();
+        // bricks are numbered rim first: a thread's first brick is a rim brick (or one of the first interior bricks)
+        int q = q_begin + threadIdx.x;
+        if (q < q_end) {
+            dmax = onchip_update<CAP, CAPH>(q - q_begin, cb, cs, nb, ns, s_sm, s_pred, s_na, s_nz, s_inv_bytes, q < q_int, ex_out,
+                                            tag_out, gout, P, q, last, last);
+            q += nthreads;
+        }
+        if (tr && threadIdx.x == 0) trow[1] = gtimer();
+        if (tr && (int)threadIdx.x == nthreads - 32) trow[3] = gtimer();
+        for (; q < q_end; q += nthreads)
+            dmax = fmaxf(dmax, onchip_update<CAP, CAPH>(q - q_begin, cb, cs, nb, ns, s_sm, s_pred, s_na, s_nz, s_inv_bytes,
+                                                        q < q_int, ex_out, tag_out, gout, P, q, last, last));
+        if (tr && threadIdx.x == 0) trow[2] = gtimer();
+        if (tr && (int)threadIdx.x == nthreads - 32) trow[4] = gtimer();
+        if (last) {
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) dmax = fmaxf(dmax, __shfl_xor_sync(0xffffffffu, dmax, o));
+            if ((threadIdx.x & 31) == 0) atomicMax(maxdelta_bits, __float_as_uint(dmax));
+        } else {
+            // the neighbours sent this sweep's rim results in THEIR first pass, one interior pass ago: fetch the halo of the
+            // next sweep (one L2 round trip; a late producer is waited for with a sleeping poll)
+            ulonglong2 hv[8], hw[8];
+#pragma unroll
+            for (int i = 0; i < 8; i++) { hv[i] = make_ulonglong2(0ull, 0ull); hw[i] = make_ulonglong2(0ull, 0ull); }
+            if (stager) {
+#pragma unroll
+                for (int i = 0; i < 8; i++) hv[i] = ll_load2(ex_out + (size_t)hg * 8 + i);
+            }
+            if (stager2) {
+#pragma unroll
+                for (int i = 0; i < 8; i++) hw[i] = ll_load2(ex_out + (size_t)hg2 * 8 + i);
+            }
+            if (stager && !ll_valid(hv, tag_out)) ll_wait_reload(ex_out + (size_t)hg * 8, tag_out, hv);
+            if (stager2 && !ll_valid(hw, tag_out)) ll_wait_reload(ex_out + (size_t)hg2 * 8, tag_out, hw);
+            if (tr && threadIdx.x == 0) trow[5] = gtimer();
+            __syncthreads();        // every read of this sweep (own slots, halo) is done
+            if (stager) halo_put(par ^ 1, threadIdx.x, hv);
+            if (stager2) halo_put(par ^ 1, h2, hw);
+            __syncthreads();        // the next sweep's inputs are complete
+            if (tr && threadIdx.x == 0) trow[6] = gtimer();
+        }
+    }
+}
+
 // ---- feature reset + F assembly ---------------------------------------------------------------------------------
 __device__ __forceinline__ size_t brick_slot(const int* __restrict__ bid, const BrickDims& bd, size_t P, size_t idx) {
     int z = (int)(idx % bd.nz);
@@ -1069,7 +1434,7 @@ int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_
     int t_grid = 0, t_fit = 0;
     int* blk_nb = nullptr;
     int* tpos = nullptr;
-    const TiledOrder ord{bd, tile_T};
+    const TiledOrder ord = make_order(bd, tile_T);
     const BrickBitPred bitpred{brick_bits, bd, (d.nz + 31) / 32};
     if (tiled && brick_bits) MRB_TRY(compact(ctx, TiledBrickPred<BrickBitPred>{bitpred, ord}, ord.count(), &tpos, &Q));
     else if (tiled) MRB_TRY(compact(ctx, TiledBrickPred<ActiveBrickPred>{ActiveBrickPred{flags, bd}, ord}, ord.count(), &tpos, &Q));
@@ -1173,14 +1538,84 @@ int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_
             if (getenv("MRB_QP_BRICK_NOSMEM") || smem > 96 * 1024 / (size_t)t_fit) { if (!expanded) { cap = 0; smem = 0; } }
             if (smem > 48 * 1024) MRB_CUDA(cudaFuncSetAttribute(t_kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
             int its = iters, QQ = Q;
-            TShard no_shard;
-            memset(&no_shard, 0, sizeof(no_shard));
-            void* args[] = {(void*)&code, (void*)&fields, (void*)&nbA, (void*)&nbB, (void*)&xa, (void*)&xb, (void*)&QQ, (void*)&its,
-                            (void*)&md, (void*)&bar, (void*)&dbg, (void*)&blk_nb, (void*)&progress, (void*)&cap, (void*)&plist, (void*)&pcount,
-                            (void*)&expanded, (void*)&P, (void*)&no_shard};
-            MRB_CUDA(cudaEventRecord(ctx->ev[6], ctx->stream));
-            MRB_CUDA(cudaLaunchCooperativeKernel(t_kern, dim3(grid), dim3(t_threads), args, smem, ctx->stream));
-            MRB_CUDA(cudaEventRecord(ctx->ev[7], ctx->stream));
+            // On-chip kernel (the block's iterate in shared memory for all sweeps): binary volumes whose per-block share fits
+            // (up to kOcCap bricks and kOcHalo foreign neighbour bricks per SM: band 4 up to about 256^3); MRB_QP_ONCHIP=0
+            // selects the tiled kernel.
+            const int need_cap = (Q + grid - 1) / grid + 9;
+            const char* eoc = getenv("MRB_QP_ONCHIP");
+            bool onchip = binary_volume && t_fit == 1 && !(dbg & 5) && !(eoc && atoi(eoc) == 0) && need_cap <= kOcCap &&
+                          (t_threads == 480 || t_threads < 480);
+            int oc_threads = t_threads;
+            int *hcount = nullptr, *hgid = nullptr;
+            unsigned short* hslot = nullptr;
+            if (onchip) {
+                int* hmax = ctx->d_mail + 51;
+                MRB_TRY(arena_alloc(ctx, (size_t)grid, &hcount));
+                MRB_TRY(arena_alloc(ctx, (size_t)grid * kOcHalo, &hgid));
+                MRB_TRY(arena_alloc(ctx, (size_t)Q * 6, &hslot));
+                MRB_CUDA(cudaMemsetAsync(hcount, 0, (size_t)grid * sizeof(int), ctx->stream));
+                MRB_CUDA(cudaMemsetAsync(hmax, 0, sizeof(int), ctx->stream));
+                MRB_LAUNCH(ctx, k_onchip_halo, cdiv(Q, 256), 256, 0, nbA, nbB, Q, grid, kOcHalo, hcount, hgid, hslot, hmax);
+                int hm = 0;
+                MRB_TRY(read_int(ctx, hmax, &hm));
+                if (getenv("MRB_QP_VERBOSE")) {
+                    std::vector<int> hb(grid), hh(grid);
+                    MRB_CUDA(cudaMemcpyAsync(hb.data(), blk_nb, grid * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+                    MRB_CUDA(cudaMemcpyAsync(hh.data(), hcount, grid * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+                    MRB_CUDA(cudaStreamSynchronize(ctx->stream));
+                    std::sort(hb.begin(), hb.end()); std::sort(hh.begin(), hh.end());
+                    fprintf(stderr, "mrb: rim bricks per block min %d p25 %d median %d p75 %d p90 %d max %d; halo min %d median %d p90 %d max %d\n",
+                            hb[0], hb[grid / 4], hb[grid / 2], hb[3 * grid / 4], hb[9 * grid / 10], hb[grid - 1], hh[0], hh[grid / 2], hh[9 * grid / 10], hh[grid - 1]);
+                }
+                if (getenv("MRB_QP_VERBOSE")) fprintf(stderr, "mrb: on-chip kernel: %d bricks per block (cap %d), largest halo %d (cap %d), %d threads\n", need_cap, kOcCap, hm, kOcHalo, oc_threads > t_threads ? oc_threads : (hm > oc_threads ? (hm + 31) / 32 * 32 : oc_threads));
+                // one halo brick per thread, a second one for the threads that have no second brick to update
+                const int nloc_max = need_cap - 9 + 8;
+                const int spare = nloc_max > oc_threads ? 2 * oc_threads - nloc_max : oc_threads;
+                if (hm > kOcHalo || hm > oc_threads + (spare > 0 ? spare : 0) || nloc_max > 2 * oc_threads) onchip = false;
+            }
+            if (onchip) {
+                typedef OnchipLayout<kOcCap, kOcHalo> OL;
+                void* oc_kern = (void*)k_qp_bricks_onchip<kOcThreadsMax, kOcCap, kOcHalo, false>;
+                unsigned long long* trace = nullptr;
+                const bool want_trace = getenv("MRB_QP_TRACE") && atoi(getenv("MRB_QP_TRACE")) && iters >= kTraceFirst + kTraceSweeps;
+                if (want_trace) {
+                    oc_kern = (void*)k_qp_bricks_onchip<kOcThreadsMax, kOcCap, kOcHalo, true>;
+                    MRB_TRY(arena_alloc(ctx, (size_t)grid * kTraceSweeps * 8, &trace));
+                    MRB_CUDA(cudaMemsetAsync(trace, 0, (size_t)grid * kTraceSweeps * 8 * sizeof(unsigned long long), ctx->stream));
+                }
+                // exchange buffer of the rim bricks: 2 parities x Q bricks x 16 words {value, sweep number}, numbers start at 1
+                ulonglong2* ex = nullptr;
+                MRB_TRY(arena_alloc(ctx, (size_t)Q * 16, &ex));
+                MRB_CUDA(cudaMemsetAsync(ex, 0, (size_t)Q * 16 * sizeof(ulonglong2), ctx->stream));
+                MRB_CUDA(cudaFuncSetAttribute(oc_kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)OL::kBytes));
+                void* args[] = {(void*)&code, (void*)&fields, (void*)&nbA, (void*)&nbB, (void*)&xa, (void*)&xb, (void*)&QQ, (void*)&its,
+                                (void*)&md, (void*)&blk_nb, (void*)&P, (void*)&ex, (void*)&hcount, (void*)&hgid, (void*)&hslot, (void*)&trace};
+                MRB_CUDA(cudaEventRecord(ctx->ev[6], ctx->stream));
+                MRB_CUDA(cudaLaunchCooperativeKernel(oc_kern, dim3(grid), dim3(oc_threads), args, OL::kBytes, ctx->stream));
+                MRB_CUDA(cudaEventRecord(ctx->ev[7], ctx->stream));
+                if (want_trace) {
+                    // tuning aid: dump the stamps (ns) for tools/qp_trace.py
+                    std::vector<unsigned long long> h((size_t)grid * kTraceSweeps * 8);
+                    MRB_CUDA(cudaMemcpyAsync(h.data(), trace, h.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
+                    MRB_CUDA(cudaStreamSynchronize(ctx->stream));
+                    const char* path = getenv("MRB_QP_TRACE_FILE") ? getenv("MRB_QP_TRACE_FILE") : "qp_trace.bin";
+                    if (FILE* f = fopen(path, "wb")) {
+                        int hdr[4] = {grid, kTraceSweeps, 8, 0};
+                        fwrite(hdr, sizeof(int), 4, f);
+                        fwrite(h.data(), sizeof(unsigned long long), h.size(), f);
+                        fclose(f);
+                    }
+                }
+            } else {
+                TShard no_shard;
+                memset(&no_shard, 0, sizeof(no_shard));
+                void* args[] = {(void*)&code, (void*)&fields, (void*)&nbA, (void*)&nbB, (void*)&xa, (void*)&xb, (void*)&QQ, (void*)&its,
+                                (void*)&md, (void*)&bar, (void*)&dbg, (void*)&blk_nb, (void*)&progress, (void*)&cap, (void*)&plist, (void*)&pcount,
+                                (void*)&expanded, (void*)&P, (void*)&no_shard};
+                MRB_CUDA(cudaEventRecord(ctx->ev[6], ctx->stream));
+                MRB_CUDA(cudaLaunchCooperativeKernel(t_kern, dim3(grid), dim3(t_threads), args, smem, ctx->stream));
+                MRB_CUDA(cudaEventRecord(ctx->ev[7], ctx->stream));
+            }
             ctx->launches++;
             xres = (iters % 2) ? (const float*)xb : (const float*)xa;
             // the residual travels to h_mail[8] with the stream; the caller reads it after its own synchronisation
