@@ -1059,7 +1059,7 @@ __device__ __forceinline__ unsigned long long ll_pack(float v, unsigned tag) {
     return (unsigned long long)__float_as_uint(v) | ((unsigned long long)tag << 32);
 }
 __device__ __forceinline__ void ll_store2(ulonglong2* dst, float a, float b, unsigned tag) {
-    asm volatile("st.global.cg.v2.u64 [%0], {%1, %2};" ::"l"(dst), "l"(ll_pack(a, tag)), "l"(ll_pack(b, tag)) : "memory");
+    asm volatile("st.global.v2.u64 [%0], {%1, %2};" ::"l"(dst), "l"(ll_pack(a, tag)), "l"(ll_pack(b, tag)) : "memory");
 }
 __device__ __forceinline__ ulonglong2 ll_load2(const ulonglong2* src) {
     ulonglong2 v;
@@ -1122,44 +1122,38 @@ struct OnchipLayout {
     static constexpr int CAPX = CAP + 1;                    // own slots + the dummy brick
     static constexpr int S = 2 * CAPX + CAPH;               // float4 per plane
     static constexpr size_t kIterBytes = (size_t)4 * S * 16;
-    static constexpr size_t kBytes = kIterBytes + (size_t)CAP * (64 + 16 + 8 + 4);
+    static constexpr size_t kBytes = kIterBytes + (size_t)CAP * (64 + 16 + 8 + 4) + (size_t)CAPH * 4;
 };
 
 // One brick update out of shared memory: slot l, neighbour slots from s_na / s_nz; `cb` = byte address (shared window) of
 // element 0 of plane 0 as the current sweep sees it, `cs` = +-16; `nb` / `ns` the same for the buffer being written.
 template <int CAP, int CAPH>
-__device__ __forceinline__ float onchip_update(int l, unsigned cb, int cs, unsigned nb, int ns, const float4* __restrict__ s_sm,
-                                               const uint4* __restrict__ s_pred,
-                                               const uint2* __restrict__ s_na, const unsigned* __restrict__ s_nz,
-                                               const char* __restrict__ s_inv_bytes, bool rim, ulonglong2* ex_out, unsigned tag_out,
+__device__ __forceinline__ float onchip_update(int l, float4* __restrict__ s_x, int c0, int cs, int n0, const float4* __restrict__ s_sm,
+                                               const uint4* __restrict__ s_pred, const uint2* __restrict__ s_na,
+                                               const unsigned* __restrict__ s_nz, const char* __restrict__ s_inv_bytes,
                                                float4* gout, size_t P, int q, bool to_global, bool want_delta) {
+    // element r of the buffer this sweep reads: s_x[k*S + c0 + cs*r] (cs = +-1); of the buffer it writes: s_x[k*S + n0 - cs*r]
     using L = OnchipLayout<CAP, CAPH>;
-    constexpr unsigned PS = (unsigned)L::S * 16u;            // plane stride in bytes
+    constexpr int S = L::S;
     BrickRegs r;
     const uint2 na = s_na[l];
     const unsigned nz = s_nz[l];
-    auto lds4 = [](unsigned addr) {
-        float4 v;
-        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
-        return v;
-    };
-    auto lds2 = [](unsigned addr) {
-        float2 v;
-        asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(addr));
-        return v;
-    };
-    const unsigned a_own = cb + (unsigned)(cs * l);
-    const unsigned a_xm = cb + (unsigned)(cs * (int)(na.x & 0xffffu)), a_xp = cb + (unsigned)(cs * (int)(na.x >> 16));
-    const unsigned a_ym = cb + (unsigned)(cs * (int)(na.y & 0xffffu)), a_yp = cb + (unsigned)(cs * (int)(na.y >> 16));
-    const unsigned a_zl = cb + (unsigned)(cs * (int)(nz & 0xffffu)) + 8u, a_zh = cb + (unsigned)(cs * (int)(nz >> 16));
+    const float4* p_own = s_x + c0 + cs * l;
+    const float4* p_xm = s_x + c0 + cs * (int)(na.x & 0xffffu);
+    const float4* p_xp = s_x + c0 + cs * (int)(na.x >> 16);
+    const float4* p_ym = s_x + c0 + cs * (int)(na.y & 0xffffu);
+    const float4* p_yp = s_x + c0 + cs * (int)(na.y >> 16);
+    const float4* p_zl = s_x + c0 + cs * (int)(nz & 0xffffu);
+    const float4* p_zh = s_x + c0 + cs * (int)(nz >> 16);
 #pragma unroll
     for (int k = 0; k < 4; k++) {
-        put4(r.own[k], lds4(a_own + k * PS));
-        put4(r.xm[k], lds4(a_xm + k * PS));
-        put4(r.xp[k], lds4(a_xp + k * PS));
-        put4(r.ym[k], lds4(a_ym + k * PS));
-        put4(r.yp[k], lds4(a_yp + k * PS));
-        const float2 lo = lds2(a_zl + k * PS), hi = lds2(a_zh + k * PS);
+        put4(r.own[k], p_own[k * S]);
+        put4(r.xm[k], p_xm[k * S]);
+        put4(r.xp[k], p_xp[k * S]);
+        put4(r.ym[k], p_ym[k * S]);
+        put4(r.yp[k], p_yp[k * S]);
+        const float2 lo = *reinterpret_cast<const float2*>(reinterpret_cast<const float*>(p_zl + k * S) + 2);
+        const float2 hi = *reinterpret_cast<const float2*>(p_zh + k * S);
         r.zl[k][0] = lo.x; r.zl[k][1] = lo.y;
         r.zh[k][0] = hi.x; r.zh[k][1] = hi.y;
     }
@@ -1176,18 +1170,8 @@ __device__ __forceinline__ float onchip_update(int l, unsigned cb, int cs, unsig
     const float4 o1 = brick_strip_x<1>(r, pw.y, s_sm[CAP + l], inv4(pw.y));
     const float4 o2 = brick_strip_x<2>(r, pw.z, s_sm[2 * CAP + l], inv4(pw.z));
     const float4 o3 = brick_strip_x<3>(r, pw.w, s_sm[3 * CAP + l], inv4(pw.w));
-    if (rim && !to_global) {
-        ulonglong2* dst = ex_out + (size_t)q * 8;
-        ll_store2(dst + 0, o0.x, o0.y, tag_out); ll_store2(dst + 1, o0.z, o0.w, tag_out);
-        ll_store2(dst + 2, o1.x, o1.y, tag_out); ll_store2(dst + 3, o1.z, o1.w, tag_out);
-        ll_store2(dst + 4, o2.x, o2.y, tag_out); ll_store2(dst + 5, o2.z, o2.w, tag_out);
-        ll_store2(dst + 6, o3.x, o3.y, tag_out); ll_store2(dst + 7, o3.z, o3.w, tag_out);
-    }
-    auto sts4 = [](unsigned addr, const float4 v) {
-        asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
-    };
-    const unsigned a_out = nb + (unsigned)(ns * l);
-    sts4(a_out, o0); sts4(a_out + PS, o1); sts4(a_out + 2 * PS, o2); sts4(a_out + 3 * PS, o3);
+    float4* p_out = s_x + n0 - cs * l;
+    p_out[0] = o0; p_out[S] = o1; p_out[2 * S] = o2; p_out[3 * S] = o3;
     if (to_global) { gout[q] = o0; gout[P + q] = o1; gout[2 * P + q] = o2; gout[3 * P + q] = o3; }
     float dmax = 0.0f;
     if (want_delta) {
@@ -1210,7 +1194,7 @@ __global__ void __launch_bounds__(Threads, 1) k_qp_bricks_onchip(const uint2* __
                                                                  unsigned* __restrict__ maxdelta_bits, const int* __restrict__ blk_nb,
                                                                  size_t P, ulonglong2* ex, const int* __restrict__ hcount,
                                                                  const int* __restrict__ hgid, const unsigned short* __restrict__ hslot,
-                                                                 unsigned long long* trace) {
+                                                                 int mode, unsigned long long* trace) {
     using L = OnchipLayout<CAP, CAPH>;
     constexpr int CAPX = L::CAPX, S = L::S;
     constexpr unsigned PS = (unsigned)S * 16u;
@@ -1231,7 +1215,6 @@ __global__ void __launch_bounds__(Threads, 1) k_qp_bricks_onchip(const uint2* __
     unsigned* s_nz = (unsigned*)(s_na + CAP);
     ulonglong2* ex0 = ex;                                    // parity 0 / 1
     ulonglong2* ex1 = ex + (size_t)Q * 8;
-    const unsigned xbase = (unsigned)__cvta_generic_to_shared(s_x);
     __syncthreads();
     for (int q = q_begin + threadIdx.x; q < q_end; q += nthreads) {
         const int l = q - q_begin;
@@ -1253,10 +1236,6 @@ __global__ void __launch_bounds__(Threads, 1) k_qp_bricks_onchip(const uint2* __
             const float4 xv = xa[k * P + q];
             s_x[k * S + l] = xv;                                        // buffer 0: forward order
             s_x[k * S + S - 1 - l] = make_float4(0.f, 0.f, 0.f, 0.f);   // buffer 1: reverse order
-            if (q < q_int) {                                            // rim brick: its initial values are "sweep number 1"
-                ll_store2(ex1 + (size_t)q * 8 + 2 * k, xv.x, xv.y, 1u);
-                ll_store2(ex1 + (size_t)q * 8 + 2 * k + 1, xv.z, xv.w, 1u);
-            }
         }
         s_pred[l] = x.pred;
     }
@@ -1264,43 +1243,89 @@ __global__ void __launch_bounds__(Threads, 1) k_qp_bricks_onchip(const uint2* __
         const int k = threadIdx.x & 3;
         s_x[k * S + ((threadIdx.x < 4) ? nloc : S - 1 - nloc)] = make_float4(0.f, 0.f, 0.f, 0.f);
     }
-    // The halo bricks this thread brings in every sweep: brick h = threadIdx.x while it updates its second brick, and --
-    // only threads WITHOUT a second brick (there are nthreads - (nloc - nthreads) of them: checked by the host) -- brick
-    // nthreads + (threadIdx.x - first such thread) in the time the others spend on theirs.
+    // The exchange is WARP-COOPERATIVE so that every global access is a full 128-byte line per brick: lane L of a warp
+    // handles piece L % 8 (16 bytes: two {value, number} words) of brick L / 8 of a group of four bricks.  (One thread
+    // reading or writing "its" brick in eight 16-byte pieces touches 32 different lines per warp instruction: measured,
+    // that alone took 6 us per sweep.)
+    //   send: after a warp has updated its 32 bricks of a pass, it copies the rim bricks among them from the freshly
+    //         written shared-memory planes into the exchange buffer (8 coalesced STG.128);
+    //   fetch: groups of four halo bricks, 133 groups for the largest halo: LDG.128, number check with a warp vote,
+    //         STS.64 into the halo slots as the next sweep will address them.
+    // Passes: a thread updates bricks q_begin + threadIdx.x + p * nthreads, p = 0 .. npass-1 (rim bricks first).
+    // Fast path (two passes, every rim brick in the first one, at least one warp without a brick in the second): those
+    // FREE warps fetch the halo of the next sweep while the others update their second brick; they know that the rim
+    // bricks are done (nobody reads the halo any more) from a split barrier: the busy warps arrive on barrier 1 after the
+    // first pass without waiting, the free warps wait on it.  Otherwise: all warps fetch after the last pass, between
+    // two block barriers.
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nwarps = nthreads >> 5;
+    const int npass = (nloc + nthreads - 1) / nthreads;
     const int nh = hcount[blockIdx.x];
-    const bool stager = (int)threadIdx.x < nh;
-    const int first_free = nloc > nthreads ? nloc - nthreads : 0;      // threads >= first_free have one brick at most
-    const int h2 = nthreads + (int)threadIdx.x - first_free;
-    const bool stager2 = (int)threadIdx.x >= first_free && h2 < nh;
-    const int hg = stager ? hgid[(size_t)blockIdx.x * CAPH + threadIdx.x] : 0;
-    const int hg2 = stager2 ? hgid[(size_t)blockIdx.x * CAPH + h2] : 0;
-    auto halo_put = [&](int parity, int h, const ulonglong2 (&v)[8]) {     // halo brick h as the sweep of that parity sees it
-        const int e = parity ? S - 1 - (CAPX + h) : CAPX + h;
+    int* s_hgid = (int*)(s_nz + CAP);
+    for (int h = threadIdx.x; h < nh; h += nthreads) s_hgid[h] = hgid[(size_t)blockIdx.x * CAPH + h];
+    const int nrim = q_int - q_begin;
+    const int first_free_warp = (nloc - (npass - 1) * nthreads + 31) >> 5;      // warps >= this have no brick in the last pass
+    const int nfree = nwarps - first_free_warp;
+    const bool fast = npass == 2 && nrim <= nthreads && nfree >= 1 && !(mode & 2);
+    const bool free_warp = fast && wid >= first_free_warp;
+    const int sync_count = nthreads;
+    auto send = [&](int q0, int n0, int cs, ulonglong2* ex_out, unsigned tag) {
+        // bricks q0 .. q0+31 of this warp's pass; rim bricks are those below q_int
 #pragma unroll
-        for (int k = 0; k < 4; k++)
-            s_x[k * S + e] = make_float4(__uint_as_float((unsigned)v[2 * k].x), __uint_as_float((unsigned)v[2 * k].y),
-                                         __uint_as_float((unsigned)v[2 * k + 1].x), __uint_as_float((unsigned)v[2 * k + 1].y));
+        for (int i = 0; i < 8; i++) {
+            const int qb = q0 + 4 * i + (lane >> 3);
+            if (qb < q_int) {
+                const int piece = lane & 7;
+                const float2 v = *reinterpret_cast<const float2*>(
+                    reinterpret_cast<const float*>(s_x + (piece >> 1) * S + n0 - cs * (qb - q_begin)) + 2 * (piece & 1));
+                ll_store2(ex_out + (size_t)qb * 8 + piece, v.x, v.y, tag);
+            }
+        }
     };
-    if (stager) {
-        ulonglong2 hv[8];
-        ll_wait_reload(ex1 + (size_t)hg * 8, 1u, hv);
-        halo_put(0, threadIdx.x, hv);
-    }
-    if (stager2) {
-        ulonglong2 hv[8];
-        ll_wait_reload(ex1 + (size_t)hg2 * 8, 1u, hv);
-        halo_put(0, h2, hv);
-    }
+    // fetch groups g = w0, w0 + nw, ... of the halo for the sweep of parity `parity`, numbers `tag`
+    auto fetch = [&](int w0, int nw, const ulonglong2* ex_in, unsigned tag, int parity) {
+        const int ngroups = (nh + 3) >> 2;
+        for (int g0 = w0; g0 < ngroups; g0 += nw * 4) {
+            ulonglong2 v[4];
+            int hb[4];
+            bool ok[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                hb[u] = 4 * (g0 + u * nw) + (lane >> 3);
+                ok[u] = true;
+                if (g0 + u * nw < ngroups && hb[u] < nh) v[u] = ll_load2(ex_in + (size_t)s_hgid[hb[u]] * 8 + (lane & 7));
+            }
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                if (g0 + u * nw >= ngroups) continue;                    // warp-uniform
+                const bool mine = hb[u] < nh;
+                unsigned spins = 0;
+                for (;;) {
+                    const bool good = !mine || ((unsigned)(v[u].x >> 32) == tag && (unsigned)(v[u].y >> 32) == tag);
+                    if (__all_sync(0xffffffffu, good)) break;
+                    if (++spins == (1u << 22)) __trap();                 // a lost producer must not hang the GPU
+                    __nanosleep(100);
+                    if (mine) v[u] = ll_load2(ex_in + (size_t)s_hgid[hb[u]] * 8 + (lane & 7));
+                }
+                if (mine) {
+                    const int piece = lane & 7;
+                    const int e = parity ? S - 1 - (CAPX + hb[u]) : CAPX + hb[u];
+                    *reinterpret_cast<float2*>(reinterpret_cast<float*>(s_x + (piece >> 1) * S + e) + 2 * (piece & 1)) =
+                        make_float2(__uint_as_float((unsigned)v[u].x), __uint_as_float((unsigned)v[u].y));
+                }
+            }
+        }
+    };
+    __syncthreads();
+    // the initial iterate of the rim bricks is "number 1"; fetch the halo of sweep 0
+    for (int q0 = q_begin + wid * 32; q0 < q_int; q0 += nthreads) send(q0, 0, -1, ex1, 1u);      // buffer 0, forward order
+    fetch(wid, nwarps, ex1, 1u, 0);
     const char* s_inv_bytes = reinterpret_cast<const char*>(s_inv);
     __syncthreads();
     for (int it = 0; it < iters; it++) {
         const bool last = it == iters - 1;
         const int par = it & 1;
-        // element r of the buffer read / written by this sweep: base + step * r
-        const unsigned cb = par ? xbase + (unsigned)(S - 1) * 16u : xbase;
-        const int cs = par ? -16 : 16;
-        const unsigned nb = par ? xbase : xbase + (unsigned)(S - 1) * 16u;
-        const int ns = -cs;
+        // element r of the buffer read by this sweep: c0 + cs * r; of the buffer it writes: n0 - cs * r
+        const int c0 = par ? S - 1 : 0, cs = par ? -1 : 1, n0 = par ? 0 : S - 1;
         float4* gout = par ? xa : xb;
         ulonglong2* ex_out = par ? ex1 : ex0;                   // this sweep's rim results: number it + 2
         const unsigned tag_out = (unsigned)it + 2u;
@@ -1308,46 +1333,41 @@ __global__ void __launch_bounds__(Threads, 1) k_qp_bricks_onchip(const uint2* __
         const bool tr = Trace && it >= kTraceFirst && it < kTraceFirst + kTraceSweeps;
         unsigned long long* trow = Trace ? trace + ((size_t)blockIdx.x * kTraceSweeps + (it - kTraceFirst)) * 8 : nullptr;
         if (tr && threadIdx.x == 0) trow[0] = gtimer();
-        // bricks are numbered rim first: a thread's first brick is a rim brick (or one of the first interior bricks)
         int q = q_begin + threadIdx.x;
-        if (q < q_end) {
-            dmax = onchip_update<CAP, CAPH>(q - q_begin, cb, cs, nb, ns, s_sm, s_pred, s_na, s_nz, s_inv_bytes, q < q_int, ex_out,
-                                            tag_out, gout, P, q, last, last);
-            q += nthreads;
+        for (int p = 0; p < npass; p++, q += nthreads) {
+            if (fast && p == 1 && free_warp) break;
+            if (q < q_end)
+                dmax = fmaxf(dmax, onchip_update<CAP, CAPH>(q - q_begin, s_x, c0, cs, n0, s_sm, s_pred, s_na, s_nz, s_inv_bytes,
+                                                            gout, P, q, last, last));
+            const int q0 = q - lane;                                     // first brick of this warp in this pass
+            if (!last && q0 < q_int) {
+                __syncwarp();                                            // the warp's results are in shared memory
+                send(q0, n0, cs, ex_out, tag_out);
+            }
+            if (tr && threadIdx.x == 0 && p == 0) trow[1] = gtimer();
+            if (tr && (int)threadIdx.x == nthreads - 32 && p == 0) trow[3] = gtimer();
+            if (fast && p == 0 && !last) {
+                // every rim brick of the block is in this pass: after it nobody reads the halo any more
+                if (free_warp) asm volatile("barrier.cta.sync 1, %0;" ::"r"(sync_count) : "memory");
+                else asm volatile("barrier.cta.arrive 1, %0;" ::"r"(sync_count) : "memory");
+            }
         }
-        if (tr && threadIdx.x == 0) trow[1] = gtimer();
-        if (tr && (int)threadIdx.x == nthreads - 32) trow[3] = gtimer();
-        for (; q < q_end; q += nthreads)
-            dmax = fmaxf(dmax, onchip_update<CAP, CAPH>(q - q_begin, cb, cs, nb, ns, s_sm, s_pred, s_na, s_nz, s_inv_bytes,
-                                                        q < q_int, ex_out, tag_out, gout, P, q, last, last));
         if (tr && threadIdx.x == 0) trow[2] = gtimer();
-        if (tr && (int)threadIdx.x == nthreads - 32) trow[4] = gtimer();
         if (last) {
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) dmax = fmaxf(dmax, __shfl_xor_sync(0xffffffffu, dmax, o));
             if ((threadIdx.x & 31) == 0) atomicMax(maxdelta_bits, __float_as_uint(dmax));
-        } else {
-            // the neighbours sent this sweep's rim results in THEIR first pass, one interior pass ago: fetch the halo of the
-            // next sweep (one L2 round trip; a late producer is waited for with a sleeping poll)
-            ulonglong2 hv[8], hw[8];
-#pragma unroll
-            for (int i = 0; i < 8; i++) { hv[i] = make_ulonglong2(0ull, 0ull); hw[i] = make_ulonglong2(0ull, 0ull); }
-            if (stager) {
-#pragma unroll
-                for (int i = 0; i < 8; i++) hv[i] = ll_load2(ex_out + (size_t)hg * 8 + i);
-            }
-            if (stager2) {
-#pragma unroll
-                for (int i = 0; i < 8; i++) hw[i] = ll_load2(ex_out + (size_t)hg2 * 8 + i);
-            }
-            if (stager && !ll_valid(hv, tag_out)) ll_wait_reload(ex_out + (size_t)hg * 8, tag_out, hv);
-            if (stager2 && !ll_valid(hw, tag_out)) ll_wait_reload(ex_out + (size_t)hg2 * 8, tag_out, hw);
+        } else if (fast) {
+            if (free_warp) fetch(wid - first_free_warp, nfree, ex_out, tag_out, par ^ 1);
+            if (tr && (int)threadIdx.x == nthreads - 32) trow[4] = gtimer();
+            __syncthreads();        // the next sweep's inputs (own planes, halo) are complete
             if (tr && threadIdx.x == 0) trow[5] = gtimer();
+        } else {
             __syncthreads();        // every read of this sweep (own slots, halo) is done
-            if (stager) halo_put(par ^ 1, threadIdx.x, hv);
-            if (stager2) halo_put(par ^ 1, h2, hw);
+            fetch(wid, nwarps, ex_out, tag_out, par ^ 1);
+            if (tr && (int)threadIdx.x == nthreads - 32) trow[4] = gtimer();
             __syncthreads();        // the next sweep's inputs are complete
-            if (tr && threadIdx.x == 0) trow[6] = gtimer();
+            if (tr && threadIdx.x == 0) trow[5] = gtimer();
         }
     }
 }
@@ -1539,11 +1559,12 @@ int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_
             if (smem > 48 * 1024) MRB_CUDA(cudaFuncSetAttribute(t_kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
             int its = iters, QQ = Q;
             // On-chip kernel (the block's iterate in shared memory for all sweeps): binary volumes whose per-block share fits
-            // (up to kOcCap bricks and kOcHalo foreign neighbour bricks per SM: band 4 up to about 256^3); MRB_QP_ONCHIP=0
-            // selects the tiled kernel.
+            // (up to kOcCap bricks and kOcHalo foreign neighbour bricks per SM: band 4 up to about 256^3).  OPT-IN with
+            // MRB_QP_ONCHIP=1: measured on B200 it is bit-identical but slower than the tiled kernel (3.7 ms against 2.7 ms
+            // at 256^3; profiles/r02_summary.md says why), so the tiled kernel stays the default.
             const int need_cap = (Q + grid - 1) / grid + 9;
             const char* eoc = getenv("MRB_QP_ONCHIP");
-            bool onchip = binary_volume && t_fit == 1 && !(dbg & 5) && !(eoc && atoi(eoc) == 0) && need_cap <= kOcCap &&
+            bool onchip = binary_volume && t_fit == 1 && !(dbg & 5) && (eoc && atoi(eoc) != 0) && need_cap <= kOcCap &&
                           (t_threads == 480 || t_threads < 480);
             int oc_threads = t_threads;
             int *hcount = nullptr, *hgid = nullptr;
@@ -1568,18 +1589,28 @@ int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_
                             hb[0], hb[grid / 4], hb[grid / 2], hb[3 * grid / 4], hb[9 * grid / 10], hb[grid - 1], hh[0], hh[grid / 2], hh[9 * grid / 10], hh[grid - 1]);
                 }
                 if (getenv("MRB_QP_VERBOSE")) fprintf(stderr, "mrb: on-chip kernel: %d bricks per block (cap %d), largest halo %d (cap %d), %d threads\n", need_cap, kOcCap, hm, kOcHalo, oc_threads > t_threads ? oc_threads : (hm > oc_threads ? (hm + 31) / 32 * 32 : oc_threads));
-                // one halo brick per thread, a second one for the threads that have no second brick to update
-                const int nloc_max = need_cap - 9 + 8;
-                const int spare = nloc_max > oc_threads ? 2 * oc_threads - nloc_max : oc_threads;
-                if (hm > kOcHalo || hm > oc_threads + (spare > 0 ? spare : 0) || nloc_max > 2 * oc_threads) onchip = false;
+                // Threads per block: MRB_QP_OC_THREADS (default: the tiled kernel's choice, 480 for grids that fill the GPU = two
+                // passes over ~830 bricks with four warps free in the second one to fetch the halo).
+                if (getenv("MRB_QP_OC_THREADS")) oc_threads = atoi(getenv("MRB_QP_OC_THREADS"));
+                oc_threads = std::max(32, std::min(kOcThreadsMax, oc_threads / 32 * 32));
+                if (hm > kOcHalo) onchip = false;
             }
             if (onchip) {
                 typedef OnchipLayout<kOcCap, kOcHalo> OL;
-                void* oc_kern = (void*)k_qp_bricks_onchip<kOcThreadsMax, kOcCap, kOcHalo, false>;
+                void* oc_kern = oc_threads <= 352 ? (void*)k_qp_bricks_onchip<352, kOcCap, kOcHalo, false>
+                                                  : (void*)k_qp_bricks_onchip<kOcThreadsMax, kOcCap, kOcHalo, false>;
+                if (getenv("MRB_QP_OC_BOUND")) {       // tuning aid: register budget of the kernel (launch bound), not its block size
+                    const int bnd = atoi(getenv("MRB_QP_OC_BOUND"));
+                    if (bnd == 480) oc_kern = (void*)k_qp_bricks_onchip<480, kOcCap, kOcHalo, false>;
+                    if (bnd == 640) oc_kern = (void*)k_qp_bricks_onchip<640, kOcCap, kOcHalo, false>;
+                    if (bnd == 544) oc_kern = (void*)k_qp_bricks_onchip<544, kOcCap, kOcHalo, false>;
+                }
+                int prefetch = getenv("MRB_QP_OC_MODE") ? atoi(getenv("MRB_QP_OC_MODE")) : 0;       // 2: no free-warp fetch (timing aid)
                 unsigned long long* trace = nullptr;
                 const bool want_trace = getenv("MRB_QP_TRACE") && atoi(getenv("MRB_QP_TRACE")) && iters >= kTraceFirst + kTraceSweeps;
                 if (want_trace) {
-                    oc_kern = (void*)k_qp_bricks_onchip<kOcThreadsMax, kOcCap, kOcHalo, true>;
+                    oc_kern = oc_threads <= 352 ? (void*)k_qp_bricks_onchip<352, kOcCap, kOcHalo, true>
+                                                : (void*)k_qp_bricks_onchip<kOcThreadsMax, kOcCap, kOcHalo, true>;
                     MRB_TRY(arena_alloc(ctx, (size_t)grid * kTraceSweeps * 8, &trace));
                     MRB_CUDA(cudaMemsetAsync(trace, 0, (size_t)grid * kTraceSweeps * 8 * sizeof(unsigned long long), ctx->stream));
                 }
@@ -1589,7 +1620,8 @@ int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_
                 MRB_CUDA(cudaMemsetAsync(ex, 0, (size_t)Q * 16 * sizeof(ulonglong2), ctx->stream));
                 MRB_CUDA(cudaFuncSetAttribute(oc_kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)OL::kBytes));
                 void* args[] = {(void*)&code, (void*)&fields, (void*)&nbA, (void*)&nbB, (void*)&xa, (void*)&xb, (void*)&QQ, (void*)&its,
-                                (void*)&md, (void*)&blk_nb, (void*)&P, (void*)&ex, (void*)&hcount, (void*)&hgid, (void*)&hslot, (void*)&trace};
+                                (void*)&md, (void*)&blk_nb, (void*)&P, (void*)&ex, (void*)&hcount, (void*)&hgid, (void*)&hslot, (void*)&prefetch,
+                                (void*)&trace};
                 MRB_CUDA(cudaEventRecord(ctx->ev[6], ctx->stream));
                 MRB_CUDA(cudaLaunchCooperativeKernel(oc_kern, dim3(grid), dim3(oc_threads), args, OL::kBytes, ctx->stream));
                 MRB_CUDA(cudaEventRecord(ctx->ev[7], ctx->stream));

@@ -149,8 +149,10 @@ def test_optimize_sync_and_layout_variants(ctx, O, synth, monkeypatch):
     for env in (B, dict(B, MRB_QP_BRICK_THREADS="512"), dict(B, MRB_QP_BRICK_THREADS="256"), dict(B, MRB_QP_BRICK_COMPACT="1"),
                 dict(B, MRB_QP_BRICK_NOSMEM="1"), dict(B, MRB_QP_TILE="3"), dict(B, MRB_QP_MIN_THREADS="128"),
                 dict(B, MRB_QP_DEBUG="32"),      # sweep flag published by thread 0 (the slab-sharded kernel's publisher)
-                dict(B, MRB_QP_ONCHIP="0"),      # tiled kernel (iterate through L1/L2) instead of the on-chip kernel
-                dict(B, MRB_QP_ONCHIP="0", MRB_QP_DEBUG="32"), dict(B, MRB_QP_ONCHIP="1", MRB_QP_BRICK_THREADS="256"),
+                # the opt-in on-chip kernel (iterate + halo in shared memory, tagged-word exchange): both fetch modes, two block sizes
+                dict(B, MRB_QP_ONCHIP="1"), dict(B, MRB_QP_ONCHIP="1", MRB_QP_OC_MODE="2"),
+                dict(B, MRB_QP_ONCHIP="1", MRB_QP_OC_THREADS="352"), dict(B, MRB_QP_ONCHIP="1", MRB_QP_ORDER="morton"),
+                dict(B, MRB_QP_ORDER="morton"), dict(B, MRB_QP_ORDER="morton:2,2,8"),
                 X, dict(X, MRB_QP_SYNC="flow"), dict(X, MRB_QP_BRICK_THREADS="512"), dict(X, MRB_QP_BRICK_THREADS="128"),
                 dict(X, MRB_QP_BRICK_NOSMEM="1"), {"MRB_QP_LAYOUT": "strips"},
                 {"MRB_QP_LAYOUT": "strips", "MRB_QP_VARIANT": "0:1024"}, {"MRB_QP_LAYOUT": "strips", "MRB_QP_VARIANT": "2:512"}):
