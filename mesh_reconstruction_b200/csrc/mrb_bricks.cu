@@ -1423,6 +1423,45 @@ __global__ void __launch_bounds__(256) k_assemble_F_sign(const float* __restrict
     }
 }
 
+// The same, four consecutive z per thread (nz % 128 == 0, 16-byte aligned grids): LDG.128 of the volume, one 32-bit load of
+// four flag bytes, one LDG.128 of the brick's strip (the four z of a thread are one strip of one brick), STG.128 of F; the four
+// sign-bit words of a 128-voxel segment are OR-reductions over groups of eight lanes.
+__global__ void __launch_bounds__(256) k_assemble_F_sign_v4(const float4* __restrict__ vol, const uint32_t* __restrict__ flags4,
+                                                            const int* __restrict__ bid, const float4* __restrict__ x, BrickDims bd,
+                                                            size_t P, double scale, float iso, float4* __restrict__ F,
+                                                            uint32_t* __restrict__ sb) {
+    const size_t n4 = (size_t)bd.nx * bd.ny * bd.nz / 4;
+    const int nz4 = bd.nz / 4;
+    const int lane = threadIdx.x & 31;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
+        const float4 v = __ldg(vol + i);
+        const uint32_t fl = __ldg(flags4 + i);
+        float4 f;
+        f.x = (float)__dmul_rn(__dsub_rn(__dmul_rn(2.0, (double)v.x), 1.0), scale);
+        f.y = (float)__dmul_rn(__dsub_rn(__dmul_rn(2.0, (double)v.y), 1.0), scale);
+        f.z = (float)__dmul_rn(__dsub_rn(__dmul_rn(2.0, (double)v.z), 1.0), scale);
+        f.w = (float)__dmul_rn(__dsub_rn(__dmul_rn(2.0, (double)v.w), 1.0), scale);
+        if (fl & 0x01010101u) {
+            const int Z = (int)(i % nz4);
+            const size_t t = i / nz4;
+            const int y = (int)(t % bd.ny), xx = (int)(t / bd.ny);
+            const int q = bid[((size_t)(xx >> 1) * bd.by + (y >> 1)) * bd.bz + Z];
+            const float4 s = x[(size_t)((xx & 1) * 2 + (y & 1)) * P + (size_t)q];
+            if (fl & 0x00000001u) f.x = s.x;
+            if (fl & 0x00000100u) f.y = s.y;
+            if (fl & 0x00010000u) f.z = s.z;
+            if (fl & 0x01000000u) f.w = s.w;
+        }
+        F[i] = f;
+        uint32_t m = ((f.x < iso) ? 1u : 0u) | ((f.y < iso) ? 2u : 0u) | ((f.z < iso) ? 4u : 0u) | ((f.w < iso) ? 8u : 0u);
+        m <<= 4 * (lane & 7);
+        m |= __shfl_xor_sync(0xffffffffu, m, 1);
+        m |= __shfl_xor_sync(0xffffffffu, m, 2);
+        m |= __shfl_xor_sync(0xffffffffu, m, 4);
+        if ((lane & 7) == 0) sb[i >> 3] = m;
+    }
+}
+
 // Builds the bricks from the stage-2 byte grids, runs `iters` sweeps, applies the feature reset and writes F.
 // *n_bricks / *closure_err_host are outputs; ev[6], ev[7] bracket the sweep kernel.
 int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_t* flags, const uint8_t* sq, Dims d,
@@ -1464,7 +1503,7 @@ int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_
     if (last_delta_host) *last_delta_host = 0.0f;
     int* bid = nullptr;
     MRB_TRY(arena_alloc(ctx, nb, &bid));
-    MRB_LAUNCH(ctx, k_fill_i32b, grid_for(ctx, nb, 256), 256, 0, bid, nb, -1);
+    MRB_CUDA(cudaMemsetAsync(bid, 0xFF, (size_t)nb * sizeof(int), ctx->stream));     // every int = -1
     if (tiled && Q > 0) {
         MRB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&t_fit, t_kern, t_threads, 0));
         if (t_fit < 1) { set_error("k_qp_bricks_tiled does not fit on an SM"); return MRB_ECUDA; }
@@ -1488,7 +1527,7 @@ int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_
         MRB_TRY(arena_alloc(ctx, (size_t)Q, &bpos));
         MRB_TRY(arena_alloc(ctx, (size_t)t_grid, &blk_nb));
         MRB_CUDA(cudaMemsetAsync(blk_nb, 0, (size_t)t_grid * sizeof(int), ctx->stream));      // blocks with an empty range
-        MRB_LAUNCH(ctx, k_fill_i32b, grid_for(ctx, nb, 256), 256, 0, bid1, nb, -1);
+        MRB_CUDA(cudaMemsetAsync(bid1, 0xFF, (size_t)nb * sizeof(int), ctx->stream));     // every int = -1
         MRB_LAUNCH(ctx, k_tiled_scatter, cdiv(Q, 256), 256, 0, tpos, Q, ord, bid1);
         MRB_LAUNCH(ctx, k_tiled_boundary, cdiv(Q, 256), 256, 0, tpos, Q, t_grid, ord, bid1, sb);
         MRB_TRY(scan_exclusive(ctx, sb, sb, (size_t)Q, sb + Q));
@@ -1743,8 +1782,12 @@ int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_
         // full warps over whole words: the grid-stride loop keeps every warp on 32 consecutive z of one row
         uint32_t* sb = nullptr;
         MRB_TRY(arena_alloc(ctx, n / 32, &sb));
-        MRB_LAUNCH(ctx, k_assemble_F_sign, grid_for(ctx, n, 256), 256, 0, vol, flags, bid, xres, bd, P, (double)band_size + 1.0,
-                   ctx->sign_iso, F_dev, sb);
+        if (d.nz % 128 == 0 && (((uintptr_t)vol | (uintptr_t)F_dev | (uintptr_t)flags) & 15) == 0 && !getenv("MRB_PACK_SCALAR"))
+            MRB_LAUNCH(ctx, k_assemble_F_sign_v4, (unsigned)ctx->sm_count * 16, 256, 0, (const float4*)vol, (const uint32_t*)flags, bid,
+                       (const float4*)xres, bd, P, (double)band_size + 1.0, ctx->sign_iso, (float4*)F_dev, sb);
+        else
+            MRB_LAUNCH(ctx, k_assemble_F_sign, grid_for(ctx, n, 256), 256, 0, vol, flags, bid, xres, bd, P, (double)band_size + 1.0,
+                       ctx->sign_iso, F_dev, sb);
         ctx->sign_bits = sb;
         ctx->sign_F = F_dev;
         return MRB_OK;
@@ -2069,7 +2112,8 @@ extern "C" {
 void mrb_qp_plan_destroy(mrb_qp_plan* plan) {
     if (!plan) return;
     if (plan->ctx) { cudaSetDevice(plan->ctx->device); cudaStreamSynchronize(plan->ctx->stream); }
-    plan->arena.release();
+    if (plan->ctx && plan->ctx->plan_arenas.size() < 2) plan->ctx->plan_arenas.push_back(std::move(plan->arena));   // kept for the next plan
+    else plan->arena.release();
     delete plan;
 }
 
@@ -2086,6 +2130,11 @@ int mrb_qp_plan_create(mrb_ctx* ctx, const float* volume, const int dims[3], int
     const Dims d = p->d;
     const size_t n = d.count();
     // every allocation below (scratch included) lands in the plan's own arena and lives as long as the plan
+    if (!ctx->plan_arenas.empty()) {
+        p->arena = std::move(ctx->plan_arenas.back());
+        ctx->plan_arenas.pop_back();
+        if (p->arena.reset() != MRB_OK) p->arena = Arena();
+    }
     std::swap(ctx->arena, p->arena);
     auto build = [&]() -> int {
         const float* dv = nullptr;
@@ -2116,7 +2165,7 @@ int mrb_qp_plan_create(mrb_ctx* ctx, const float* volume, const int dims[3], int
         const int Q = p->Q;
         const size_t Qn = (size_t)(Q > 0 ? Q : 1);
         MRB_TRY(arena_alloc(ctx, nb, &p->bid));
-        MRB_LAUNCH(ctx, k_fill_i32b, grid_for(ctx, nb, 256), 256, 0, p->bid, nb, -1);
+        MRB_CUDA(cudaMemsetAsync(p->bid, 0xFF, (size_t)nb * sizeof(int), ctx->stream));     // every int = -1
         MRB_TRY(arena_alloc(ctx, Qn, &p->code));
         MRB_TRY(arena_alloc(ctx, 2 * Qn, &p->fields));
         MRB_TRY(arena_alloc(ctx, 4 * (Qn + 1), &p->x0));
@@ -2253,8 +2302,8 @@ static int solve_sharded_tiled(mrb_qp_plan* plan, int rank, int world, void* con
     MRB_TRY(arena_alloc(ctx, (size_t)Qo, &pos_of));
     MRB_TRY(arena_alloc(ctx, (size_t)grid, &blk_nb));
     MRB_TRY(arena_alloc(ctx, (size_t)grid * 2, &blk_has));
-    MRB_LAUNCH(ctx, k_fill_i32b, grid_for(ctx, msz, 256), 256, 0, lmap1, msz, -1);
-    MRB_LAUNCH(ctx, k_fill_i32b, grid_for(ctx, msz, 256), 256, 0, lmap, msz, -1);
+    MRB_CUDA(cudaMemsetAsync(lmap1, 0xFF, (size_t)msz * sizeof(int), ctx->stream));     // every int = -1
+    MRB_CUDA(cudaMemsetAsync(lmap, 0xFF, (size_t)msz * sizeof(int), ctx->stream));     // every int = -1
     MRB_CUDA(cudaMemsetAsync(blk_nb, 0, (size_t)grid * sizeof(int), ctx->stream));
     MRB_CUDA(cudaMemsetAsync(blk_has, 0, (size_t)grid * 2 * sizeof(int), ctx->stream));
     const int plane_n = bd.by * bd.bz;

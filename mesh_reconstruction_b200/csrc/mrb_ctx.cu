@@ -211,17 +211,91 @@ __global__ void k_scan_down(const int* __restrict__ in, int* __restrict__ out, c
     }
 }
 
+// Single-pass scan (decoupled look-back): tiles are handed out by a ticket counter (a tile's predecessors are running or done,
+// so waiting for them cannot deadlock); a tile publishes its aggregate, then looks back over its predecessors' words until it
+// meets one that already carries an inclusive prefix, and publishes its own.  A word is 64 bits -- status (1 aggregate, 2
+// inclusive prefix) above the 32-bit value -- written and read with one relaxed 64-bit access, so value and status always
+// arrive together and no fence is needed.  `state` (one word per tile) and `ticket` are zero at launch.
+__global__ void __launch_bounds__(kScanThreads) k_scan_lookback(const int* in, int* out, size_t n,
+                                                                unsigned long long* state, unsigned* ticket,
+                                                                int* __restrict__ total_out, unsigned ntiles) {
+    __shared__ unsigned s_tile;
+    __shared__ int s_prefix;
+    if (threadIdx.x == 0) s_tile = atomicAdd(ticket, 1u);
+    __syncthreads();
+    const unsigned tile = s_tile;
+    const size_t base = (size_t)tile * kScanTile + (size_t)threadIdx.x * kScanItems;
+    int v[kScanItems];
+    int s = 0;
+#pragma unroll
+    for (int i = 0; i < kScanItems; i++) {
+        const size_t idx = base + i;
+        v[i] = idx < n ? in[idx] : 0;
+        s += v[i];
+    }
+    __shared__ int tot;
+    const int ex = block_excl_scan(s, &tot);
+    auto put = [&](unsigned t, unsigned status, int value) {
+        const unsigned long long w = ((unsigned long long)status << 32) | (unsigned)value;
+        asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(state + t), "l"(w) : "memory");
+    };
+    if (threadIdx.x == 0) {
+        if (tile == 0) { put(0, 2u, tot); s_prefix = 0; }
+        else put(tile, 1u, tot);
+    }
+    if (tile > 0 && threadIdx.x < 32) {
+        int prefix = 0;
+        int j = (int)tile - 1;                      // lane L looks at tile j - L
+        for (;;) {
+            const int t = j - (int)threadIdx.x;
+            unsigned long long w = 0;
+            unsigned spins = 0;
+            if (t >= 0) {
+                do {
+                    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(w) : "l"(state + t) : "memory");
+                    if (++spins == (1u << 26)) __trap();
+                } while ((w >> 32) == 0);
+            }
+            const unsigned has_prefix = __ballot_sync(0xffffffffu, t >= 0 && (w >> 32) == 2u);
+            const int first = has_prefix ? __ffs(has_prefix) - 1 : 32;        // nearest predecessor with an inclusive prefix
+            int val = (t >= 0 && (int)threadIdx.x <= first) ? (int)(unsigned)w : 0;
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) val += __shfl_xor_sync(0xffffffffu, val, o);
+            prefix += val;
+            if (has_prefix || j - 32 < 0) break;
+            j -= 32;
+        }
+        if (threadIdx.x == 0) { put(tile, 2u, prefix + tot); s_prefix = prefix; }
+    }
+    __syncthreads();
+    int run = ex + s_prefix;
+#pragma unroll
+    for (int i = 0; i < kScanItems; i++) {
+        const size_t idx = base + i;
+        if (idx < n) out[idx] = run;
+        run += v[i];
+    }
+    if (total_out && tile == ntiles - 1 && threadIdx.x == 0) *total_out = s_prefix + tot;
+}
+
 int scan_exclusive(mrb_ctx* ctx, const int* in, int* out, size_t n, int* total_dev) {
     if (n == 0) {
         if (total_dev) MRB_CUDA(cudaMemsetAsync(total_dev, 0, sizeof(int), ctx->stream));
         return MRB_OK;
     }
     unsigned nblocks = cdiv(n, kScanTile);
-    int* partial = nullptr;
-    MRB_TRY(arena_alloc(ctx, nblocks, &partial));
-    MRB_LAUNCH(ctx, k_scan_reduce, nblocks, kScanThreads, 0, in, partial, n);
-    MRB_LAUNCH(ctx, k_scan_partials, 1, 1024, 0, partial, (int)nblocks, total_dev);
-    MRB_LAUNCH(ctx, k_scan_down, nblocks, kScanThreads, 0, in, out, partial, n);
+    if (getenv("MRB_SCAN_THREE_PASS")) {            // the three-kernel scan (reduce, scan of the partials, down-sweep)
+        int* partial = nullptr;
+        MRB_TRY(arena_alloc(ctx, nblocks, &partial));
+        MRB_LAUNCH(ctx, k_scan_reduce, nblocks, kScanThreads, 0, in, partial, n);
+        MRB_LAUNCH(ctx, k_scan_partials, 1, 1024, 0, partial, (int)nblocks, total_dev);
+        MRB_LAUNCH(ctx, k_scan_down, nblocks, kScanThreads, 0, in, out, partial, n);
+        return MRB_OK;
+    }
+    unsigned long long* state = nullptr;
+    MRB_TRY(arena_alloc(ctx, (size_t)nblocks + 1, &state));      // last word: the ticket counter
+    MRB_CUDA(cudaMemsetAsync(state, 0, ((size_t)nblocks + 1) * sizeof(unsigned long long), ctx->stream));
+    MRB_LAUNCH(ctx, k_scan_lookback, nblocks, kScanThreads, 0, in, out, n, state, (unsigned*)(state + nblocks), total_dev, nblocks);
     return MRB_OK;
 }
 
@@ -265,6 +339,7 @@ void mrb_ctx_destroy(mrb_ctx* ctx) {
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     ctx->arena.release();
+    for (auto& a : ctx->plan_arenas) a.release();
     for (int i = 0; i < 8; i++) if (ctx->ev[i]) cudaEventDestroy(ctx->ev[i]);
     if (ctx->h_mail) cudaFreeHost(ctx->h_mail);
     if (ctx->d_mail) cudaFree(ctx->d_mail);

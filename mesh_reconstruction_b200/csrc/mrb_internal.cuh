@@ -75,6 +75,9 @@ struct mrb_ctx {
     // composed from several entry points (mrb_reconstruct with features)
     char* side[2] = {nullptr, nullptr};
     size_t side_cap[2] = {0, 0};
+    // arenas of destroyed plans (mrb_qp_plan_destroy), reused by the next mrb_qp_plan_create on this context: a plan per
+    // call would otherwise pay cudaMalloc + cudaFree (about 2 ms for a 256^3 grid) every time
+    std::vector<mrb::Arena> plan_arenas;
     bool want_sign_bits = false;
     float sign_iso = 0.0f;
     const float* sign_F = nullptr;

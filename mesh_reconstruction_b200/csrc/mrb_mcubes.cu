@@ -228,15 +228,8 @@ __device__ __forceinline__ uint32_t mix64(unsigned long long k) {
     return (uint32_t)k;
 }
 
-__global__ void k_hash_clear(unsigned long long* __restrict__ tkeys, int* __restrict__ tfirst, size_t cap) {
-    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < cap; i += (size_t)gridDim.x * blockDim.x) {
-        tkeys[i] = kEmptyKey;
-        tfirst[i] = 0x7fffffff;
-    }
-}
-
 __global__ void k_hash_insert(const unsigned long long* __restrict__ keys, int ncorner, unsigned long long* tkeys,
-                              int* tfirst, uint32_t mask, int* __restrict__ slot_of) {
+                              unsigned* tfirst, uint32_t mask, int* __restrict__ slot_of) {
     int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= ncorner) return;
     unsigned long long key = keys[p];
@@ -246,7 +239,7 @@ __global__ void k_hash_insert(const unsigned long long* __restrict__ keys, int n
         if (prev == kEmptyKey || prev == key) break;
         s = (s + 1) & mask;
     }
-    atomicMin(&tfirst[s], p);
+    atomicMin(&tfirst[s], (unsigned)p);           // table entries start at 0xffffffff (one memset clears keys and positions)
     slot_of[p] = (int)s;
 }
 
@@ -282,9 +275,10 @@ int dev_dedup(mrb_ctx* ctx, const float* soup, const unsigned long long* keys, i
     MRB_TRY(arena_alloc(ctx, cap, &tfirst));
     MRB_TRY(arena_alloc(ctx, (size_t)ncorner, &slot_of));
     MRB_TRY(arena_alloc(ctx, (size_t)ncorner, &is_first));
-    size_t want = (cap + 255) / 256, lim = (size_t)ctx->sm_count * 16;
-    MRB_LAUNCH(ctx, k_hash_clear, (unsigned)(want < lim ? want : lim), 256, 0, tkeys, tfirst, cap);
-    MRB_LAUNCH(ctx, k_hash_insert, cdiv(ncorner, 256), 256, 0, keys, ncorner, tkeys, tfirst, (uint32_t)(cap - 1), slot_of);
+    // empty key = all ones, "no position yet" = 0xffffffff as unsigned: two memsets instead of a clearing kernel
+    MRB_CUDA(cudaMemsetAsync(tkeys, 0xFF, cap * sizeof(unsigned long long), ctx->stream));
+    MRB_CUDA(cudaMemsetAsync(tfirst, 0xFF, cap * sizeof(int), ctx->stream));
+    MRB_LAUNCH(ctx, k_hash_insert, cdiv(ncorner, 256), 256, 0, keys, ncorner, tkeys, (unsigned*)tfirst, (uint32_t)(cap - 1), slot_of);
     MRB_LAUNCH(ctx, k_mark_first, cdiv(ncorner, 256), 256, 0, slot_of, tfirst, ncorner, is_first);
     MRB_TRY(scan_exclusive(ctx, is_first, is_first, (size_t)ncorner, ctx->d_mail));
     int nverts = 0;

@@ -332,7 +332,7 @@ static int build_strips(mrb_ctx* ctx, const float* vol, MarginFn margin, uint8_t
     MRB_TRY(compact(ctx, ActiveStripPred{flags, sb->sd}, ns, &sb->spos, &sb->S));
     const int S = sb->S;
     MRB_TRY(arena_alloc(ctx, ns, &sb->sid));
-    MRB_LAUNCH(ctx, k_fill_i32, grid_for(ctx, ns, 256), 256, 0, sb->sid, ns, -1);
+    MRB_CUDA(cudaMemsetAsync(sb->sid, 0xFF, (size_t)ns * sizeof(int), ctx->stream));     // every int = -1
     size_t Sn = (size_t)(S > 0 ? S : 1);
     MRB_TRY(arena_alloc(ctx, Sn, &sb->code));
     MRB_TRY(arena_alloc(ctx, Sn, &sb->lb4));
