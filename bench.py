@@ -99,6 +99,29 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
+def bind_to_gpu_numa_node(local):
+    """N > 1: keep this rank's host threads (and the pinned buffers they first touch) on the NUMA node of its GPU, so that
+    eight ranks do not all stream their 64 MiB volumes out of one socket's memory.  Best effort: returns a note for the line."""
+    try:
+        import torch
+        pr = torch.cuda.get_device_properties(local)
+        bdf = "%04x:%02x:%02x.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)
+        node = int(open("/sys/bus/pci/devices/%s/numa_node" % bdf).read())
+        if node < 0:
+            return "gpu %s: no NUMA node reported" % bdf
+        cpus = set()
+        for part in open("/sys/devices/system/node/node%d/cpulist" % node).read().strip().split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        allowed = cpus & os.sched_getaffinity(0)
+        if not allowed:
+            return "gpu %s on node %d: none of its cpus allowed here" % (bdf, node)
+        os.sched_setaffinity(0, allowed)
+        return "gpu %s -> NUMA node %d, %d cpus" % (bdf, node, len(allowed))
+    except Exception as e:      # noqa: BLE001
+        return "not bound (%s)" % type(e).__name__
+
+
 def measured_peak():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -317,6 +340,7 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
+    numa_note = bind_to_gpu_numa_node(local) if world > 1 else "single rank: not bound"
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
@@ -431,7 +455,7 @@ def main():
                 "stage4_mc": (4.0 * volume.size + 12.0 * len(faces) + 12.0 * len(verts)) / (np.mean([s["ms_mc"] for s in stats]) * 1e6) / peak},
             "qp_kernel_voxel_updates_per_s": float(B) * args.iters / (qp_kernel_ms / 1000.0),
             "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_ms_per_step,
-                    "host_threads": E2E_WORKERS, "latency_ms_one_call": float(np.median(lat_ms)),
+                    "host_threads": E2E_WORKERS, "host_binding_rank0": numa_note, "latency_ms_one_call": float(np.median(lat_ms)),
                     "meshes_per_s": world / (e2e_ms_per_step / 1000.0),
                     "h2d_bytes_per_step": int(volume.nbytes), "d2h_bytes_per_step": int(d2h)},
             "gpu_launches": int(launches),

@@ -816,6 +816,14 @@ __global__ void k_tiled_bitmap(const int4* __restrict__ nbA, const int2* __restr
 // with the sweep's own stores.  Blocks that own such bricks publish the sweep in a slot of the neighbour's flag array
 // (system scope) and wait for the neighbour's slots the same way as for local blocks: behind the interior phase.
 static const int kShardSlots = 128;
+// Timeline instrumentation (MRB_QP_TRACE=1): per block and sweep eight %globaltimer stamps for sweeps [kTraceFirst,
+// kTraceFirst + kTraceSweeps); tools/qp_trace.py prints the phase lengths.  trace == nullptr: off.
+static const int kTraceFirst = 200, kTraceSweeps = 32;
+__device__ __forceinline__ unsigned long long gtimer() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
 struct TShard {
     float4* peer_lo[2];          // lower / upper neighbour's iterate buffers (A, B); nullptr = no neighbour
     float4* peer_hi[2];
@@ -864,7 +872,8 @@ __global__ void __launch_bounds__(Threads, MinBlocks) k_qp_bricks_tiled(const ui
                                                                         unsigned* __restrict__ maxdelta_bits, unsigned* bar, int dbg,
                                                                         const int* __restrict__ blk_nb, unsigned* progress, int cap,
                                                                         const int* __restrict__ plist, const int* __restrict__ pcount,
-                                                                        int expanded, size_t P, TShard sh) {
+                                                                        int expanded, size_t P, TShard sh,
+                                                                        unsigned long long* trace) {
     __shared__ float s_sqrt[256];
     __shared__ float s_inv[32];
     // Threads is the launch bound; the block may be launched with fewer threads (grids that do not fill the GPU)
@@ -914,6 +923,7 @@ __global__ void __launch_bounds__(Threads, MinBlocks) k_qp_bricks_tiled(const ui
     // down, so that warp 0 (which publishes and polls) has the least to do.
     const int W = nthreads / 32;
     const int rtid = (W - 1 - (int)(threadIdx.x >> 5)) * 32 + (int)(threadIdx.x & 31);
+    const int itid = W > 1 && !(dbg & 64) ? ((int)threadIdx.x + nthreads - 32) % nthreads : (int)threadIdx.x;
     __shared__ unsigned s_seen;              // number of sweeps whose neighbour flags have all been observed
     __shared__ int s_nrem[2];                // slots to wait for in the lower / upper neighbour's flag rows
     if (threadIdx.x == 0) s_seen = 0;
@@ -952,6 +962,9 @@ __global__ void __launch_bounds__(Threads, MinBlocks) k_qp_bricks_tiled(const ui
         const bool last = it == iters - 1;
         float dmax = 0.0f;
         const bool flags_on = !(dbg & 5);
+        const bool tr = trace && it >= kTraceFirst && it < kTraceFirst + kTraceSweeps;
+        unsigned long long* trow = trace + ((size_t)blockIdx.x * kTraceSweeps + (tr ? it - kTraceFirst : 0)) * 8;
+        if (tr && threadIdx.x == 0) trow[0] = gtimer();
         if (it > 0 && (dbg & 4) && !(dbg & 1)) brick_grid_barrier(bar, (unsigned)it, gridDim.x);
         if (it > 0 && flags_on && threadIdx.x < 32) {
             // warp 0: collect the neighbours' flags of sweep it-1, then tell the block
@@ -979,14 +992,21 @@ __global__ void __launch_bounds__(Threads, MinBlocks) k_qp_bricks_tiled(const ui
             }
             __syncwarp();
             if (threadIdx.x == 0) asm volatile("st.release.cta.shared.u32 [%0], %1;" ::"r"(s_seen_addr), "r"((unsigned)it) : "memory");
+            if (tr && threadIdx.x == 0) trow[1] = gtimer();
         }
-        for (int q = q_int + threadIdx.x; q < q_end; q += nthreads) dmax = fmaxf(dmax, tiled_update(tc, q, P, in, out, last));
+        // interior bricks are dealt from warp 1 up and wrap around to warp 0 last: warp 0 starts late (it collects the flags
+        // first), so the stray second brick of a 481-brick interior must not be its lane 0's (measured: the block barrier
+        // was waiting for exactly that brick)
+        for (int q = q_int + itid; q < q_end; q += nthreads) dmax = fmaxf(dmax, tiled_update(tc, q, P, in, out, last));
+        if (tr && threadIdx.x == 0) trow[2] = gtimer();
+        if (tr && (int)threadIdx.x == nthreads - 32) trow[3] = gtimer();
         if (it > 0 && flags_on && q_begin + rtid < q_int) {
             unsigned v;
             do {
                 asm volatile("ld.acquire.cta.shared.u32 %0, [%1];" : "=r"(v) : "r"(s_seen_addr) : "memory");
             } while (v < (unsigned)it);
         }
+        if (tr && (int)threadIdx.x == nthreads - 32) trow[4] = gtimer();
         for (int q = q_begin + rtid; q < q_int; q += nthreads) {
             dmax = fmaxf(dmax, tiled_update(tc, q, P, in, out, last));
             if (Sharded && !last && (my_lo >= 0 || my_hi >= 0)) {
@@ -1009,7 +1029,9 @@ __global__ void __launch_bounds__(Threads, MinBlocks) k_qp_bricks_tiled(const ui
             for (int o = 16; o > 0; o >>= 1) dmax = fmaxf(dmax, __shfl_xor_sync(0xffffffffu, dmax, o));
             if ((threadIdx.x & 31) == 0) atomicMax(maxdelta_bits, __float_as_uint(dmax));
         } else if (!(dbg & 1)) {
+            if (tr && (int)threadIdx.x == nthreads - 32) trow[5] = gtimer();
             __syncthreads();        // the block's stores of this sweep are issued; its reads of the neighbours' bricks are done
+            if (tr && (int)threadIdx.x == nthreads - 32) trow[6] = gtimer();
             // Published by the LAST warp's first lane (MRB_QP_DEBUG=32: by thread 0): the release waits for the block's
             // stores to be visible, and warp 0 should already be polling the neighbours' flags during that time.
             if (flags_on && (int)threadIdx.x == ((dbg & 32) ? 0 : nthreads - 32)) {
@@ -1020,6 +1042,7 @@ __global__ void __launch_bounds__(Threads, MinBlocks) k_qp_bricks_tiled(const ui
                     if (my_hi >= 0) asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(sh.flag_hi_remote + my_hi), "r"((unsigned)(it + 1)) : "memory");
                 }
                 asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(mine), "r"((unsigned)(it + 1)) : "memory");
+                if (tr) trow[7] = gtimer();
             }
         }
         const float4* t = in; in = out; out = (float4*)t;
@@ -1048,13 +1071,7 @@ __global__ void __launch_bounds__(Threads, MinBlocks) k_qp_bricks_tiled(const ui
 // own slots in REVERSE order].  Neighbour slot r (own brick, CAP' = the all-zero dummy brick, CAP+1+h = halo brick h)
 // is element r of a plane in even sweeps and element S-1-r in odd sweeps (the halo is written in that order too), so a
 // sweep addresses everything as base + step * r with step = +-16 bytes and the plane offsets are immediates.
-static const int kTraceFirst = 200, kTraceSweeps = 32;
 static const int kOcCap = 848, kOcHalo = 608, kOcThreadsMax = 480;
-__device__ __forceinline__ unsigned long long gtimer() {
-    unsigned long long t;
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-    return t;
-}
 __device__ __forceinline__ unsigned long long ll_pack(float v, unsigned tag) {
     return (unsigned long long)__float_as_uint(v) | ((unsigned long long)tag << 32);
 }
@@ -1680,12 +1697,30 @@ int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_
             } else {
                 TShard no_shard;
                 memset(&no_shard, 0, sizeof(no_shard));
+                unsigned long long* trace = nullptr;
+                const bool want_trace = getenv("MRB_QP_TRACE") && atoi(getenv("MRB_QP_TRACE")) && iters >= kTraceFirst + kTraceSweeps;
+                if (want_trace) {
+                    MRB_TRY(arena_alloc(ctx, (size_t)grid * kTraceSweeps * 8, &trace));
+                    MRB_CUDA(cudaMemsetAsync(trace, 0, (size_t)grid * kTraceSweeps * 8 * sizeof(unsigned long long), ctx->stream));
+                }
                 void* args[] = {(void*)&code, (void*)&fields, (void*)&nbA, (void*)&nbB, (void*)&xa, (void*)&xb, (void*)&QQ, (void*)&its,
                                 (void*)&md, (void*)&bar, (void*)&dbg, (void*)&blk_nb, (void*)&progress, (void*)&cap, (void*)&plist, (void*)&pcount,
-                                (void*)&expanded, (void*)&P, (void*)&no_shard};
+                                (void*)&expanded, (void*)&P, (void*)&no_shard, (void*)&trace};
                 MRB_CUDA(cudaEventRecord(ctx->ev[6], ctx->stream));
                 MRB_CUDA(cudaLaunchCooperativeKernel(t_kern, dim3(grid), dim3(t_threads), args, smem, ctx->stream));
                 MRB_CUDA(cudaEventRecord(ctx->ev[7], ctx->stream));
+                if (want_trace) {
+                    std::vector<unsigned long long> h((size_t)grid * kTraceSweeps * 8);
+                    MRB_CUDA(cudaMemcpyAsync(h.data(), trace, h.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
+                    MRB_CUDA(cudaStreamSynchronize(ctx->stream));
+                    const char* path = getenv("MRB_QP_TRACE_FILE") ? getenv("MRB_QP_TRACE_FILE") : "qp_trace.bin";
+                    if (FILE* f = fopen(path, "wb")) {
+                        int hdr[4] = {grid, kTraceSweeps, 8, 1};
+                        fwrite(hdr, sizeof(int), 4, f);
+                        fwrite(h.data(), sizeof(unsigned long long), h.size(), f);
+                        fclose(f);
+                    }
+                }
             }
             ctx->launches++;
             xres = (iters % 2) ? (const float*)xb : (const float*)xa;
@@ -2408,9 +2443,10 @@ static int solve_sharded_tiled(mrb_qp_plan* plan, int rank, int world, void* con
         if (smem > 48 * 1024) MRB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         int its = iters, QQ = Qo, dbg = 32;      // thread 0 publishes (the configuration the multi-GPU runs were validated with)
         size_t PP = P;
+        unsigned long long* no_trace = nullptr;
         void* args[] = {(void*)&code, (void*)&fields, (void*)&nbA, (void*)&nbB, (void*)&xa, (void*)&xb, (void*)&QQ, (void*)&its,
                         (void*)&md, (void*)&bar, (void*)&dbg, (void*)&blk_nb, (void*)&progress, (void*)&cap, (void*)&plist, (void*)&pcount,
-                        (void*)&expanded, (void*)&PP, (void*)&sh};
+                        (void*)&expanded, (void*)&PP, (void*)&sh, (void*)&no_trace};
         MRB_CUDA(cudaEventRecord(ctx->ev[6], ctx->stream));
         MRB_CUDA(cudaLaunchCooperativeKernel(kern, dim3(grid), dim3(threads), args, smem, ctx->stream));
         MRB_CUDA(cudaEventRecord(ctx->ev[7], ctx->stream));

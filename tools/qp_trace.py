@@ -1,21 +1,35 @@
 #!/usr/bin/env python3
-"""Phase lengths of the on-chip sweep kernel from a MRB_QP_TRACE=1 dump (see k_qp_bricks_onchip): mean over blocks and sweeps, us.
-Stamps: 0 sweep start (thread 0), 1 thread 0 past its first brick + send, 2 thread 0 past its last brick, 3 last warp past the
-first pass, 4 last warp past the halo fetch, 5 thread 0 past the block barrier that ends the sweep."""
+"""Phase lengths of the sweep kernels from a MRB_QP_TRACE=1 dump: mean over blocks and sweeps, us.
+Tiled kernel (header flag 1) stamps: 0 sweep start (thread 0), 1 neighbours' flags seen (warp 0), 2 thread 0 past its interior
+bricks, 3 last warp past its interior bricks, 4 last warp past the wait for the flags, 5 last warp past its rim bricks,
+6 past the block barrier, 7 past the release store.
+On-chip kernel (flag 0) stamps: 0 sweep start, 1 thread 0 past its first brick + send, 2 thread 0 past its last brick, 3 last warp
+past the first pass, 4 last warp past the halo fetch, 5 thread 0 past the block barrier that ends the sweep."""
 import sys
 import numpy as np
 raw = open(sys.argv[1] if len(sys.argv) > 1 else "qp_trace.bin", "rb").read()
-grid, ns, ne, _ = np.frombuffer(raw[:16], np.int32)
+grid, ns, ne, kind = np.frombuffer(raw[:16], np.int32)
 t = np.frombuffer(raw[16:], np.uint64).reshape(grid, ns, ne).astype(np.int64)
 sl = (t[:, 1:, 0] - t[:, :-1, 0]) / 1000.0
-print("blocks %d, sweeps %d" % (grid, ns))
+print("blocks %d, sweeps %d, kernel: %s" % (grid, ns, "tiled" if kind == 1 else "on-chip"))
 def row(name, x):
     print("%-46s mean %6.2f  p10 %6.2f  p90 %6.2f" % (name, x.mean(), np.percentile(x, 10), np.percentile(x, 90)))
 row("sweep length (start -> next start)", sl)
 d = lambda a, b: (t[:, :, b] - t[:, :, a]) / 1000.0
-row("thread 0: first brick + send", d(0, 1))
-row("thread 0: all its bricks", d(0, 2))
-row("last warp: first pass", d(0, 3))
-row("last warp: first pass -> halo fetched", d(3, 4))
-row("thread 0: last brick -> past the end barrier", d(2, 5))
+if kind == 1:
+    row("start -> flags seen by warp 0", d(0, 1))
+    row("start -> thread 0 past interior", d(0, 2))
+    row("start -> last warp past interior", d(0, 3))
+    row("last warp: wait for the flags", d(3, 4))
+    row("last warp: rim bricks", d(4, 5))
+    row("last warp: block barrier", d(5, 6))
+    row("release store (fence + st)", d(6, 7))
+    rel = t[:, :-1, 7]; seen = t[:, 1:, 1]
+    print("own release(k-1) -> own flags seen(k): mean %.2f us" % ((seen - rel).mean() / 1000.0))
+else:
+    row("thread 0: first brick + send", d(0, 1))
+    row("thread 0: all its bricks", d(0, 2))
+    row("last warp: first pass", d(0, 3))
+    row("last warp: first pass -> halo fetched", d(3, 4))
+    row("thread 0: last brick -> past the end barrier", d(2, 5))
 print("spread of sweep starts across blocks: mean %.2f us" % ((t[:, :, 0].max(0) - t[:, :, 0].min(0)).mean() / 1000.0))
