@@ -255,6 +255,7 @@ def slab_records(ctx, args, world, local):
     solver = slab.FusedSolver(ctx, slab.max_bricks_for((512,) * 3 if world >= 8 else (256,) * 3) // 4)
     for name, cfg in cases:
         vol = synth.config_volume_t(cfg, device=dev)
+        torch.cuda.synchronize()                      # generated on torch's stream; the library reads it on its own
         out[name] = slab.check_against_single_gpu(ctx, solver, vol, iters=args.iters, band_size=args.band_size, reps=3)
         del vol
     out["note"] = ("one grid on N GPUs: stages 1-2 and 4 on every rank, stage 3 slab-sharded along x in one persistent "

@@ -79,6 +79,12 @@ class Context:
             want = {np.float32: torch.float32, np.int32: torch.int32}[dtype]
             if a.dtype != want or not a.is_contiguous():
                 a = a.to(want).contiguous()
+            if a.is_cuda:
+                # The library works on its own (non-blocking) stream: work torch has queued on its current stream -- the
+                # kernels that are still producing this tensor -- must be finished before the library reads it.
+                st = torch.cuda.current_stream(a.device)
+                if not st.query():
+                    st.synchronize()
             return a, C.c_void_p(a.data_ptr()), tuple(a.shape), a
         arr = np.ascontiguousarray(a, dtype=dtype)
         return arr, C.c_void_p(arr.ctypes.data), arr.shape, None

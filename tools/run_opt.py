@@ -9,6 +9,7 @@ from mesh_reconstruction_b200 import synth
 reps = int(sys.argv[1]) if len(sys.argv) > 1 else 5
 size = int(sys.argv[2]) if len(sys.argv) > 2 else 256
 v = synth.sphere_t(size, 110.0 if size == 256 else size / 2.0 - 18.0, device="cuda")
+torch.cuda.synchronize()
 ctx = mrb.Context(0)
 ts = []
 for _ in range(reps):

@@ -13,6 +13,7 @@ torch.cuda.set_device(local)
 dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 ctx = mrb.Context(local)
 v = synth.sphere_t(size, 110.0 if size == 256 else size / 2.0 - 18.0, device="cuda")
+torch.cuda.synchronize()
 solver = slab.FusedSolver(ctx, slab.max_bricks_for(v.shape) // 4)
 T = {}
 def tick(name, t0):
