@@ -258,8 +258,10 @@ def slab_records(ctx, args, world, local):
         torch.cuda.synchronize()                      # generated on torch's stream; the library reads it on its own
         out[name] = slab.check_against_single_gpu(ctx, solver, vol, iters=args.iters, band_size=args.band_size, reps=3)
         del vol
-    out["note"] = ("one grid on N GPUs: stages 1-2 and 4 on every rank, stage 3 slab-sharded along x in one persistent "
-                   "kernel per GPU, halo bricks stored into the neighbours' buffers over NVLink peer memory, per-sweep flags")
+    out["note"] = ("one grid on N GPUs, x-slabs: stage 3 in one persistent kernel per GPU (halo bricks stored into the neighbours' "
+                   "buffers over NVLink peer memory, per-sweep flags); stage 4 per slab (F assembled on the rank's planes only, marching "
+                   "cubes in whole-grid coordinates, shared-plane vertices owned by the lower rank, ids by prefix over the ranks); "
+                   "stages 1-2 on the whole grid on every rank")
     return out
 
 

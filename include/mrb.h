@@ -251,6 +251,17 @@ int  mrb_qp_plan_assemble(mrb_qp_plan* plan, const float* x_dev, float* F_out);
 int  mrb_qp_plan_solve_sharded(mrb_qp_plan* plan, int rank, int world, void* const* xa_ptrs, void* const* xb_ptrs,
                                void* const* flag_ptrs, const int* plane_cuts, int iters);
 float mrb_qp_plan_last_kernel_ms(mrb_qp_plan* plan);
+/* mrb_qp_plan_assemble for the voxel planes [x_begin, x_end) only: F_slab_out holds (x_end - x_begin) * ny * nz floats.  Only
+ * the bricks of those planes are read from x_dev (plan layout), so a rank of a slab-sharded run needs its own brick planes and
+ * the first plane of its upper neighbour.  No counterpart in the reference. */
+int  mrb_qp_plan_assemble_slab(mrb_qp_plan* plan, const float* x_dev, int x_begin, int x_end, float* F_slab_out);
+/* mrb_mcubes on an x-slab of a larger grid: F_slab = planes [x_origin, x_origin + dims[0]) of the whole grid (dims[1], dims[2] are
+ * the whole grid's).  Cells x_origin .. x_origin + dims[0] - 2; vertex coordinates and hash keys are those of the whole grid, bit for
+ * bit; faces index this slab's own vertex list.  Concatenating the slabs' triangles in slab order and merging the vertices of the
+ * shared planes by hash key (first slab wins) gives mcubes' result on the whole grid (mesh_reconstruction_b200/slab.py:
+ * merge_slab_meshes).  No counterpart in the reference (marching_cubes/mcubes.cpp:592-662 is single-process). */
+int  mrb_mcubes_slab(mrb_ctx* ctx, const float* F_slab, const int dims[3], int x_origin, float isolevel, int device_out,
+                     mrb_mesh* out);
 
 #ifdef __cplusplus
 }

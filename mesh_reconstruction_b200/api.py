@@ -259,6 +259,15 @@ class Context:
             self.write_ply(filename, verts, faces, scale, shift, pad)
         return verts, faces
 
+    def mcubes_slab(self, F_slab, x_origin, isolevel=0.0):
+        """Marching cubes on planes [x_origin, x_origin + F_slab.shape[0]) of a larger grid: vertices in the whole grid's
+        coordinates (bit for bit those of an unsharded run), faces index this slab's own vertex list (mrb_mcubes_slab)."""
+        kF, pF, shape, like = self._in(F_slab)
+        m = L.Mesh()
+        self._check(self.lib.mrb_mcubes_slab(self.h, pF, self._dims(shape), int(x_origin), float(isolevel),
+                                             1 if like is not None else 2, C.byref(m)))
+        return self._take_mesh(m, like)
+
     def mcubes_features(self, F, surfaceMap, normals, isolevel=0.0, feat_thresh=0.75, corner_thresh=0.8):
         """mcubes(..., USING_FEATURES=true) (mcubes.h:354): feature points, triangle fans and edge flips."""
         kF, pF, shape, like = self._in(F)

@@ -865,7 +865,7 @@ __device__ __forceinline__ float tiled_update(const TiledConsts& tc, int q, size
     return brick_update(q, P, na, nz, c, f0, f1, in, out, tc.s_sqrt, tc.s_inv, last);
 }
 
-template <int Threads, int MinBlocks, bool Sharded>
+template <int Threads, int MinBlocks, bool Sharded, bool Trace = false>
 __global__ void __launch_bounds__(Threads, MinBlocks) k_qp_bricks_tiled(const uint2* __restrict__ code, const uint4* __restrict__ fields,
                                                                         const int4* __restrict__ nbA, const int2* __restrict__ nbB,
                                                                         float4* xa, float4* xb, int Q, int iters,
@@ -923,7 +923,6 @@ __global__ void __launch_bounds__(Threads, MinBlocks) k_qp_bricks_tiled(const ui
     // down, so that warp 0 (which publishes and polls) has the least to do.
     const int W = nthreads / 32;
     const int rtid = (W - 1 - (int)(threadIdx.x >> 5)) * 32 + (int)(threadIdx.x & 31);
-    const int itid = W > 1 && !(dbg & 64) ? ((int)threadIdx.x + nthreads - 32) % nthreads : (int)threadIdx.x;
     __shared__ unsigned s_seen;              // number of sweeps whose neighbour flags have all been observed
     __shared__ int s_nrem[2];                // slots to wait for in the lower / upper neighbour's flag rows
     if (threadIdx.x == 0) s_seen = 0;
@@ -962,8 +961,8 @@ __global__ void __launch_bounds__(Threads, MinBlocks) k_qp_bricks_tiled(const ui
         const bool last = it == iters - 1;
         float dmax = 0.0f;
         const bool flags_on = !(dbg & 5);
-        const bool tr = trace && it >= kTraceFirst && it < kTraceFirst + kTraceSweeps;
-        unsigned long long* trow = trace + ((size_t)blockIdx.x * kTraceSweeps + (tr ? it - kTraceFirst : 0)) * 8;
+        const bool tr = Trace && it >= kTraceFirst && it < kTraceFirst + kTraceSweeps;
+        unsigned long long* trow = Trace ? trace + ((size_t)blockIdx.x * kTraceSweeps + (tr ? it - kTraceFirst : 0)) * 8 : nullptr;
         if (tr && threadIdx.x == 0) trow[0] = gtimer();
         if (it > 0 && (dbg & 4) && !(dbg & 1)) brick_grid_barrier(bar, (unsigned)it, gridDim.x);
         if (it > 0 && flags_on && threadIdx.x < 32) {
@@ -997,7 +996,8 @@ __global__ void __launch_bounds__(Threads, MinBlocks) k_qp_bricks_tiled(const ui
         // interior bricks are dealt from warp 1 up and wrap around to warp 0 last: warp 0 starts late (it collects the flags
         // first), so the stray second brick of a 481-brick interior must not be its lane 0's (measured: the block barrier
         // was waiting for exactly that brick)
-        for (int q = q_int + itid; q < q_end; q += nthreads) dmax = fmaxf(dmax, tiled_update(tc, q, P, in, out, last));
+        for (int q = q_int + ((int)threadIdx.x >= 32 ? (int)threadIdx.x - 32 : nthreads - 32 + (int)threadIdx.x); q < q_end; q += nthreads)
+            dmax = fmaxf(dmax, tiled_update(tc, q, P, in, out, last));
         if (tr && threadIdx.x == 0) trow[2] = gtimer();
         if (tr && (int)threadIdx.x == nthreads - 32) trow[3] = gtimer();
         if (it > 0 && flags_on && q_begin + rtid < q_int) {
@@ -1479,6 +1479,47 @@ __global__ void __launch_bounds__(256) k_assemble_F_sign_v4(const float4* __rest
     }
 }
 
+// F for the voxels [v0, v0 + count) of the grid only (an x-slab: whole planes), written to F[0 .. count): scalar and
+// four-voxels-per-thread versions (count, v0 multiples of 4 and 16-byte aligned pointers for the latter).
+__global__ void __launch_bounds__(256) k_assemble_F_range(const float* __restrict__ vol, const uint8_t* __restrict__ flags,
+                                                          const int* __restrict__ bid, const float* __restrict__ x, BrickDims bd,
+                                                          size_t P, double scale, size_t v0, size_t count, float* __restrict__ F) {
+    MRB_VOXEL_LOOP(i, count) {
+        const size_t idx = v0 + i;
+        float f;
+        if (flags[idx] & 1) f = x[brick_slot(bid, bd, P, idx)];
+        else f = (float)__dmul_rn(__dsub_rn(__dmul_rn(2.0, (double)vol[idx]), 1.0), scale);
+        F[i] = f;
+    }
+}
+__global__ void __launch_bounds__(256) k_assemble_F_range_v4(const float4* __restrict__ vol, const uint32_t* __restrict__ flags4,
+                                                             const int* __restrict__ bid, const float4* __restrict__ x, BrickDims bd,
+                                                             size_t P, double scale, size_t v04, size_t count4, float4* __restrict__ F) {
+    const int nz4 = bd.nz / 4;
+    for (size_t j = (size_t)blockIdx.x * blockDim.x + threadIdx.x; j < count4; j += (size_t)gridDim.x * blockDim.x) {
+        const size_t i = v04 + j;
+        const float4 v = __ldg(vol + i);
+        const uint32_t fl = __ldg(flags4 + i);
+        float4 f;
+        f.x = (float)__dmul_rn(__dsub_rn(__dmul_rn(2.0, (double)v.x), 1.0), scale);
+        f.y = (float)__dmul_rn(__dsub_rn(__dmul_rn(2.0, (double)v.y), 1.0), scale);
+        f.z = (float)__dmul_rn(__dsub_rn(__dmul_rn(2.0, (double)v.z), 1.0), scale);
+        f.w = (float)__dmul_rn(__dsub_rn(__dmul_rn(2.0, (double)v.w), 1.0), scale);
+        if (fl & 0x01010101u) {
+            const int Z = (int)(i % nz4);
+            const size_t t = i / nz4;
+            const int y = (int)(t % bd.ny), xx = (int)(t / bd.ny);
+            const int q = bid[((size_t)(xx >> 1) * bd.by + (y >> 1)) * bd.bz + Z];
+            const float4 s = x[(size_t)((xx & 1) * 2 + (y & 1)) * P + (size_t)q];
+            if (fl & 0x00000001u) f.x = s.x;
+            if (fl & 0x00000100u) f.y = s.y;
+            if (fl & 0x00010000u) f.z = s.z;
+            if (fl & 0x01000000u) f.w = s.w;
+        }
+        F[j] = f;
+    }
+}
+
 // Builds the bricks from the stage-2 byte grids, runs `iters` sweeps, applies the feature reset and writes F.
 // *n_bricks / *closure_err_host are outputs; ev[6], ev[7] bracket the sweep kernel.
 int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_t* flags, const uint8_t* sq, Dims d,
@@ -1698,8 +1739,9 @@ int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_
                 TShard no_shard;
                 memset(&no_shard, 0, sizeof(no_shard));
                 unsigned long long* trace = nullptr;
-                const bool want_trace = getenv("MRB_QP_TRACE") && atoi(getenv("MRB_QP_TRACE")) && iters >= kTraceFirst + kTraceSweeps;
+                const bool want_trace = getenv("MRB_QP_TRACE") && atoi(getenv("MRB_QP_TRACE")) && iters >= kTraceFirst + kTraceSweeps && t_threads <= 480;
                 if (want_trace) {
+                    if (t_threads <= 480) t_kern = (void*)k_qp_bricks_tiled<480, 1, false, true>;     // launch bound >= the block size
                     MRB_TRY(arena_alloc(ctx, (size_t)grid * kTraceSweeps * 8, &trace));
                     MRB_CUDA(cudaMemsetAsync(trace, 0, (size_t)grid * kTraceSweeps * 8 * sizeof(unsigned long long), ctx->stream));
                 }
@@ -2123,6 +2165,18 @@ __global__ void k_sh_ctrl(unsigned* p, unsigned v) {
 
 }  // namespace mrb
 
+namespace mrb {
+// bricks sorted by grid position: thread q (0 .. Q) writes plane_off[X] = q for every plane X in (plane(q-1), plane(q)]
+// (plane(-1) = -1, plane(Q) = bx)
+__global__ void k_plane_offsets(const int* __restrict__ bpos, int Q, int per_plane, int bx, int* __restrict__ plane_off) {
+    const int q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q > Q) return;
+    const int hi = q < Q ? bpos[q] / per_plane : bx;
+    const int lo = q > 0 ? bpos[q - 1] / per_plane : -1;
+    for (int X = lo + 1; X <= hi; X++) plane_off[X] = q;
+}
+}  // namespace mrb
+
 struct mrb_qp_plan {
     mrb_ctx* ctx = nullptr;
     mrb::Arena arena;                 // owns every device buffer of the plan
@@ -2187,13 +2241,15 @@ int mrb_qp_plan_create(mrb_ctx* ctx, const float* volume, const int dims[3], int
         int* counts = ctx->d_mail + 32;
         MRB_CUDA(cudaMemsetAsync(counts, 0, 4 * sizeof(int), ctx->stream));
         int binary = 0;
-        MRB_TRY(stage12_binary(ctx, dv, d, band_size, p->sq, p->flags, counts, &binary, nullptr));
+        uint8_t* brick_bits = nullptr;     // by-product of the tile kernel: which bricks hold a band voxel
+        MRB_TRY(stage12_binary(ctx, dv, d, band_size, p->sq, p->flags, counts, &binary, &brick_bits));
         if (!binary) { set_error("mrb_qp_plan_create: the volume must contain only 0 and 1"); return MRB_EINVAL; }
         MRB_CUDA(cudaMemcpyAsync(ctx->h_mail + 32, counts, 4 * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
         p->bd = BrickDims{d.nx, d.ny, d.nz, (d.nx + 1) / 2, (d.ny + 1) / 2, (d.nz + 3) / 4};
         const size_t nb = p->bd.count();
         int* bpos = nullptr;
-        MRB_TRY(compact(ctx, ActiveBrickPred{p->flags, p->bd}, nb, &bpos, &p->Q));
+        if (brick_bits) MRB_TRY(compact(ctx, BrickBitPred{brick_bits, p->bd, (d.nz + 31) / 32}, nb, &bpos, &p->Q));
+        else MRB_TRY(compact(ctx, ActiveBrickPred{p->flags, p->bd}, nb, &bpos, &p->Q));
         p->n_band = ctx->h_mail[32];
         p->n_tight = ctx->h_mail[33];
         if (ctx->h_mail[34]) { set_error("narrow band touches the grid border (reference exits, grid.cpp:20-37)"); return MRB_EBORDER; }
@@ -2214,17 +2270,14 @@ int mrb_qp_plan_create(mrb_ctx* ctx, const float* volume, const int dims[3], int
         MRB_CUDA(cudaMemsetAsync(p->x0, 0, 4 * (Qn + 1) * sizeof(float4), ctx->stream));
         MRB_LAUNCH(ctx, k_brick_build, cdiv(Q, 128), 128, 0, dv, p->sq, p->flags, p->bid, bpos, Q, p->bd, p->code, p->fields,
                    p->x0, p->nbA, p->nbB, err, (size_t)Q + 1);
-        std::vector<int> hpos((size_t)Q);
-        MRB_CUDA(cudaMemcpyAsync(hpos.data(), bpos, (size_t)Q * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+        // plane_off[X] = first brick id whose plane is >= X (bricks are sorted by position): computed on the device, bx + 1 ints come back
+        int* poff = nullptr;
+        MRB_TRY(arena_alloc(ctx, (size_t)p->bd.bx + 1, &poff));
+        MRB_LAUNCH(ctx, k_plane_offsets, cdiv(Q + 1, 256), 256, 0, bpos, Q, p->bd.by * p->bd.bz, p->bd.bx, poff);
+        MRB_CUDA(cudaMemcpyAsync(p->plane_off.data(), poff, ((size_t)p->bd.bx + 1) * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
         MRB_CUDA(cudaMemcpyAsync(ctx->h_mail + 24, err, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
         MRB_CUDA(cudaStreamSynchronize(ctx->stream));
         if (ctx->h_mail[24]) { set_error("narrow band touches the grid border (reference exits, grid.cpp:20-37)"); return MRB_EBORDER; }
-        const int per_plane = p->bd.by * p->bd.bz;
-        int q = 0;
-        for (int X = 0; X <= p->bd.bx; X++) {          // bricks are sorted by position: first id with plane >= X
-            while (q < Q && hpos[q] / per_plane < X) q++;
-            p->plane_off[X] = q;
-        }
         return MRB_OK;
     };
     int rc = build();
@@ -2551,8 +2604,39 @@ int mrb_qp_plan_assemble(mrb_qp_plan* plan, const float* x_dev, float* F_out) {
     const size_t n = plan->d.count();
     Out<float> o;
     MRB_TRY(o.init(ctx, F_out, n));
-    MRB_LAUNCH(ctx, k_assemble_F_b, grid_for(ctx, n, 256), 256, 0, plan->vol, plan->flags, plan->bid, x_dev, plan->bd,
-               (size_t)plan->Q + 1, (double)plan->band_size + 1.0, o.dev);
+    const Dims d = plan->d;
+    if (d.nz % 128 == 0 && n % 256 == 0 && (((uintptr_t)plan->vol | (uintptr_t)o.dev | (uintptr_t)plan->flags | (uintptr_t)x_dev) & 15) == 0) {
+        // four voxels per thread; the sign bits it packs on the way are not needed here
+        uint32_t* sb = nullptr;
+        MRB_TRY(arena_alloc(ctx, n / 32, &sb));
+        MRB_LAUNCH(ctx, k_assemble_F_sign_v4, (unsigned)ctx->sm_count * 16, 256, 0, (const float4*)plan->vol, (const uint32_t*)plan->flags,
+                   plan->bid, (const float4*)x_dev, plan->bd, (size_t)plan->Q + 1, (double)plan->band_size + 1.0, 0.0f, (float4*)o.dev, sb);
+    } else {
+        MRB_LAUNCH(ctx, k_assemble_F_b, grid_for(ctx, n, 256), 256, 0, plan->vol, plan->flags, plan->bid, x_dev, plan->bd,
+                   (size_t)plan->Q + 1, (double)plan->band_size + 1.0, o.dev);
+    }
+    MRB_TRY(o.commit(ctx));
+    return sync(ctx);
+}
+
+int mrb_qp_plan_assemble_slab(mrb_qp_plan* plan, const float* x_dev, int x_begin, int x_end, float* F_slab_out) {
+    MRB_REQUIRE(plan && x_dev && F_slab_out, "NULL argument");
+    MRB_REQUIRE(x_begin >= 0 && x_begin < x_end && x_end <= plan->d.nx, "bad plane range");
+    mrb_ctx* ctx = plan->ctx;
+    MRB_CUDA(cudaSetDevice(ctx->device));
+    MRB_TRY(ctx->arena.reset());
+    const Dims d = plan->d;
+    const size_t plane = (size_t)d.ny * d.nz, v0 = (size_t)x_begin * plane, count = (size_t)(x_end - x_begin) * plane;
+    Out<float> o;
+    MRB_TRY(o.init(ctx, F_slab_out, count));
+    if (d.nz % 4 == 0 && (((uintptr_t)plan->vol | (uintptr_t)o.dev | (uintptr_t)plan->flags | (uintptr_t)x_dev) & 15) == 0) {
+        MRB_LAUNCH(ctx, k_assemble_F_range_v4, (unsigned)ctx->sm_count * 16, 256, 0, (const float4*)plan->vol, (const uint32_t*)plan->flags,
+                   plan->bid, (const float4*)x_dev, plan->bd, (size_t)plan->Q + 1, (double)plan->band_size + 1.0, v0 / 4, count / 4,
+                   (float4*)o.dev);
+    } else {
+        MRB_LAUNCH(ctx, k_assemble_F_range, grid_for(ctx, count, 256), 256, 0, plan->vol, plan->flags, plan->bid, x_dev, plan->bd,
+                   (size_t)plan->Q + 1, (double)plan->band_size + 1.0, v0, count, o.dev);
+    }
     MRB_TRY(o.commit(ctx));
     return sync(ctx);
 }

@@ -202,6 +202,6 @@ struct McStack {
     int *face_off_host, *vert_off_host, *seam_err_host;
 };
 int dev_mcubes(mrb_ctx* ctx, const float* F, Dims d, float isolevel, float** verts_dev, int** faces_dev,
-               int* nverts, int* nfaces, const McStack* stack = nullptr);
+               int* nverts, int* nfaces, const McStack* stack = nullptr, int xorg = 0);
 
 }  // namespace mrb

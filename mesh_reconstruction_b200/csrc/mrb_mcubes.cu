@@ -38,6 +38,10 @@ struct CellDims {
     // gets exactly the vertices, keys and first-appearance order it would get alone.  0 = one object.
     int xpitch;
     unsigned long long kstride;
+    // x-slab of a larger grid (mrb_mcubes_slab): plane 0 of this grid is plane xorg of the whole grid; vertex coordinates
+    // (and through them the hash keys) are those of the whole grid.  i + xorg is added as an integer BEFORE the conversion to
+    // float, so the interpolation rounds exactly as in an unsharded run.
+    int xorg;
 };
 
 // corner n of cell (i,j,k): (i + [n%4 in {1,2}], j + (n%4)/2, k + n/4)  (mcubes.cpp:166-168)
@@ -135,6 +139,7 @@ __device__ __forceinline__ int polygonise(const float* __restrict__ F, const Cel
     const int ob = cd.xpitch ? i / cd.xpitch : 0;
     const unsigned long long kofs = (unsigned long long)ob * cd.kstride;
     i -= ob * cd.xpitch;             // coordinates local to the object (the corner values were read above)
+    i += cd.xorg;                    // ... or global, for an x-slab of a larger grid
     F3 vert[12];
 #pragma unroll
     for (int e = 0; e < 12; e++) {
@@ -384,14 +389,14 @@ int classify_cells(mrb_ctx* ctx, const float* F, Dims d, float iso, int** cells_
 }
 
 int dev_mcubes(mrb_ctx* ctx, const float* F, Dims d, float isolevel, float** verts_dev, int** faces_dev, int* nverts,
-               int* nfaces, const McStack* stack) {
+               int* nfaces, const McStack* stack, int xorg) {
     *verts_dev = nullptr; *faces_dev = nullptr; *nverts = 0; *nfaces = 0;
     if (stack) {
         for (int o = 0; o <= stack->nobj; o++) { stack->face_off_host[o] = 0; stack->vert_off_host[o] = 0; }
         *stack->seam_err_host = 0;
     }
     if (d.nx < 2 || d.ny < 2 || d.nz < 2) return MRB_OK;
-    CellDims cd{d.nx, d.ny, d.nz, d.nx - 1, d.ny - 1, d.nz - 1, 0, 0ull};
+    CellDims cd{d.nx, d.ny, d.nz, d.nx - 1, d.ny - 1, d.nz - 1, 0, 0ull, xorg};
     if (stack) { cd.xpitch = stack->xpitch; cd.kstride = stack->kstride; }
     int* cells = nullptr;
     int ncells = 0;
@@ -495,6 +500,22 @@ int mrb_mcubes(mrb_ctx* ctx, const float* F, const int dims[3], float isolevel, 
     int* faces = nullptr;
     int nv = 0, nf = 0;
     MRB_TRY(dev_mcubes(ctx, dF, d, isolevel, &verts, &faces, &nv, &nf));
+    return export_mesh(ctx, verts, faces, nv, nf, device_out, out);
+}
+
+int mrb_mcubes_slab(mrb_ctx* ctx, const float* F_slab, const int dims[3], int x_origin, float isolevel, int device_out,
+                    mrb_mesh* out) {
+    MRB_REQUIRE(ctx && F_slab && dims && out && x_origin >= 0, "bad argument");
+    MRB_CUDA(cudaSetDevice(ctx->device));
+    MRB_TRY(ctx->arena.reset());
+    memset(out, 0, sizeof(*out));
+    Dims d = mkdims(dims);
+    const float* dF = nullptr;
+    MRB_TRY(stage_in(ctx, F_slab, d.count(), &dF));
+    float* verts = nullptr;
+    int* faces = nullptr;
+    int nv = 0, nf = 0;
+    MRB_TRY(dev_mcubes(ctx, dF, d, isolevel, &verts, &faces, &nv, &nf, nullptr, x_origin));
     return export_mesh(ctx, verts, faces, nv, nf, device_out, out);
 }
 

@@ -46,3 +46,55 @@ def test_fused_sharded_kernel_world1(ctx, synth):
     for iters in (1, 40, 41):
         F = slab.solve_fused(ctx, v, iters=iters).cpu().numpy()
         assert np.array_equal(F, ctx.optimize(v, iters=iters)), iters
+
+
+def _slab_mesh(ctx, F, cuts, iso):
+    """Marching cubes slab by slab (mrb_mcubes_slab) + merge_slab_meshes, all on one GPU."""
+    import torch
+    from mesh_reconstruction_b200 import slab
+    nx = F.shape[0]
+    parts = []
+    for x0, x1 in zip(cuts[:-1], cuts[1:]):
+        v, f = ctx.mcubes_slab(np.ascontiguousarray(F[x0:min(x1 + 1, nx)]), x0, iso)
+        parts.append((torch.from_numpy(v), torch.from_numpy(f), x0, x1))
+    v, f = slab.merge_slab_meshes(parts, F.shape)
+    return v.numpy(), f.numpy()
+
+
+@pytest.mark.parametrize("cuts", [[0, 64], [0, 30, 64], [0, 22, 23, 41, 64], [0, 2, 62, 64]])
+def test_sharded_marching_cubes_equals_whole_grid(ctx, synth, cuts):
+    """Stage 4 slab by slab: same vertices (bits), same first-appearance ids, same faces as mcubes on the whole grid, for
+    cuts through the surface, a one-plane slab and slabs that hold no surface at all."""
+    v = synth.union(synth.sphere(64, 20.0), synth.box(64, (24, 8, 8), None, 0.0, 0.0))
+    F = ctx.optimize(v, iters=40)
+    verts, faces = ctx.mcubes(F, 0.0)
+    sv, sf = _slab_mesh(ctx, F, cuts, 0.0)
+    assert sv.shape == verts.shape and np.array_equal(sv.view(np.uint32), verts.view(np.uint32))
+    assert np.array_equal(sf, faces)
+
+
+def test_sharded_marching_cubes_exact_zeros_and_binary_volume(ctx, synth):
+    """Vertices that fall exactly on grid points of the cut plane (F == isolevel there) and the degenerate-triangle filter:
+    a binary volume at isolevel 0.5 (m_cubes.cpp) and an embedding with exact zeros on the cut plane."""
+    v = synth.union(synth.sphere(48, 13.0), synth.box(48, (15, 5, 5), None, 0.0, 0.0))
+    verts, faces = ctx.mcubes(v, 0.5)
+    sv, sf = _slab_mesh(ctx, v, [0, 17, 24, 31, 48], 0.5)
+    assert np.array_equal(sv.view(np.uint32), verts.view(np.uint32)) and np.array_equal(sf, faces)
+    F = ctx.optimize(v, iters=30)
+    F[24][np.abs(F[24]) < 0.3] = 0.0                      # exact zeros on plane 24 (and the cells around it change sign there)
+    verts, faces = ctx.mcubes(F, 0.0)
+    sv, sf = _slab_mesh(ctx, F, [0, 24, 48], 0.0)
+    assert np.array_equal(sv.view(np.uint32), verts.view(np.uint32)) and np.array_equal(sf, faces)
+
+
+def test_fused_sharded_back_end_world1(ctx, synth):
+    """FusedSolver.reconstruct_sharded with a single rank: slab assembly + slab marching cubes == mrb_reconstruct."""
+    import torch
+    from mesh_reconstruction_b200 import slab
+    v = synth.union(synth.sphere(64, 20.0), synth.box(64, (24, 8, 8), None, 0.0, 0.0))
+    vt = torch.from_numpy(v).cuda()
+    solver = slab.FusedSolver(ctx, slab.max_bricks_for(v.shape))
+    (sv, sf), F_slab, (x0, x1) = solver.reconstruct_sharded(vt, iters=40)
+    verts, faces = ctx.reconstruct(v, iters=40)
+    assert (x0, x1) == (0, 64) and np.array_equal(F_slab.cpu().numpy(), ctx.optimize(v, iters=40))
+    assert np.array_equal(sv.cpu().numpy().view(np.uint32), verts.view(np.uint32)) and np.array_equal(sf.cpu().numpy(), faces)

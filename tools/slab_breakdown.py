@@ -34,4 +34,12 @@ for rep in range(4):
     T["kernel_ms"] = T.get("kernel_ms", 0.0) + tm["kernel_ms"]
 if dist.get_rank() == 0:
     print(json.dumps({k: round(val / 3, 3) for k, val in T.items()}))
+ph = {}
+for rep in range(4):
+    if rep == 1:
+        ph.clear()
+    torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
+    solver.reconstruct_sharded(v, iters=500, timings={"phases": ph})
+if dist.get_rank() == 0:
+    print("sharded back end:", json.dumps({k: round(val / 3, 3) for k, val in ph.items()}))
 dist.destroy_process_group()
