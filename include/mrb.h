@@ -251,6 +251,17 @@ int  mrb_qp_plan_assemble(mrb_qp_plan* plan, const float* x_dev, float* F_out);
 int  mrb_qp_plan_solve_sharded(mrb_qp_plan* plan, int rank, int world, void* const* xa_ptrs, void* const* xb_ptrs,
                                void* const* flag_ptrs, const int* plane_cuts, int iters);
 float mrb_qp_plan_last_kernel_ms(mrb_qp_plan* plan);
+/* Slab-local plans (stages 1-2 sharded too).  mrb_qp_plan_create_slab builds a plan of a SUB-grid, planes [a, b) of a larger grid
+ * whose x faces are cuts: everything at least band_size + 5 voxel planes away from a cut equals what the whole grid's plan holds
+ * (perimeter +-1, EDT +-(band_size+1), erosion +-1, dilation +-1, the brick build's neighbour tests +-1), so a rank takes its
+ * own planes plus that margin.  A band that touches a face is not an error here (it always touches the cuts); run the unsharded
+ * path to get MRB_EBORDER.  mrb_qp_plan_solve_sharded_sub is mrb_qp_plan_solve_sharded on such a plan: the rank owns brick planes
+ * [plane_lo, plane_hi) of ITS plan, which must also hold the neighbours' adjacent planes; nb_layout = {owned bricks, lower-halo
+ * bricks, upper-halo bricks} of the lower neighbour, then of the upper neighbour (exchanged by the caller; ignored where there is no
+ * neighbour).  Result as in mrb_qp_plan_solve_sharded, in this plan's layout.  No counterpart in the reference. */
+int  mrb_qp_plan_create_slab(mrb_ctx* ctx, const float* volume_sub, const int dims_sub[3], int band_size, mrb_qp_plan** out);
+int  mrb_qp_plan_solve_sharded_sub(mrb_qp_plan* plan, int rank, int world, void* const* xa_ptrs, void* const* xb_ptrs,
+                                   void* const* flag_ptrs, int plane_lo, int plane_hi, const int* nb_layout, int iters);
 /* mrb_qp_plan_assemble for the voxel planes [x_begin, x_end) only: F_slab_out holds (x_end - x_begin) * ny * nz floats.  Only
  * the bricks of those planes are read from x_dev (plan layout), so a rank of a slab-sharded run needs its own brick planes and
  * the first plane of its upper neighbour.  No counterpart in the reference. */

@@ -76,6 +76,9 @@ SYMBOLS = {
     "mrb_qp_plan_solve_sharded": (C.c_int, [_VP, C.c_int, C.c_int, C.POINTER(_VP), C.POINTER(_VP), C.POINTER(_VP), c_int_p,
                                             C.c_int]),
     "mrb_qp_plan_last_kernel_ms": (C.c_float, [_VP]),
+    "mrb_qp_plan_create_slab": (C.c_int, [_VP, _VP, c_int_p, C.c_int, C.POINTER(_VP)]),
+    "mrb_qp_plan_solve_sharded_sub": (C.c_int, [_VP, C.c_int, C.c_int, C.POINTER(_VP), C.POINTER(_VP), C.POINTER(_VP), C.c_int, C.c_int,
+                                                c_int_p, C.c_int]),
     "mrb_qp_plan_assemble_slab": (C.c_int, [_VP, _VP, C.c_int, C.c_int, _VP]),
     "mrb_mcubes_slab": (C.c_int, [_VP, _VP, c_int_p, C.c_int, C.c_float, C.c_int, C.POINTER(Mesh)]),
     "mrb_reconstruct_batch": (C.c_int, [_VP, _VP, c_int_p, C.c_int, C.POINTER(Options), C.POINTER(Mesh), c_int_p,

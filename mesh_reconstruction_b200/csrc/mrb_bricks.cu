@@ -2206,7 +2206,16 @@ void mrb_qp_plan_destroy(mrb_qp_plan* plan) {
     delete plan;
 }
 
+static int plan_create_impl(mrb_ctx* ctx, const float* volume, const int dims[3], int band_size, bool allow_border, mrb_qp_plan** out);
+
 int mrb_qp_plan_create(mrb_ctx* ctx, const float* volume, const int dims[3], int band_size, mrb_qp_plan** out) {
+    return plan_create_impl(ctx, volume, dims, band_size, false, out);
+}
+int mrb_qp_plan_create_slab(mrb_ctx* ctx, const float* volume_sub, const int dims_sub[3], int band_size, mrb_qp_plan** out) {
+    return plan_create_impl(ctx, volume_sub, dims_sub, band_size, true, out);
+}
+
+static int plan_create_impl(mrb_ctx* ctx, const float* volume, const int dims[3], int band_size, bool allow_border, mrb_qp_plan** out) {
     MRB_REQUIRE(ctx && volume && dims && out, "NULL argument");
     MRB_REQUIRE(band_size >= 1 && band_size <= 15, "plans support band_size 1..15");
     *out = nullptr;
@@ -2252,7 +2261,7 @@ int mrb_qp_plan_create(mrb_ctx* ctx, const float* volume, const int dims[3], int
         else MRB_TRY(compact(ctx, ActiveBrickPred{p->flags, p->bd}, nb, &bpos, &p->Q));
         p->n_band = ctx->h_mail[32];
         p->n_tight = ctx->h_mail[33];
-        if (ctx->h_mail[34]) { set_error("narrow band touches the grid border (reference exits, grid.cpp:20-37)"); return MRB_EBORDER; }
+        if (ctx->h_mail[34] && !allow_border) { set_error("narrow band touches the grid border (reference exits, grid.cpp:20-37)"); return MRB_EBORDER; }
         const int Q = p->Q;
         const size_t Qn = (size_t)(Q > 0 ? Q : 1);
         MRB_TRY(arena_alloc(ctx, nb, &p->bid));
@@ -2277,7 +2286,7 @@ int mrb_qp_plan_create(mrb_ctx* ctx, const float* volume, const int dims[3], int
         MRB_CUDA(cudaMemcpyAsync(p->plane_off.data(), poff, ((size_t)p->bd.bx + 1) * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
         MRB_CUDA(cudaMemcpyAsync(ctx->h_mail + 24, err, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
         MRB_CUDA(cudaStreamSynchronize(ctx->stream));
-        if (ctx->h_mail[24]) { set_error("narrow band touches the grid border (reference exits, grid.cpp:20-37)"); return MRB_EBORDER; }
+        if (ctx->h_mail[24] && !allow_border) { set_error("narrow band touches the grid border (reference exits, grid.cpp:20-37)"); return MRB_EBORDER; }
         return MRB_OK;
     };
     int rc = build();
@@ -2343,19 +2352,28 @@ static int shard_grid(int fit, int sm_count, int Ql, int threads) {
 // Buffers: 16 * (Q + 9) floats each (the slab-local layout needs a plane stride that is a multiple of 8 bricks);
 // flags: 512 ints, zeroed by the caller before a barrier across the ranks.  On return the owned bricks' values sit in
 // xa (even iters) / xb (odd iters) in the plan's GLOBAL layout (four planes of Q + 1 float4), like the older kernel.
+// cuts: brick-plane boundaries of all ranks in this plan's plane indices, or nullptr when the plan covers only this rank's
+// neighbourhood (mrb_qp_plan_solve_sharded_sub): then [Xa_sub, Xb_sub) is the owned range and nbl = {owned bricks, lower halo
+// bricks, upper halo bricks} of the lower and of the upper neighbour (what layout() computes from a whole-grid plan).
 static int solve_sharded_tiled(mrb_qp_plan* plan, int rank, int world, void* const* xa_ptrs, void* const* xb_ptrs,
-                               void* const* flag_ptrs, const int* cuts, int iters) {
+                               void* const* flag_ptrs, const int* cuts, int iters, int Xa_sub = 0, int Xb_sub = 0,
+                               const int* nbl = nullptr) {
     mrb_ctx* ctx = plan->ctx;
     const std::vector<int>& po = plan->plane_off;
     const BrickDims bd = plan->bd;
     const int Qg = plan->Q;
-    const int Xa = cuts[rank], Xb = cuts[rank + 1], nX = Xb - Xa;
+    const int Xa = cuts ? cuts[rank] : Xa_sub, Xb = cuts ? cuts[rank + 1] : Xb_sub, nX = Xb - Xa;
     const int Qo = po[Xb] - po[Xa];
     const bool has_lo = rank > 0, has_hi = rank < world - 1;
     const int nh_lo = has_lo ? po[Xa] - po[Xa - 1] : 0, nh_hi = has_hi ? po[Xb + 1] - po[Xb] : 0;
     const int D = Qo + nh_lo + nh_hi;
     const size_t P = tiled_stride(D);
     auto layout = [&](int r, int* Qo_r, int* nlo_r, int* nhi_r) {
+        if (!cuts) {
+            const int* t = nbl + (r < rank ? 0 : 3);
+            *Qo_r = t[0]; *nlo_r = t[1]; *nhi_r = t[2];
+            return;
+        }
         *Qo_r = po[cuts[r + 1]] - po[cuts[r]];
         *nlo_r = r > 0 ? po[cuts[r]] - po[cuts[r] - 1] : 0;
         *nhi_r = r < world - 1 ? po[cuts[r + 1] + 1] - po[cuts[r + 1]] : 0;
@@ -2639,6 +2657,20 @@ int mrb_qp_plan_assemble_slab(mrb_qp_plan* plan, const float* x_dev, int x_begin
     }
     MRB_TRY(o.commit(ctx));
     return sync(ctx);
+}
+
+int mrb_qp_plan_solve_sharded_sub(mrb_qp_plan* plan, int rank, int world, void* const* xa_ptrs, void* const* xb_ptrs,
+                                  void* const* flag_ptrs, int plane_lo, int plane_hi, const int* nb_layout, int iters) {
+    MRB_REQUIRE(plan && xa_ptrs && xb_ptrs && flag_ptrs && nb_layout && world >= 1 && rank >= 0 && rank < world && iters >= 0,
+                "bad argument");
+    const std::vector<int>& po = plan->plane_off;
+    MRB_REQUIRE(plane_lo >= 0 && plane_lo < plane_hi && plane_hi <= plan->bd.bx && po[plane_lo] < po[plane_hi], "bad owned plane range");
+    MRB_REQUIRE((rank == 0 || plane_lo >= 1) && (rank == world - 1 || plane_hi + 1 <= plan->bd.bx), "the plan must hold the neighbours' planes");
+    mrb_ctx* ctx = plan->ctx;
+    MRB_CUDA(cudaSetDevice(ctx->device));
+    MRB_TRY(ctx->arena.reset());
+    MRB_TRY(upload_tables(ctx->device));
+    return solve_sharded_tiled(plan, rank, world, xa_ptrs, xb_ptrs, flag_ptrs, nullptr, iters, plane_lo, plane_hi, nb_layout);
 }
 
 }  // extern "C"

@@ -98,3 +98,39 @@ def test_fused_sharded_back_end_world1(ctx, synth):
     verts, faces = ctx.reconstruct(v, iters=40)
     assert (x0, x1) == (0, 64) and np.array_equal(F_slab.cpu().numpy(), ctx.optimize(v, iters=40))
     assert np.array_equal(sv.cpu().numpy().view(np.uint32), verts.view(np.uint32)) and np.array_equal(sf.cpu().numpy(), faces)
+
+
+def test_slab_local_plan_world1(ctx, synth):
+    """FusedSolver.reconstruct_local with a single rank (the sub-grid is the whole grid): == mrb_reconstruct."""
+    import torch
+    from mesh_reconstruction_b200 import slab
+    v = synth.union(synth.sphere(64, 20.0), synth.box(64, (24, 8, 8), None, 0.0, 0.0))
+    vt = torch.from_numpy(v).cuda()
+    solver = slab.FusedSolver(ctx, slab.max_bricks_for(v.shape))
+    (sv, sf), F_slab, (x0, x1) = solver.reconstruct_local(vt, iters=40)
+    verts, faces = ctx.reconstruct(v, iters=40)
+    assert (x0, x1) == (0, 64) and np.array_equal(F_slab.cpu().numpy(), ctx.optimize(v, iters=40))
+    assert np.array_equal(sv.cpu().numpy().view(np.uint32), verts.view(np.uint32)) and np.array_equal(sf.cpu().numpy(), faces)
+
+
+@pytest.mark.parametrize("lo,hi", [(10, 40), (0, 33), (27, 64)])
+def test_slab_local_stage12_equals_whole_grid(ctx, synth, lo, hi):
+    """The exactness claim behind slab-local plans: a plan built from x-planes [lo - margin, hi + margin) assembles, for the
+    initial iterate, the same F on [lo, hi) as the whole grid's plan (same band, same signed margins, same +-5 outside)."""
+    import torch
+    from mesh_reconstruction_b200 import slab
+    v = synth.union(synth.sphere(64, 20.0), synth.box(64, (24, 8, 8), None, 0.0, 0.0))
+    vt = torch.from_numpy(v).cuda()
+    full = slab.Plan(ctx, vt)
+    F_full = full.assemble(full.new_x()).cpu().numpy()
+    full.close()
+    margin = 4 + 5
+    a, b = max(0, lo - margin) // 2 * 2, min(64, hi + margin + 1) // 2 * 2
+    sub = slab.Plan(ctx, vt[a:b], slab=True)
+    F_sub = torch.empty((hi - lo, 64, 64), dtype=torch.float32, device="cuda")
+    import ctypes as C
+    x = sub.new_x()
+    torch.cuda.synchronize()
+    sub._check(sub.lib.mrb_qp_plan_assemble_slab(sub.h, C.c_void_p(x.data_ptr()), lo - a, hi - a, C.c_void_p(F_sub.data_ptr())))
+    sub.close()
+    assert np.array_equal(F_sub.cpu().numpy(), F_full[lo:hi])

@@ -23,18 +23,20 @@ for cfg in cfgs:
     torch.cuda.synchronize()
     F1 = ctx.optimize(v, iters=iters)
     v1, f1 = ctx.reconstruct(v, iters=iters)
+    mode = os.environ.get("SLAB_MODE", "local")
     for r in range(reps):
-        t = {}
-        F2 = solver.solve(v, iters=iters, timings=t)
-        ok = bool(torch.equal(F1, F2))
-        info = {"cfg": cfg, "rep": r, "ok": ok, "kernel_ms": round(t["kernel_ms"], 3)}
+        t = {"phases": {}}
+        fn = {"local": solver.reconstruct_local, "sharded": solver.reconstruct_sharded}[mode]
+        (v2, f2), Fs, (xa, xb) = fn(v, iters=iters, timings=t)
+        ok = bool(torch.equal(F1[xa:xb], Fs))
+        info = {"cfg": cfg, "rep": r, "mode": mode, "ok": ok, "kernel_ms": round(t["kernel_ms"], 3), "planes": [xa, xb],
+                "phases": {k: round(x, 2) for k, x in t["phases"].items()}}
         if not ok:
-            bad = (F1 != F2).nonzero()
-            info.update(n_bad=int(len(bad)), x_min=int(bad[:, 0].min()), x_max=int(bad[:, 0].max()), cuts=[2 * c for c in t["cuts"]],
-                        max_abs=float((F1 - F2).abs().max()))
-        else:
-            v2, f2 = ctx.mcubes(F2, 0.0)
-            info["mesh_ok"] = bool(torch.equal(v1, v2) and torch.equal(f1, f2))
+            bad = (F1[xa:xb] != Fs).nonzero()
+            info.update(n_bad=int(len(bad)), x_min=xa + int(bad[:, 0].min()), x_max=xa + int(bad[:, 0].max()), cuts=[2 * c for c in t["cuts"]],
+                        max_abs=float((F1[xa:xb] - Fs).abs().max()))
+        info["mesh_ok"] = bool(v1.shape == v2.shape and f1.shape == f2.shape and torch.equal(v1.view(torch.int32), v2.view(torch.int32)) and torch.equal(f1, f2))
+        info["ok"] = ok and info["mesh_ok"]
         res.append(info)
     del v, F1
 cfg = cfgs
