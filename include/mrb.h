@@ -274,6 +274,52 @@ int  mrb_qp_plan_assemble_slab(mrb_qp_plan* plan, const float* x_dev, int x_begi
 int  mrb_mcubes_slab(mrb_ctx* ctx, const float* F_slab, const int dims[3], int x_origin, float isolevel, int device_out,
                      mrb_mesh* out);
 
+/* ---- front end: binvox completion + observed points -> occupancy grid -------------------------
+ * The reference does this on the CPU with PCL (mesh_reconstruction.cpp:99-120).  Points are xyz interleaved floats, finite.
+ * Outputs follow mrb_mesh's device_out convention (0 malloc'd host array, 1 the context's arena, 2 its pinned staging; 1 and 2
+ * are valid until the next call on the context). */
+typedef struct mrb_points { float* xyz; int n; int on_device; } mrb_points;
+typedef struct mrb_volume {
+    float* voxels;          /* dims[0]*dims[1]*dims[2] floats, 0 / 1, [x][y][z] */
+    int    dims[3];
+    float  scale[3], shift[3];   /* grid::scale / grid::shift (grid.cpp:94-120): voxel -> world by getCloudPoint */
+    int    pad;             /* 6 empty voxels on every side (grid.cpp:91) */
+    int    occupied_leaves; /* "PointCloud after filtering" (voxelize.cpp:48) */
+    int    on_device;
+} mrb_volume;
+typedef struct mrb_front_info {
+    float observed_dist_total;  int observed_count;     /* getDensity(observed): "Total Dist: .. Count: .." (binvoxToPcl.cpp:196) */
+    float completed_dist_total; int completed_count;    /* getDensity(binvoxToPCL(file, 1)) */
+    float observed_density, completed_density;          /* binvoxToPcl.cpp:205-209 (observed already scaled by 3/8) */
+    int   res_factor;
+    int   n_predicted;          /* points of binvoxToPCL(file, res_factor) */
+    int   n_cloud;              /* observed + predicted = "PointCloud before filtering" */
+    float leaf;                 /* getResolution: "Leaf size is" (voxelize.cpp:92-93) */
+} mrb_front_info;
+/* binvoxToPCL (binvoxToPCL/binvoxToPcl.cpp:105-169) on the decoded voxel bytes of a binvox file (read_binvox, :15-103, stays host
+ * I/O): dwh = {depth, width, height}, xform = {scale, tx, ty, tz}; voxel (x, y, z) is voxels[x*width*height + z*width + y]
+ * (get_index, :9-13).  Points in the reference's order (cell x, y, z, then sample i, j, k).  res_factor < 1 is MRB_EINVAL
+ * (the reference exits). */
+int  mrb_binvox_to_points(mrb_ctx* ctx, const unsigned char* voxels, const int dwh[3], const float xform[4], int res_factor,
+                          int device_out, mrb_points* out);
+void mrb_points_free(mrb_points* p);
+/* The statistic inside getDensity (binvoxToPcl.cpp:172-201) and getResolution (voxelize/voxelize.cpp:6-32): for every tenth point
+ * the distance to its nearest neighbour among the other nine tenths, summed in float in query order.  density = count / dist_total,
+ * leaf size = 2 * dist_total / count.  pcl::KdTreeFLANN itself is not in the reference tree: exact search, squared distance
+ * ((dx^2 + dy^2) + dz^2) in float. */
+int  mrb_nn_stats(mrb_ctx* ctx, const float* xyz, int n, float* dist_total, int* count);
+/* voxelize (voxelize.cpp:34-51) + grid(cloud, vox) (grid/grid.cpp:84-121) + fillGrid(res_factor) (grid.cpp:213-265; skipped for
+ * res_factor <= 0, as m_cubes does) + getBinaryVolume (grid.cpp:322-334) with every strength 1 (ConstConf(1),
+ * mesh_reconstruction.cpp:107).  pcl::VoxelGrid is restated: leaf (i, j, k) = floor(p * (1 / leaf)) - floor(min * (1 / leaf)),
+ * centroid = float sum of the leaf's points in cloud order / count. */
+int  mrb_voxelize_leaf(mrb_ctx* ctx, const float* xyz, int n, float leaf, int res_factor, int device_out, mrb_volume* out);
+void mrb_volume_free(mrb_volume* v);
+/* mesh_reconstruction.cpp:99-120 in one call: getResolutionFactor (res_factor < 1; a value >= 1 is taken as given), binvoxToPCL,
+ * observed points followed by the completion, voxelizeData, createGrid, getBinaryVolume.  With device_out = 1 the volume can be
+ * handed straight to mrb_reconstruct (which stages its own copy before the arena is reused).  info may be NULL. */
+int  mrb_front_end(mrb_ctx* ctx, const unsigned char* voxels, const int dwh[3], const float xform[4], const float* observed,
+                   int n_observed, int res_factor, int device_out, mrb_volume* out, mrb_front_info* info);
+
 #ifdef __cplusplus
 }
 #endif

@@ -25,6 +25,21 @@ class Mesh(C.Structure):
                 ("on_device", C.c_int)]
 
 
+class Points(C.Structure):
+    _fields_ = [("xyz", c_float_p), ("n", C.c_int), ("on_device", C.c_int)]
+
+
+class Volume(C.Structure):
+    _fields_ = [("voxels", c_float_p), ("dims", C.c_int * 3), ("scale", C.c_float * 3), ("shift", C.c_float * 3),
+                ("pad", C.c_int), ("occupied_leaves", C.c_int), ("on_device", C.c_int)]
+
+
+class FrontInfo(C.Structure):
+    _fields_ = [("observed_dist_total", C.c_float), ("observed_count", C.c_int), ("completed_dist_total", C.c_float),
+                ("completed_count", C.c_int), ("observed_density", C.c_float), ("completed_density", C.c_float),
+                ("res_factor", C.c_int), ("n_predicted", C.c_int), ("n_cloud", C.c_int), ("leaf", C.c_float)]
+
+
 class Options(C.Structure):
     _fields_ = [("using_features", C.c_int), ("band_size", C.c_int), ("iters", C.c_int), ("isolevel", C.c_float),
                 ("feature_threshold", C.c_float), ("corner_threshold", C.c_float)]
@@ -81,6 +96,13 @@ SYMBOLS = {
                                                 c_int_p, C.c_int]),
     "mrb_qp_plan_assemble_slab": (C.c_int, [_VP, _VP, C.c_int, C.c_int, _VP]),
     "mrb_mcubes_slab": (C.c_int, [_VP, _VP, c_int_p, C.c_int, C.c_float, C.c_int, C.POINTER(Mesh)]),
+    "mrb_binvox_to_points": (C.c_int, [_VP, _VP, c_int_p, c_float_p, C.c_int, C.c_int, C.POINTER(Points)]),
+    "mrb_points_free": (None, [C.POINTER(Points)]),
+    "mrb_nn_stats": (C.c_int, [_VP, _VP, C.c_int, c_float_p, c_int_p]),
+    "mrb_voxelize_leaf": (C.c_int, [_VP, _VP, C.c_int, C.c_float, C.c_int, C.c_int, C.POINTER(Volume)]),
+    "mrb_volume_free": (None, [C.POINTER(Volume)]),
+    "mrb_front_end": (C.c_int, [_VP, _VP, c_int_p, c_float_p, _VP, C.c_int, C.c_int, C.c_int, C.POINTER(Volume),
+                                C.POINTER(FrontInfo)]),
     "mrb_reconstruct_batch": (C.c_int, [_VP, _VP, c_int_p, C.c_int, C.POINTER(Options), C.POINTER(Mesh), c_int_p,
                                         c_int_p]),
 }

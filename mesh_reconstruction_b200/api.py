@@ -268,6 +268,65 @@ class Context:
                                              1 if like is not None else 2, C.byref(m)))
         return self._take_mesh(m, like)
 
+    # ---- front end (row f1): binvox completion + observed points -> occupancy volume ------------------------------------
+    def _take_volume(self, v, like):
+        dims = tuple(v.dims)
+        n = dims[0] * dims[1] * dims[2]
+        if v.on_device == 1:
+            import torch
+            vol = torch.empty(dims, dtype=torch.float32, device=like.device)
+            self._check(self.lib.mrb_copy(self.h, vol.data_ptr(), C.cast(v.voxels, C.c_void_p), n * 4))
+        else:
+            vol = np.ctypeslib.as_array(v.voxels, shape=(max(n, 1),))[:n].copy().reshape(dims)
+            self.lib.mrb_volume_free(C.byref(v))
+        return {"volume": vol, "dims": dims, "pad": v.pad, "occupied_leaves": v.occupied_leaves,
+                "scale": np.array(list(v.scale), np.float32), "shift": np.array(list(v.shift), np.float32)}
+
+    def binvox_to_points(self, voxels, dwh, xform, res_factor=1):
+        """binvoxToPCL (binvoxToPcl.cpp:105-169): the up-sampled completion as points [n, 3], in the reference's order.
+        voxels: decoded binvox bytes (read_binvox), dwh = (depth, width, height), xform = (scale, tx, ty, tz)."""
+        v = np.ascontiguousarray(voxels, np.uint8).ravel()
+        assert v.size == dwh[0] * dwh[1] * dwh[2]
+        p = L.Points()
+        self._check(self.lib.mrb_binvox_to_points(self.h, C.c_void_p(v.ctypes.data), (C.c_int * 3)(*dwh), (C.c_float * 4)(*xform),
+                                                  int(res_factor), 2, C.byref(p)))
+        return np.ctypeslib.as_array(p.xyz, shape=(max(p.n, 1), 3))[:p.n].copy()
+
+    def nn_stats(self, xyz):
+        """(dist_total, count) of getDensity / getResolution (binvoxToPcl.cpp:172-201, voxelize.cpp:6-32)."""
+        k, p, shape, like = self._in(xyz if _is_torch(xyz) else np.asarray(xyz, np.float32).reshape(-1, 3))
+        dt, cnt = C.c_float(0), C.c_int(0)
+        self._check(self.lib.mrb_nn_stats(self.h, p, int(shape[0]), C.byref(dt), C.byref(cnt)))
+        return np.float32(dt.value), cnt.value
+
+    def voxelize_leaf(self, xyz, leaf, res_factor):
+        """voxelize + grid(cloud, vox) + fillGrid + getBinaryVolume for a given leaf size (voxelize.cpp:34-51, grid.cpp:84-121,
+        213-265, 322-334).  Returns a dict: volume, dims, pad, scale, shift, occupied_leaves."""
+        k, p, shape, like = self._in(xyz if _is_torch(xyz) else np.asarray(xyz, np.float32).reshape(-1, 3))
+        v = L.Volume()
+        self._check(self.lib.mrb_voxelize_leaf(self.h, p, int(shape[0]), float(leaf), int(res_factor), 1 if like is not None else 2,
+                                               C.byref(v)))
+        return self._take_volume(v, like)
+
+    def front_end(self, voxels, dwh, xform, observed, res_factor=0, device=False):
+        """mesh_reconstruction.cpp:99-120 in one call (mrb_front_end): resolution factor (res_factor < 1: from the densities),
+        up-sampled completion, merged cloud, leaf size, occupancy volume.  device=True returns the volume as a CUDA tensor."""
+        vb = np.ascontiguousarray(voxels, np.uint8).ravel()
+        assert vb.size == dwh[0] * dwh[1] * dwh[2]
+        k, p, shape, like = self._in(observed if _is_torch(observed) else np.asarray(observed, np.float32).reshape(-1, 3))
+        if device and like is None:
+            import torch
+            like = torch.empty(0, device="cuda:%d" % self.device)
+        v, fi = L.Volume(), L.FrontInfo()
+        self._check(self.lib.mrb_front_end(self.h, C.c_void_p(vb.ctypes.data), (C.c_int * 3)(*dwh), (C.c_float * 4)(*xform), p,
+                                           int(shape[0]), int(res_factor), 1 if (device and like is not None) else 2, C.byref(v),
+                                           C.byref(fi)))
+        out = self._take_volume(v, like if device else None)
+        for name, _t in L.FrontInfo._fields_:
+            val = getattr(fi, name)
+            out[name] = np.float32(val) if _t is C.c_float else val
+        return out
+
     def mcubes_features(self, F, surfaceMap, normals, isolevel=0.0, feat_thresh=0.75, corner_thresh=0.8):
         """mcubes(..., USING_FEATURES=true) (mcubes.h:354): feature points, triangle fans and edge flips."""
         kF, pF, shape, like = self._in(F)

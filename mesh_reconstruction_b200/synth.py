@@ -203,3 +203,47 @@ def config_volume_t(cfg, device="cpu"):
             v = torch.maximum(v, sphere_t(512, r, c, device=device))
         return v
     raise ValueError(cfg)
+
+
+def completion_scene(n=40, kind="sphere", seed=0, view_fraction=0.5, observed_step=0.35, noise=0.002, z_shift=0.0,
+                     xform=(0.3, -0.12, 0.05, 0.6)):
+    """A synthetic input pair of the CLI (mesh_reconstruction.cpp:99-106): the shape-completion network's binvox grid and a
+    partial, denser, noisy point cloud of the same object as a depth camera would see it.
+
+    Returns (voxels, dwh, xform, observed): voxel bytes in binvox file order (index = x*width*height + z*width + y),
+    dwh = (depth, width, height), xform = (scale, tx, ty, tz), observed float32 [m, 3] in the binvox file's frame.
+    z_shift moves the observed points along z by that many binvox cells, which opens the gap fillGrid closes."""
+    rng = np.random.default_rng(seed)
+    d = w = h = int(n)
+    x, z, y = np.meshgrid(np.arange(d, dtype=np.float32), np.arange(h, dtype=np.float32), np.arange(w, dtype=np.float32), indexing="ij")
+    c = (n - 1) / 2.0
+    if kind == "sphere":
+        inside = (x - c) ** 2 + (y - c) ** 2 + (z - c) ** 2 <= (0.3 * n) ** 2
+    elif kind == "box":
+        inside = (np.abs(x - c) <= 0.28 * n) & (np.abs(y - c) <= 0.2 * n) & (np.abs(z - c) <= 0.24 * n)
+    elif kind == "blobs":
+        inside = np.zeros_like(x, dtype=bool)
+        for _ in range(4):
+            cc = rng.uniform(0.35 * n, 0.65 * n, 3)
+            r = rng.uniform(0.12 * n, 0.22 * n)
+            inside |= (x - cc[0]) ** 2 + (y - cc[1]) ** 2 + (z - cc[2]) ** 2 <= r * r
+    else:
+        raise ValueError(kind)
+    vox = inside.astype(np.uint8)                     # [x][z][y] = file order
+    # observed: surface samples on a finer lattice, the part with x below a cut ("seen from -x"), noisy
+    s = np.arange(0.0, n - 1.0, observed_step, dtype=np.float32)
+    gx, gy, gz = np.meshgrid(s, s, s, indexing="ij")
+    def occ(ax, ay, az):
+        ix, iy, iz = np.clip(np.rint(ax).astype(int), 0, n - 1), np.clip(np.rint(ay).astype(int), 0, n - 1), np.clip(np.rint(az).astype(int), 0, n - 1)
+        return vox[ix, iz, iy] > 0
+    o = occ(gx, gy, gz)
+    surf = o & ~(occ(gx - 1, gy, gz) & occ(gx + 1, gy, gz) & occ(gx, gy - 1, gz) & occ(gx, gy + 1, gz) & occ(gx, gy, gz - 1) & occ(gx, gy, gz + 1))
+    keep = surf & (gx <= np.quantile(gx[surf], view_fraction))
+    p = np.stack([gx[keep], gy[keep], gz[keep] + np.float32(z_shift)], 1).astype(np.float32)
+    p += rng.normal(0.0, noise * n, p.shape).astype(np.float32)
+    sc, tx, ty, tz = [np.float32(t) for t in xform]
+    obs = np.empty_like(p)
+    obs[:, 0] = (p[:, 0] + np.float32(0.5)) * sc / np.float32(d) + tx
+    obs[:, 1] = (p[:, 1] + np.float32(0.5)) * sc / np.float32(w) + ty
+    obs[:, 2] = (p[:, 2] + np.float32(0.5)) * sc / np.float32(h) + tz
+    return vox.ravel().copy(), (d, w, h), (sc, tx, ty, tz), np.ascontiguousarray(obs, np.float32)

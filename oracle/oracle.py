@@ -14,8 +14,8 @@ _lib = None
 
 
 def build(force=False):
-    src = os.path.join(_HERE, "mrb_oracle.cpp")
-    if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < os.path.getmtime(src):
+    srcs = [os.path.join(_HERE, f) for f in ("mrb_oracle.cpp", "frontend_oracle.cpp")]
+    if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < max(os.path.getmtime(f) for f in srcs):
         subprocess.check_call(["make", "-C", _HERE, "-s"])
     return _SO
 
@@ -237,3 +237,62 @@ def mcubes_features(F, surface_map, normals, isolevel=0.0, feat_thresh=0.75, cor
     faces = np.ctypeslib.as_array(mesh.faces, shape=(max(mesh.nfaces, 1), 3))[:mesh.nfaces].copy()
     lib().mrbo_mesh_free(C.byref(mesh))
     return verts, faces
+
+
+# ---- front end (row f1): oracle/frontend_oracle.cpp ------------------------------------------------------------------
+def binvox_to_points(voxels, dwh, xform, res):
+    """binvoxToPCL (binvoxToPcl.cpp:105-169) on decoded voxel bytes; dwh = (depth, width, height), xform = (scale, tx, ty, tz)."""
+    v = np.ascontiguousarray(voxels, dtype=np.uint8).ravel()
+    d = (C.c_int * 3)(*dwh)
+    x = (C.c_float * 4)(*xform)
+    vp = v.ctypes.data_as(C.POINTER(C.c_ubyte))
+    n = lib().fo_binvox_to_points(vp, d, x, C.c_int(res), None, C.c_int(0))
+    out = np.empty((n, 3), np.float32)
+    lib().fo_binvox_to_points(vp, d, x, C.c_int(res), out.ctypes.data_as(C.POINTER(C.c_float)), C.c_int(n))
+    return out
+
+
+def nn_stats(xyz):
+    """(dist_total, count) of getDensity / getResolution (binvoxToPcl.cpp:172-201, voxelize.cpp:6-32), exact brute-force NN."""
+    a, ap = _f(np.asarray(xyz).reshape(-1, 3))
+    dt, cnt = C.c_float(0), C.c_int(0)
+    lib().fo_nn_stats(ap, C.c_int(len(a)), C.byref(dt), C.byref(cnt))
+    return np.float32(dt.value), cnt.value
+
+
+def _front_out(meta, fmeta, vol):
+    return {"volume": vol, "dims": tuple(meta[:3]), "pad": meta[3], "occupied_leaves": meta[4],
+            "scale": np.array(fmeta[:3], np.float32), "shift": np.array(fmeta[3:6], np.float32)}
+
+
+def voxelize_leaf(xyz, leaf, res_factor):
+    """voxelize + grid(cloud, vox) + fillGrid + getBinaryVolume (voxelize.cpp:34-51, grid.cpp:84-121,213-265,322-334)."""
+    a, ap = _f(np.asarray(xyz).reshape(-1, 3))
+    meta, fmeta = (C.c_int * 5)(), (C.c_float * 6)()
+    rc = lib().fo_voxelize_leaf(ap, C.c_int(len(a)), C.c_float(leaf), C.c_int(res_factor), meta, fmeta, None, C.c_longlong(0))
+    if rc != 0:
+        raise RuntimeError("fo_voxelize_leaf failed (%d)" % rc)
+    vol = np.empty(tuple(meta[:3]), np.float32)
+    rc = lib().fo_voxelize_leaf(ap, C.c_int(len(a)), C.c_float(leaf), C.c_int(res_factor), meta, fmeta,
+                                vol.ctypes.data_as(C.POINTER(C.c_float)), C.c_longlong(vol.size))
+    assert rc == 0
+    return _front_out(meta, fmeta, vol)
+
+
+def front_end(voxels, dwh, xform, observed, res_factor=0, max_voxels=1 << 28):
+    """mesh_reconstruction.cpp:99-120: resolution factor, up-sampling, merged cloud, leaf size, occupancy volume."""
+    v = np.ascontiguousarray(voxels, dtype=np.uint8).ravel()
+    a, ap = _f(np.asarray(observed).reshape(-1, 3))
+    meta, fmeta, info, finfo = (C.c_int * 5)(), (C.c_float * 6)(), (C.c_int * 5)(), (C.c_float * 5)()
+    args = (v.ctypes.data_as(C.POINTER(C.c_ubyte)), (C.c_int * 3)(*dwh), (C.c_float * 4)(*xform), ap, C.c_int(len(a)), C.c_int(res_factor))
+    rc = lib().fo_front_end(*args, meta, fmeta, info, finfo, None, C.c_longlong(0))
+    if rc != 0:
+        raise RuntimeError("fo_front_end failed (%d)" % rc)
+    vol = np.empty(tuple(meta[:3]), np.float32)
+    rc = lib().fo_front_end(*args, meta, fmeta, info, finfo, vol.ctypes.data_as(C.POINTER(C.c_float)), C.c_longlong(vol.size))
+    assert rc == 0
+    out = _front_out(meta, fmeta, vol)
+    out.update(res_factor=info[0], n_predicted=info[1], n_cloud=info[2], observed_count=info[3], completed_count=info[4],
+               observed_dist_total=np.float32(finfo[0]), completed_dist_total=np.float32(finfo[1]),
+               observed_density=np.float32(finfo[2]), completed_density=np.float32(finfo[3]), leaf=np.float32(finfo[4]))
+    return out

@@ -274,3 +274,90 @@ def cloud_point(p, scale, shift, pad):
     out = np.empty(3, np.float32)
     _check(lib().ref_cloud_point(ap, sp, hp, pad, _fp(out)), "getCloudPoint")
     return out
+
+
+# ---- front end (row f1): oracle/_ref/libmrb_ref_front.so = binvoxToPcl.cpp, confidence_pcl/, voxelize.cpp, grid.cpp ----------
+_front = None
+
+
+def front_available():
+    so = os.path.join(_HERE, "_ref", "libmrb_ref_front.so")
+    if not os.path.exists(so) and os.path.isdir(os.environ.get("MRB_REFERENCE_DIR", "/root/reference")):
+        build()
+    return os.path.exists(so)
+
+
+def front():
+    global _front
+    if _front is None:
+        if not front_available():
+            raise RuntimeError("oracle/_ref/libmrb_ref_front.so is not built (needs /root/reference)")
+        _front = C.CDLL(os.path.join(_HERE, "_ref", "libmrb_ref_front.so"))
+        _front.reff_density.restype = C.c_float
+        _front.reff_resolution.restype = C.c_float
+    return _front
+
+
+def read_binvox(path):
+    """read_binvox (binvoxToPcl.cpp:15-103): (voxel bytes, (depth, width, height), (scale, tx, ty, tz))."""
+    hdr, fh = (C.c_int * 3)(), (C.c_float * 4)()
+    n = front().reff_read_binvox(path.encode(), hdr, fh, None, C.c_longlong(0))
+    if n < 0:
+        raise RuntimeError("read_binvox failed")
+    v = np.empty(n, np.uint8)
+    front().reff_read_binvox(path.encode(), hdr, fh, v.ctypes.data_as(C.POINTER(C.c_ubyte)), C.c_longlong(n))
+    return v, (hdr[0], hdr[2], hdr[1]), (fh[3], fh[0], fh[1], fh[2])
+
+
+def binvox_to_points(path, res):
+    n = front().reff_binvox_to_points(path.encode(), C.c_int(res), None, C.c_int(0))
+    out = np.empty((n, 3), np.float32)
+    front().reff_binvox_to_points(path.encode(), C.c_int(res), _fp(out), C.c_int(n))
+    return out
+
+
+def density(xyz):
+    a = np.ascontiguousarray(xyz, np.float32)
+    return np.float32(front().reff_density(_fp(a), C.c_int(len(a))))
+
+
+def resolution(xyz):
+    a = np.ascontiguousarray(xyz, np.float32)
+    return np.float32(front().reff_resolution(_fp(a), C.c_int(len(a))))
+
+
+def resolution_factor(path, observed):
+    a = np.ascontiguousarray(observed, np.float32)
+    return front().reff_resolution_factor(path.encode(), _fp(a), C.c_int(len(a)))
+
+
+def _vol_out(meta, fm, vol):
+    return {"volume": vol, "dims": tuple(meta[:3]), "pad": meta[3], "scale": np.array(fm[:3], np.float32), "shift": np.array(fm[3:6], np.float32)}
+
+
+def volume_of_cloud(xyz, res_factor):
+    """voxelizeData + createGrid(res_factor) + getBinaryVolume on a cloud whose strengths are all 1."""
+    a = np.ascontiguousarray(xyz, np.float32)
+    meta, fm, leaf = (C.c_int * 4)(), (C.c_float * 6)(), C.c_float()
+    rc = front().reff_volume_of_cloud(_fp(a), C.c_int(len(a)), C.c_int(res_factor), meta, fm, C.byref(leaf), None, C.c_longlong(0))
+    assert rc == 0
+    vol = np.empty(tuple(meta[:3]), np.float32)
+    rc = front().reff_volume_of_cloud(_fp(a), C.c_int(len(a)), C.c_int(res_factor), meta, fm, C.byref(leaf), _fp(vol), C.c_longlong(vol.size))
+    assert rc == 0
+    out = _vol_out(meta, fm, vol)
+    out["leaf"] = np.float32(leaf.value)
+    return out
+
+
+def front_end(binvox_path, observed):
+    """mesh_reconstruction.cpp:99-120."""
+    a = np.ascontiguousarray(observed, np.float32)
+    meta, fm, info, leaf = (C.c_int * 4)(), (C.c_float * 6)(), (C.c_int * 3)(), C.c_float()
+    rc = front().reff_front_end(binvox_path.encode(), _fp(a), C.c_int(len(a)), meta, fm, info, C.byref(leaf), None, C.c_longlong(0))
+    assert rc == 0
+    vol = np.empty(tuple(meta[:3]), np.float32)
+    rc = front().reff_front_end(binvox_path.encode(), _fp(a), C.c_int(len(a)), meta, fm, info, C.byref(leaf), _fp(vol), C.c_longlong(vol.size))
+    assert rc == 0
+    out = _vol_out(meta, fm, vol)
+    out.update(res_factor=info[0], n_predicted=info[1], n_cloud=info[2], leaf=np.float32(leaf.value))
+    return out
