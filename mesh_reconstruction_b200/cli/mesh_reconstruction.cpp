@@ -6,7 +6,8 @@
 // (:59-82) and the same exit codes (1 on success and on usage errors, 0 for --help; :50,:56,:136).
 // --cuda is accepted and selects the only compute path there is: the hot path always runs on the GPU
 // (no CPU fallback inside the library).  Extra, not in the reference: --dump-volume <file> writes the
-// occupancy grid the front end produced (dims as 3 int32, then float32 voxels) and skips the GPU stages.
+// occupancy grid the front end produced (dims as 3 int32, then float32 voxels) and skips the stages after it.
+// The front end itself (mesh_reconstruction.cpp:99-120) also runs on the GPU: mrb_front_end (csrc/mrb_frontend.cu).
 #include <cstdlib>
 #include <cstring>
 #include <iostream>
@@ -14,7 +15,7 @@
 #include <vector>
 
 #include "../compat/mesh_reconstruction_compat.h"
-#include "frontend.h"
+#include "readers.h"
 
 using namespace std;
 
@@ -56,24 +57,36 @@ int main(int argc, char** argv) {
     if (!mrbfront::load_pcd(pcd_path, observe)) { cerr << "Couldn't read pcd file " << endl; exit(1); }
     mrbfront::Binvox vox;
     if (!mrbfront::read_binvox(vox, binvox_path)) { cout << "Error reading [" << binvox_path << "]" << endl << endl; exit(1); }
-    int res = mrbfront::resolution_factor(vox, observe);
-    vector<mrbfront::P3> predict = mrbfront::binvox_to_points(vox, res);
-    vector<mrbfront::P3> all(observe);                 // full_confidence + assign_confidence(ConstConf(1))
-    all.insert(all.end(), predict.begin(), predict.end());
-    mrbfront::Volume vol = mrbfront::voxelize(all, res);
+    /* getResolutionFactor, binvoxToPCL, full_confidence + assign_confidence(ConstConf(1)), voxelizeData, createGrid and
+       getBinaryVolume (mesh_reconstruction.cpp:104-120) in one GPU call; the reference's progress lines from what it reports */
+    const int dwh[3] = {vox.depth, vox.width, vox.height};
+    const float xform[4] = {vox.scale, vox.tx, vox.ty, vox.tz};
+    mrb_volume vol;
+    mrb_front_info fi;
+    mrbcompat::check(mrb_front_end(mrbcompat::ctx(), vox.voxels.data(), dwh, xform, observe.empty() ? nullptr : &observe[0].x, (int)observe.size(),
+                                   0, 0, &vol, &fi));
+    cout << "Total Dist: " << fi.observed_dist_total << " Count: " << fi.observed_count << endl;
+    cout << "Total Dist: " << fi.completed_dist_total << " Count: " << fi.completed_count << endl;
+    cout << "Observed density: " << fi.observed_density << endl << "Completed density: " << fi.completed_density << endl;
+    cout << "Resolution Factor: " << fi.res_factor << endl;
+    cout << "Leaf size is " << fi.leaf << endl;
+    cout << "PointCloud before filtering: " << fi.n_cloud << " data points" << endl;
+    cout << "PointCloud after filtering: " << vol.occupied_leaves << " data points" << endl;
+    const size_t nvox = (size_t)vol.dims[0] * vol.dims[1] * vol.dims[2];
 
     if (!dump_volume.empty()) {
         FILE* f = fopen(dump_volume.c_str(), "wb");
         if (!f) { cerr << "cannot write " << dump_volume << endl; return 1; }
         fwrite(vol.dims, sizeof(int), 3, f);
-        fwrite(vol.voxels.data(), sizeof(float), vol.voxels.size(), f);
+        fwrite(vol.voxels, sizeof(float), nvox, f);
         fclose(f);
         return 1;
     }
 
     gridPtr volume(new grid(Eigen::Vector3i(vol.dims[0], vol.dims[1], vol.dims[2]), Eigen::Vector3f(vol.scale[0], vol.scale[1], vol.scale[2]),
                             Eigen::Vector3f(vol.shift[0], vol.shift[1], vol.shift[2]), vol.pad));
-    memcpy(volume->data(), vol.voxels.data(), vol.voxels.size() * sizeof(float));
+    memcpy(volume->data(), vol.voxels, nvox * sizeof(float));
+    mrb_volume_free(&vol);
 
     /* Perform feature detection (mesh_reconstruction.cpp:123-128) */
     vector<int> surface = getSurface(volume);

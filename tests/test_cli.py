@@ -1,4 +1,4 @@
-"""mesh_reconstruction CLI: argument handling and the PCL-free front end (CPU), the full run (GPU)."""
+"""mesh_reconstruction CLI: argument handling (CPU), the front end and the full run (GPU)."""
 import os
 import subprocess
 
@@ -31,7 +31,16 @@ def test_usage_and_exit_codes(cli):
     assert r.returncode == 1
 
 
-def test_front_end_volume(cli, synth, tmp_path):
+def read_pcd_ascii(path):
+    lines = open(path).read().splitlines()
+    start = next(i for i, l in enumerate(lines) if l.startswith("DATA")) + 1
+    return np.array([l.split()[:3] for l in lines[start:] if l.strip()], dtype=np.float64).astype(np.float32)
+
+
+@pytest.mark.gpu
+def test_front_end_volume(cli, synth, O, tmp_path):
+    """The CLI's front end runs on the GPU (mrb_front_end); its occupancy grid equals the CPU oracle's on the same files."""
+    from mesh_reconstruction_b200 import binvox
     bv, pcd = synth.cli_inputs(str(tmp_path))
     vol_path = tmp_path / "vol.bin"
     r = subprocess.run([cli, bv, pcd, str(tmp_path / "out.ply"), "--feature-threshold", "0.7", "--dump-volume", str(vol_path)],
@@ -42,6 +51,12 @@ def test_front_end_volume(cli, synth, tmp_path):
         assert line in r.stdout, line
     v = read_volume(vol_path)
     assert set(np.unique(v)) <= {0.0, 1.0}
+    vox, dwh, xf = binvox.read(bv)
+    ref = O.front_end(vox, dwh, xf, read_pcd_ascii(pcd))
+    assert ("Resolution Factor: %d" % ref["res_factor"]) in r.stdout
+    assert ("PointCloud before filtering: %d data points" % ref["n_cloud"]) in r.stdout
+    assert ("PointCloud after filtering: %d data points" % ref["occupied_leaves"]) in r.stdout
+    assert v.shape == ref["volume"].shape and np.array_equal(v, ref["volume"])
     occ = v == 1
     assert occ.sum() > 1000
     # pad = 6 empty voxels on every side (grid.cpp:91-114)
