@@ -308,6 +308,39 @@ def batch_record(ctx, args, world, rank, local):
             "faces_rank0": int(sum(len(m[1]) for m in meshes))}
 
 
+def front_end_record(ctx):
+    """Row f1 (mesh_reconstruction.cpp:99-120): a 40^3 binvox completion + a partial observed cloud -> occupancy grid through
+    mrb_front_end (host inputs, volume left on the device), then mrb_reconstruct on that volume: the whole CLI pipeline.
+    The CPU figure is the oracle restatement (brute-force nearest neighbour, all cores) on the same input, checked equal."""
+    import torch
+    from mesh_reconstruction_b200 import synth
+    from oracle import oracle as O
+    vox, dwh, xf, obs = synth.completion_scene(40, "blobs", seed=5, z_shift=1.0, observed_step=0.3)
+    fe = ctx.front_end(vox, dwh, xf, obs, device=True)
+    ctx.reconstruct(fe["volume"])
+    reps = 10
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        fe = ctx.front_end(vox, dwh, xf, obs, device=True)
+    t1 = time.perf_counter()
+    for _ in range(reps):
+        fe = ctx.front_end(vox, dwh, xf, obs, device=True)
+        verts, faces = ctx.reconstruct(fe["volume"])
+    torch.cuda.synchronize()
+    t2 = time.perf_counter()
+    c0 = time.perf_counter()
+    ref = O.front_end(vox, dwh, xf, obs)
+    c1 = time.perf_counter()
+    same = bool(np.array_equal(fe["volume"].cpu().numpy(), ref["volume"]) and fe["leaf"] == ref["leaf"] and
+                np.array_equal(fe["scale"], ref["scale"]) and np.array_equal(fe["shift"], ref["shift"]))
+    return {"workload": "40^3 binvox completion (4 blobs) + %d observed points -> %d points -> %dx%dx%d occupancy grid" %
+                        ((len(obs), fe["n_cloud"]) + tuple(fe["dims"])),
+            "res_factor": int(fe["res_factor"]), "front_end_ms": 1000.0 * (t1 - t0) / reps,
+            "front_end_plus_reconstruct_ms": 1000.0 * (t2 - t1) / reps, "faces": int(len(faces)),
+            "cpu_oracle_ms": 1000.0 * (c1 - c0), "cpu_threads": os.cpu_count(), "equals_cpu_oracle": same}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -487,6 +520,7 @@ def main():
         rec = batch_record(ctx, args, world, rank, local)
         if rank == 0:
             line["batch"] = rec
+            line["front_end"] = front_end_record(ctx)
     if rank == 0:
         print(json.dumps(line))
     ctx.close()

@@ -752,6 +752,24 @@ struct TiledBrickPred {
         return p >= 0 && base((size_t)p);
     }
 };
+// How many bricks of a block run in the second ("rim") phase of a sweep.  The rim bricks must; interior bricks may, and a
+// few do when that saves the interior phase a pass: a pass of a brick update is a ~1.5 us dependency chain however few
+// threads take part, so 505 interior bricks on 480 threads cost two passes (measured: 3.2 us against 1.5 us) and the block
+// falls behind its neighbours.  T threads; warp 0 collects the neighbours' flags first, so a single interior pass should
+// not reach it (T - 32 bricks).  threads <= 0: off (rim bricks only).
+__host__ __device__ __forceinline__ int late_count(int nrim, int nblock, int T) {
+    if (T <= 0) return nrim;
+    const int I = nblock - nrim;
+    // interior passes deal T bricks each, warp 0's 32 last: keep the last pass off warp 0 (at most T - 32 bricks in it) and
+    // drop a last pass that is less than half full
+    const int full = I / T, rem = I % T;
+    int keep = full * T + (rem < T - 32 ? rem : T - 32);
+    if (full > 0 && rem < T / 2) keep = full * T - 32;
+    int r = I - keep;
+    const int room = ((nrim > 0 ? nrim : 1) + T - 1) / T * T;        // the rim phase keeps its number of passes
+    if (r > 0 && nrim + r <= room) return nrim + r;
+    return nrim;
+}
 __global__ void k_tiled_scatter(const int* __restrict__ tpos, int Q, TiledOrder ord, int* __restrict__ bid1) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < Q) bid1[ord.position((size_t)tpos[i])] = i;
@@ -780,7 +798,7 @@ __global__ void k_tiled_boundary(const int* __restrict__ tpos, int Q, int G, Til
 }
 // final id = block begin + (boundary ? rank among the block's boundary bricks : #boundary + rank among its interior bricks)
 __global__ void k_tiled_final(const int* __restrict__ tpos, const int* __restrict__ sb, int Q, int G, TiledOrder ord,
-                              int* __restrict__ bpos, int* __restrict__ bid, int* __restrict__ blk_nb) {
+                              int* __restrict__ bpos, int* __restrict__ bid, int* __restrict__ blk_nb, int late_T) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= Q) return;
     const int b = tiled_owner(i, Q, G);
@@ -792,7 +810,7 @@ __global__ void k_tiled_final(const int* __restrict__ tpos, const int* __restric
     const int p = (int)ord.position((size_t)tpos[i]);
     bpos[id] = p;
     bid[p] = id;
-    if (i == qb) blk_nb[b] = nbc;
+    if (i == qb) blk_nb[b] = late_count(nbc, qe - qb, late_T);
 }
 
 __global__ void k_tiled_bitmap(const int4* __restrict__ nbA, const int2* __restrict__ nbB, int Q, int G, int NW,
@@ -1589,7 +1607,8 @@ int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_
         MRB_LAUNCH(ctx, k_tiled_scatter, cdiv(Q, 256), 256, 0, tpos, Q, ord, bid1);
         MRB_LAUNCH(ctx, k_tiled_boundary, cdiv(Q, 256), 256, 0, tpos, Q, t_grid, ord, bid1, sb);
         MRB_TRY(scan_exclusive(ctx, sb, sb, (size_t)Q, sb + Q));
-        MRB_LAUNCH(ctx, k_tiled_final, cdiv(Q, 256), 256, 0, tpos, sb, Q, t_grid, ord, bpos, bid, blk_nb);
+        MRB_LAUNCH(ctx, k_tiled_final, cdiv(Q, 256), 256, 0, tpos, sb, Q, t_grid, ord, bpos, bid, blk_nb,
+                   ((getenv("MRB_QP_LATE") && atoi(getenv("MRB_QP_LATE")) == 0) || (getenv("MRB_QP_ONCHIP") && atoi(getenv("MRB_QP_ONCHIP")))) ? 0 : t_threads);
     }
     const size_t Qn = (size_t)(Q > 0 ? Q : 1);
     const size_t P = tiled ? tiled_stride(Q) : (size_t)Q + 1;       // plane stride of the SoA iterate
@@ -1742,6 +1761,7 @@ int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_
                 const bool want_trace = getenv("MRB_QP_TRACE") && atoi(getenv("MRB_QP_TRACE")) && iters >= kTraceFirst + kTraceSweeps && t_threads <= 480;
                 if (want_trace) {
                     if (t_threads <= 480) t_kern = (void*)k_qp_bricks_tiled<480, 1, false, true>;     // launch bound >= the block size
+                    if (smem > 48 * 1024) MRB_CUDA(cudaFuncSetAttribute(t_kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
                     MRB_TRY(arena_alloc(ctx, (size_t)grid * kTraceSweeps * 8, &trace));
                     MRB_CUDA(cudaMemsetAsync(trace, 0, (size_t)grid * kTraceSweeps * 8 * sizeof(unsigned long long), ctx->stream));
                 }
@@ -1756,10 +1776,15 @@ int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_
                     MRB_CUDA(cudaMemcpyAsync(h.data(), trace, h.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
                     MRB_CUDA(cudaStreamSynchronize(ctx->stream));
                     const char* path = getenv("MRB_QP_TRACE_FILE") ? getenv("MRB_QP_TRACE_FILE") : "qp_trace.bin";
+                    std::vector<int> hnb(grid), hsz(grid);
+                    MRB_CUDA(cudaMemcpy(hnb.data(), blk_nb, grid * sizeof(int), cudaMemcpyDeviceToHost));
+                    for (int b = 0; b < grid; b++) hsz[b] = tiled_begin(b + 1, Q, grid) - tiled_begin(b, Q, grid);
                     if (FILE* f = fopen(path, "wb")) {
                         int hdr[4] = {grid, kTraceSweeps, 8, 1};
                         fwrite(hdr, sizeof(int), 4, f);
                         fwrite(h.data(), sizeof(unsigned long long), h.size(), f);
+                        fwrite(hnb.data(), sizeof(int), hnb.size(), f);       // rim bricks per block, bricks per block
+                        fwrite(hsz.data(), sizeof(int), hsz.size(), f);
                         fclose(f);
                     }
                 }
@@ -2085,7 +2110,7 @@ __global__ void k_sh_boundary(const int* __restrict__ tpos, int Qo, int G, Shard
 }
 __global__ void k_sh_final(const int* __restrict__ tpos, const int* __restrict__ sb, int Qo, int G, ShardSub sub,
                            const int* __restrict__ gbid, int* __restrict__ lmap, int* __restrict__ gid_of, int* __restrict__ pos_of,
-                           int* __restrict__ blk_nb) {
+                           int* __restrict__ blk_nb, int late_T) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= Qo) return;
     const int b = tiled_owner(i, Qo, G);
@@ -2098,7 +2123,7 @@ __global__ void k_sh_final(const int* __restrict__ tpos, const int* __restrict__
     lmap[sub.map_index(p)] = id;
     gid_of[id] = gbid[p];
     pos_of[id] = (int)p;
-    if (i == qb) blk_nb[b] = nbc;
+    if (i == qb) blk_nb[b] = late_count(nbc, qe - qb, late_T);
 }
 struct ShardBuild {
     int Qo, D, Qg, G;             // owned bricks, dummy slot, bricks of the whole plan, blocks
@@ -2418,7 +2443,8 @@ static int solve_sharded_tiled(mrb_qp_plan* plan, int rank, int world, void* con
     if (has_hi) MRB_LAUNCH(ctx, k_sh_halo_ids, cdiv(plane_n, 256), 256, 0, plan->bid, sub, Xb, Qo + nh_lo, po[Xb], lmap1, lmap);
     MRB_LAUNCH(ctx, k_sh_boundary, cdiv(Qo, 256), 256, 0, tpos, Qo, grid, sub, lmap1, sbuf);
     MRB_TRY(scan_exclusive(ctx, sbuf, sbuf, (size_t)Qo, sbuf + Qo));
-    MRB_LAUNCH(ctx, k_sh_final, cdiv(Qo, 256), 256, 0, tpos, sbuf, Qo, grid, sub, plan->bid, lmap, gid_of, pos_of, blk_nb);
+    MRB_LAUNCH(ctx, k_sh_final, cdiv(Qo, 256), 256, 0, tpos, sbuf, Qo, grid, sub, plan->bid, lmap, gid_of, pos_of, blk_nb,
+               (getenv("MRB_QP_LATE") && atoi(getenv("MRB_QP_LATE")) == 0) ? 0 : threads);
 
     // ---- slab-local constants, neighbour ids, initial iterate, peer slots
     uint2* code = nullptr;
