@@ -261,7 +261,8 @@ def slab_records(ctx, args, world, local):
     out["note"] = ("one grid on N GPUs, x-slabs: stage 3 in one persistent kernel per GPU (halo bricks stored into the neighbours' "
                    "buffers over NVLink peer memory, per-sweep flags); stage 4 per slab (F assembled on the rank's planes only, marching "
                    "cubes in whole-grid coordinates, shared-plane vertices owned by the lower rank, ids by prefix over the ranks); "
-                   "stages 1-2 on the whole grid on every rank")
+                   "stages 1-2: mode 'local' = on the rank's own planes + a margin of band_size + 5 planes (slab-local plan), mode 'sharded' = "
+                   "on the whole grid on every rank")
     return out
 
 
@@ -338,7 +339,8 @@ def front_end_record(ctx):
                         ((len(obs), fe["n_cloud"]) + tuple(fe["dims"])),
             "res_factor": int(fe["res_factor"]), "front_end_ms": 1000.0 * (t1 - t0) / reps,
             "front_end_plus_reconstruct_ms": 1000.0 * (t2 - t1) / reps, "faces": int(len(faces)),
-            "cpu_oracle_ms": 1000.0 * (c1 - c0), "cpu_threads": os.cpu_count(), "equals_cpu_oracle": same}
+            "cpu_oracle_ms": 1000.0 * (c1 - c0), "cpu_threads": int(os.environ.get("OMP_NUM_THREADS") or os.cpu_count()),
+            "equals_cpu_oracle": same}
 
 
 def main():
