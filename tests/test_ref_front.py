@@ -200,3 +200,28 @@ def test_gpu_front_end_argument_errors(ctx):
     assert ctx.binvox_to_points(v, (3, 3, 3), (1, 0, 0, 0), 2).shape == (0, 3)      # an empty completion: no points, no error
     with pytest.raises(mrb.MrbError):
         ctx.voxelize_leaf(np.zeros((4, 3), np.float32), 0.0, 1)
+
+
+@pytest.mark.gpu
+def test_gpu_voxel_grid_on_random_clouds(ctx, O):
+    """Negative coordinates, large offsets (few mantissa bits left for the leaf index), planar and clustered clouds, duplicates,
+    leaves with hundreds of points (float summation order inside a leaf), res_factor 0..5."""
+    rng = np.random.default_rng(21)
+    def clouds():
+        yield "uniform_neg", rng.uniform(-3.0, -1.0, (20000, 3)), 0.05
+        yield "offset_1e3", rng.uniform(0.0, 1.0, (15000, 3)) + [1000.0, -2000.0, 500.0], 0.04
+        yield "planar", np.stack([rng.uniform(0, 2, 12000), rng.uniform(0, 1, 12000), np.full(12000, 0.3)], 1), 0.03
+        yield "clusters", np.concatenate([rng.normal(c, 0.02, (4000, 3)) for c in ([0, 0, 0], [0.5, 0.1, -0.4], [0.2, 0.9, 0.3])]), 0.015
+        yield "dense_leaves", rng.uniform(0.0, 0.3, (30000, 3)), 0.1
+        yield "duplicates", np.repeat(rng.uniform(0, 1, (3000, 3)), 4, axis=0), 0.06
+        g = np.arange(0, 24, dtype=np.float64) * 0.125                       # points exactly on leaf boundaries
+        yield "lattice", np.stack(np.meshgrid(g, g, g, indexing="ij"), -1).reshape(-1, 3), 0.25
+    for name, pts, leaf in clouds():
+        pts = np.ascontiguousarray(pts, np.float32)
+        for rf in (0, 1, 5):
+            a, b = ctx.voxelize_leaf(pts, leaf, rf), O.voxelize_leaf(pts, leaf, rf)
+            assert a["dims"] == b["dims"] and a["occupied_leaves"] == b["occupied_leaves"], (name, rf)
+            assert np.array_equal(a["scale"], b["scale"]) and np.array_equal(a["shift"], b["shift"]), (name, rf, a["scale"], b["scale"])
+            assert np.array_equal(a["volume"], b["volume"]), (name, rf)
+        ga, oa = ctx.nn_stats(pts), O.nn_stats(pts)
+        assert ga[1] == oa[1] and ga[0] == oa[0], (name, ga, oa)
