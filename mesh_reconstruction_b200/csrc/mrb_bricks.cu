@@ -1672,7 +1672,7 @@ int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_
             const size_t smem_max = (size_t)220 * 1024 / (size_t)t_fit;
             if (getenv("MRB_QP_BRICK_COMPACT") || !expanded || smem > smem_max) { expanded = 0; smem = (size_t)cap * 64; }
             if (getenv("MRB_QP_BRICK_NOSMEM") || smem > 96 * 1024 / (size_t)t_fit) { if (!expanded) { cap = 0; smem = 0; } }
-            if (smem > 48 * 1024) MRB_CUDA(cudaFuncSetAttribute(t_kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            MRB_CUDA(allow_dyn_smem((const void*)t_kern, smem));
             int its = iters, QQ = Q;
             // On-chip kernel (the block's iterate in shared memory for all sweeps): binary volumes whose per-block share fits
             // (up to kOcCap bricks and kOcHalo foreign neighbour bricks per SM: band 4 up to about 256^3).  OPT-IN with
@@ -1761,7 +1761,7 @@ int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_
                 const bool want_trace = getenv("MRB_QP_TRACE") && atoi(getenv("MRB_QP_TRACE")) && iters >= kTraceFirst + kTraceSweeps && t_threads <= 480;
                 if (want_trace) {
                     if (t_threads <= 480) t_kern = (void*)k_qp_bricks_tiled<480, 1, false, true>;     // launch bound >= the block size
-                    if (smem > 48 * 1024) MRB_CUDA(cudaFuncSetAttribute(t_kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+                    MRB_CUDA(allow_dyn_smem((const void*)t_kern, smem));
                     MRB_TRY(arena_alloc(ctx, (size_t)grid * kTraceSweeps * 8, &trace));
                     MRB_CUDA(cudaMemsetAsync(trace, 0, (size_t)grid * kTraceSweeps * 8 * sizeof(unsigned long long), ctx->stream));
                 }
@@ -1830,8 +1830,8 @@ int bricks_solve(mrb_ctx* ctx, const float* vol, const float* fmap, const uint8_
             size_t smem = (size_t)cap * 64;
             if (getenv("MRB_QP_BRICK_NOSMEM") || smem > 96 * 1024 / (size_t)fit) { cap = 0; smem = 0; }
             if (smem > 48 * 1024) {
-                MRB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-                MRB_CUDA(cudaFuncSetAttribute(kern_block, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+                MRB_CUDA(allow_dyn_smem((const void*)kern, smem));
+                MRB_CUDA(allow_dyn_smem((const void*)kern_block, smem));
             }
             // producer lists of the warp chunks (warp-dataflow synchronisation)
             int *plist = nullptr, *pcount = nullptr;
@@ -2537,7 +2537,7 @@ static int solve_sharded_tiled(mrb_qp_plan* plan, int rank, int world, void* con
         size_t smem = (size_t)cap * 168;
         if (getenv("MRB_QP_BRICK_COMPACT") || smem > (size_t)220 * 1024 / (size_t)fit) { expanded = 0; smem = (size_t)cap * 64; }
         if (!expanded && smem > 96 * 1024 / (size_t)fit) { cap = 0; smem = 0; }
-        if (smem > 48 * 1024) MRB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        MRB_CUDA(allow_dyn_smem((const void*)kern, smem));
         int its = iters, QQ = Qo, dbg = 32;      // thread 0 publishes (the configuration the multi-GPU runs were validated with)
         size_t PP = P;
         unsigned long long* no_trace = nullptr;

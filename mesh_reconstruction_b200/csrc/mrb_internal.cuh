@@ -150,6 +150,15 @@ inline int sync(mrb_ctx* ctx) {
         MRB_CUDA(cudaGetLastError());                                               \
     } while (0)
 
+// Opt-in to more than 48 KB of dynamic shared memory.  The attribute belongs to the function, not to the launch, and contexts on
+// several host threads launch the same kernels with different sizes: always ask for the largest size any call uses (220 KB), so
+// that one thread can never lower it under another thread's launch.
+inline cudaError_t allow_dyn_smem(const void* kern, size_t smem) {
+    if (smem <= 48 * 1024) return cudaSuccess;
+    const size_t most = (size_t)220 * 1024;
+    return cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(smem > most ? smem : most));
+}
+
 inline unsigned cdiv(size_t a, size_t b) { return (unsigned)((a + b - 1) / b); }
 
 // ---- device-wide primitives (mrb_scan.cu) ----

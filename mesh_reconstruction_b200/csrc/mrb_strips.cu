@@ -26,6 +26,7 @@
 #include "mrb_internal.cuh"
 #include "mrb_compact.cuh"
 
+#include <algorithm>
 #include <cooperative_groups.h>
 namespace cg = cooperative_groups;
 
@@ -533,7 +534,7 @@ static int solve_strips(mrb_ctx* ctx, const StripBand& sb, int iters, float4** r
     if (grid > need) grid = need;
     int cap = (S + grid - 1) / grid;
     size_t smem = mode == 0 ? (size_t)cap * 40 : 0;
-    if (smem > 48 * 1024) MRB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    MRB_CUDA(allow_dyn_smem((const void*)kern, smem));
     int fit = 0;
     MRB_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessorWithFlags(&fit, kern, block, smem, 0));
     if (fit < 1) { set_error("k_qp_strips does not fit on an SM"); return MRB_ECUDA; }
@@ -541,7 +542,7 @@ static int solve_strips(mrb_ctx* ctx, const StripBand& sb, int iters, float4** r
         grid = fit * ctx->sm_count;
         cap = (S + grid - 1) / grid;
         if (mode == 0) { smem = (size_t)cap * 40; if (smem > kSmemBudget) { set_error("k_qp_strips: ids do not fit in shared memory"); return MRB_ECUDA; } }
-        if (smem > 48 * 1024) MRB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        MRB_CUDA(allow_dyn_smem((const void*)kern, smem));
     }
     const uint32_t* code = sb.code;
     const float4 *lb4 = sb.lb4, *ub4 = sb.ub4, *inv4 = sb.inv4;
@@ -559,6 +560,177 @@ static int solve_strips(mrb_ctx* ctx, const StripBand& sb, int iters, float4** r
     MRB_CUDA(cudaEventRecord(ctx->ev[7], ctx->stream));
     ctx->launches++;
     *result = (iters % 2) ? sb.xb : sb.xa;
+    if (last_delta_host) {
+        MRB_CUDA(cudaMemcpyAsync(ctx->h_mail + 8, md, sizeof(unsigned), cudaMemcpyDeviceToHost, ctx->stream));
+        MRB_CUDA(cudaStreamSynchronize(ctx->stream));
+        unsigned bits = (unsigned)ctx->h_mail[8];
+        memcpy(last_delta_host, &bits, sizeof(float));
+    }
+    return MRB_OK;
+}
+
+// ---- small bands: the whole solve inside ONE thread-block cluster ---------------------------------------------------
+// Grids of the size the reference was written for (40^3 completions: 40 .. 64 voxels per edge, up to ~30 000 strips) are
+// pure synchronisation latency in k_qp_strips: 2.7 us per sweep whatever the size (flag or grid-barrier round trips through
+// L2), 1.35 ms for 500 sweeps.  Here the band lives in the shared memory of a cluster of up to 16 CTAs for the whole solve:
+//   * CTA r owns strips [r*cap, (r+1)*cap): both iterate buffers, the constants and, per strip, the ten neighbour strips as
+//     32-bit shared::cluster addresses (mapa once at start-up), so a neighbour in another CTA is one ld.shared::cluster
+//     (distributed shared memory, ~215 cycles) and costs no index arithmetic in the sweep;
+//   * one hardware cluster barrier per sweep (barrier.cluster arrive.release / wait.acquire, ~380 cycles) instead of flags
+//     in global memory; nothing touches L2 or HBM between the initial load and the final store.
+// The per-voxel arithmetic is qp_voxel, the same instruction sequence as k_qp_strips: bit-identical results.
+static const int kClThreads = 512;
+static const int kClBytesPerStrip = 2 * 16 + 3 * 16 + 4 + 10 * 4;          // xa, xb, lb, ub, inv, code, 10 neighbour addresses
+static const int kClCapMax = (227 * 1024 - 64) / kClBytesPerStrip - 1;      // strips per CTA
+__device__ __forceinline__ float4 ld_cluster4(uint32_t addr) {
+    float4 v;
+    asm volatile("ld.shared::cluster.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr) : "memory");
+    return v;
+}
+__device__ __forceinline__ uint32_t mapa_cluster(uint32_t local_addr, uint32_t rank) {
+    uint32_t r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local_addr), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__global__ void __launch_bounds__(kClThreads, 1) k_qp_cluster(const uint32_t* __restrict__ code, const float4* __restrict__ lb4,
+                                                              const float4* __restrict__ ub4, const float4* __restrict__ inv4,
+                                                              const int4* __restrict__ nbA, const int4* __restrict__ nbB,
+                                                              const int2* __restrict__ nbC, float4* xa, float4* xb, int S, int iters, int cap,
+                                                              unsigned* __restrict__ maxdelta_bits) {
+    extern __shared__ float4 s_cl[];
+    // layout (the same in every CTA of the cluster): xA[cap+1] | xB[cap+1] | lb[cap] | ub[cap] | inv[cap] | code[cap] | nb[cap][10]
+    float4* s_xa = s_cl;
+    float4* s_xb = s_xa + (cap + 1);
+    float4* s_lb = s_xb + (cap + 1);
+    float4* s_ub = s_lb + cap;
+    float4* s_inv = s_ub + cap;
+    uint32_t* s_code = (uint32_t*)(s_inv + cap);
+    uint32_t* s_nb = s_code + cap;
+    uint32_t rank;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
+    const int s_begin = (int)rank * cap;
+    const int n_own = max(0, min(S - s_begin, cap));
+    const uint32_t xa_local = (uint32_t)__cvta_generic_to_shared(s_xa);
+    const uint32_t buf_off = (uint32_t)(cap + 1) * 16u;                     // xB = xA + buf_off in every CTA
+    // a neighbour strip id -> shared::cluster address of its slot in buffer A (slot cap of the own CTA = the all-zero dummy)
+    auto slot_addr = [&](int id) -> uint32_t {
+        if (id >= S) return xa_local + (uint32_t)cap * 16u;
+        const uint32_t r = (uint32_t)(id / cap), l = (uint32_t)(id - (int)r * cap);
+        return mapa_cluster(xa_local + l * 16u, r);
+    };
+    for (int l = threadIdx.x; l < n_own; l += kClThreads) {
+        const int s = s_begin + l;
+        s_xa[l] = xa[s];
+        s_xb[l] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        s_lb[l] = __ldg(lb4 + s); s_ub[l] = __ldg(ub4 + s); s_inv[l] = __ldg(inv4 + s);
+        s_code[l] = __ldg(code + s);
+        const int4 a = __ldg(nbA + s), b = __ldg(nbB + s);
+        const int2 c = __ldg(nbC + s);
+        uint32_t* nb = s_nb + (size_t)l * 10;
+        nb[0] = slot_addr(a.x); nb[1] = slot_addr(a.y); nb[2] = slot_addr(a.z); nb[3] = slot_addr(a.w);
+        nb[4] = slot_addr(b.x); nb[5] = slot_addr(b.y); nb[6] = slot_addr(b.z); nb[7] = slot_addr(b.w);
+        nb[8] = slot_addr(c.x); nb[9] = slot_addr(c.y);
+    }
+    if (threadIdx.x == 0) { s_xa[cap] = make_float4(0.0f, 0.0f, 0.0f, 0.0f); s_xb[cap] = make_float4(0.0f, 0.0f, 0.0f, 0.0f); }
+    cluster_sync_all();
+    uint32_t off = 0;                                                          // buffer the sweep reads: 0 = A, buf_off = B
+    float dmax = 0.0f;
+    for (int it = 0; it < iters; it++) {
+        float4* s_out = off ? s_xa : s_xb;
+        for (int l = threadIdx.x; l < n_own; l += kClThreads) {
+            const uint32_t* nb = s_nb + (size_t)l * 10;
+            const uint32_t c = s_code[l];
+            const float4 xc = ld_cluster4(xa_local + (uint32_t)l * 16u + off);
+            const float4 xm2 = ld_cluster4(nb[0] + off), xm1 = ld_cluster4(nb[1] + off), ym2 = ld_cluster4(nb[2] + off), ym1 = ld_cluster4(nb[3] + off);
+            const float4 zlo = ld_cluster4(nb[4] + off), zhi = ld_cluster4(nb[5] + off), yp1 = ld_cluster4(nb[6] + off), yp2 = ld_cluster4(nb[7] + off);
+            const float4 xp1 = ld_cluster4(nb[8] + off), xp2 = ld_cluster4(nb[9] + off);
+            const float4 lb = s_lb[l], ub = s_ub[l], inv = s_inv[l];
+            float4 r;
+            r.x = qp_voxel<1u << 0, 1u << 6, 1u << 10, 1u << 14, 1u << 18, 1u << 4, 1u << 1>(
+                c, xc.x, xm2.x, xm1.x, ym2.x, ym1.x, zlo.z, zlo.w, xc.y, xc.z, yp1.x, yp2.x, xp1.x, xp2.x, inv.x, lb.x, ub.x);
+            r.y = qp_voxel<1u << 1, 1u << 7, 1u << 11, 1u << 15, 1u << 19, 1u << 0, 1u << 2>(
+                c, xc.y, xm2.y, xm1.y, ym2.y, ym1.y, zlo.w, xc.x, xc.z, xc.w, yp1.y, yp2.y, xp1.y, xp2.y, inv.y, lb.y, ub.y);
+            r.z = qp_voxel<1u << 2, 1u << 8, 1u << 12, 1u << 16, 1u << 20, 1u << 1, 1u << 3>(
+                c, xc.z, xm2.z, xm1.z, ym2.z, ym1.z, xc.x, xc.y, xc.w, zhi.x, yp1.z, yp2.z, xp1.z, xp2.z, inv.z, lb.z, ub.z);
+            r.w = qp_voxel<1u << 3, 1u << 9, 1u << 13, 1u << 17, 1u << 21, 1u << 2, 1u << 5>(
+                c, xc.w, xm2.w, xm1.w, ym2.w, ym1.w, xc.y, xc.z, zhi.x, zhi.y, yp1.w, yp2.w, xp1.w, xp2.w, inv.w, lb.w, ub.w);
+            s_out[l] = r;
+            if (it == iters - 1)
+                dmax = fmaxf(fmaxf(dmax, fmaxf(fabsf(r.x - xc.x), fabsf(r.y - xc.y))), fmaxf(fabsf(r.z - xc.z), fabsf(r.w - xc.w)));
+        }
+        off ^= buf_off;
+        // every CTA's stores of this sweep before anybody's loads of the next (and their loads of this sweep before the next
+        // sweep's stores into the same buffer); after the last sweep nobody reads remote memory any more
+        if (it + 1 < iters) cluster_sync_all();
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) dmax = fmaxf(dmax, __shfl_xor_sync(0xffffffffu, dmax, o));
+    if ((threadIdx.x & 31) == 0 && iters > 0) atomicMax(maxdelta_bits, __float_as_uint(dmax));
+    // the result goes where k_qp_strips leaves it: buffer B after an odd number of sweeps, A after an even one
+    float4* gout = (iters & 1) ? xb : xa;
+    const float4* s_res = (iters & 1) ? s_xb : s_xa;
+    for (int l = threadIdx.x; l < n_own; l += kClThreads) gout[s_begin + l] = s_res[l];
+    // a CTA must not exit while another may still read its shared memory (the last sweep's loads): one more barrier
+    cluster_sync_all();
+}
+
+// Returns MRB_OK with *used = true when the cluster kernel ran.
+static int solve_strips_cluster(mrb_ctx* ctx, const StripBand& sb, int iters, float4** result, float* last_delta_host, bool* used) {
+    *used = false;
+    const int S = sb.S;
+    if (S == 0 || iters == 0) return MRB_OK;
+    const char* e = getenv("MRB_QP_CLUSTER");
+    if (e && atoi(e) == 0) return MRB_OK;
+    // Sixteen SMs do all the arithmetic: measured on B200 1.4 us per sweep with one strip per thread (42^3), 1.9 us with two
+    // (52^3), 3.0 us with three (64^3) against 2.7 us for k_qp_strips on all SMs -- so up to two strips per thread.
+    const int kClStripsMax = e && atoi(e) > 1 ? 16 * kClCapMax : 2 * 16 * kClThreads;
+    if (S > kClStripsMax) return MRB_OK;
+    int cs = 1;
+    while (cs < 16 && (cs * kClThreads < S || (S + cs - 1) / cs > kClCapMax)) cs *= 2;
+    if (e && atoi(e) > 1) cs = atoi(e);                       // tuning knob: the cluster size
+    if (cs != 1 && cs != 2 && cs != 4 && cs != 8 && cs != 16) return MRB_OK;
+    const int cap = (S + cs - 1) / cs;
+    if (cap > kClCapMax) return MRB_OK;                       // does not fit: the L2-resident kernel
+    const size_t smem = (size_t)cap * kClBytesPerStrip + 2 * 16 + 16;
+    {
+        // function attributes are process-wide: set once to the largest value any call can need (contexts on several host
+        // threads launch this kernel with different sizes)
+        static bool attr_set[64] = {false};
+        if (!attr_set[ctx->device & 63]) {
+            MRB_CUDA(cudaFuncSetAttribute(k_qp_cluster, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+            MRB_CUDA(cudaFuncSetAttribute(k_qp_cluster, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+            attr_set[ctx->device & 63] = true;
+        }
+    }
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3(cs);
+    cfg.blockDim = dim3(kClThreads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = ctx->stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = cs; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    int nclusters = 0;
+    if (cudaOccupancyMaxActiveClusters(&nclusters, k_qp_cluster, &cfg) != cudaSuccess || nclusters < 1) {
+        cudaGetLastError();
+        return MRB_OK;                                        // this GPU cannot co-schedule such a cluster
+    }
+    unsigned* md = (unsigned*)(ctx->d_mail + 8);
+    MRB_CUDA(cudaMemsetAsync(md, 0, sizeof(unsigned), ctx->stream));
+    MRB_CUDA(cudaEventRecord(ctx->ev[6], ctx->stream));
+    MRB_CUDA(cudaLaunchKernelEx(&cfg, k_qp_cluster, (const uint32_t*)sb.code, (const float4*)sb.lb4, (const float4*)sb.ub4,
+                                (const float4*)sb.inv4, (const int4*)sb.nbA, (const int4*)sb.nbB, (const int2*)sb.nbC, sb.xa, sb.xb, S,
+                                iters, cap, md));
+    MRB_CUDA(cudaEventRecord(ctx->ev[7], ctx->stream));
+    ctx->launches++;
+    *result = (iters % 2) ? sb.xb : sb.xa;
+    *used = true;
     if (last_delta_host) {
         MRB_CUDA(cudaMemcpyAsync(ctx->h_mail + 8, md, sizeof(unsigned), cudaMemcpyDeviceToHost, ctx->stream));
         MRB_CUDA(cudaStreamSynchronize(ctx->stream));
@@ -712,7 +884,10 @@ int optimize_strips(mrb_ctx* ctx, const float* vol, const float* fmap, Dims d, i
     }
     float4* xres = nullptr;
     float last_delta = 0.0f;
-    MRB_TRY(solve_strips(ctx, sb, iters, &xres, stats ? &last_delta : nullptr));
+    bool in_cluster = false;
+    xres = sb.xa;
+    MRB_TRY(solve_strips_cluster(ctx, sb, iters, &xres, stats ? &last_delta : nullptr, &in_cluster));
+    if (!in_cluster) MRB_TRY(solve_strips(ctx, sb, iters, &xres, stats ? &last_delta : nullptr));
     if (using_features && fmap && sb.S > 0) {
         int* flag = ctx->d_mail + 16;
         MRB_CUDA(cudaMemsetAsync(flag, 0, sizeof(int), ctx->stream));

@@ -155,6 +155,9 @@ def test_optimize_sync_and_layout_variants(ctx, O, synth, monkeypatch):
                 dict(B, MRB_QP_ORDER="morton"), dict(B, MRB_QP_ORDER="morton:2,2,8"),
                 X, dict(X, MRB_QP_SYNC="flow"), dict(X, MRB_QP_BRICK_THREADS="512"), dict(X, MRB_QP_BRICK_THREADS="128"),
                 dict(X, MRB_QP_BRICK_NOSMEM="1"), {"MRB_QP_LAYOUT": "strips"},
+                # strips: the default for a grid this small is the thread-block-cluster kernel (band in distributed shared
+                # memory); cluster sizes 16 / 8 / 4 and the L2-resident kernel it replaces
+                {"MRB_QP_CLUSTER": "16"}, {"MRB_QP_CLUSTER": "8"}, {"MRB_QP_CLUSTER": "4"}, {"MRB_QP_CLUSTER": "0"},
                 {"MRB_QP_LAYOUT": "strips", "MRB_QP_VARIANT": "0:1024"}, {"MRB_QP_LAYOUT": "strips", "MRB_QP_VARIANT": "2:512"}):
         for k, val in env.items():
             monkeypatch.setenv(k, val)
@@ -301,6 +304,24 @@ def test_pool_of_contexts(ctx, synth):
     for v, (verts, faces) in zip(vols, got):
         v1, f1 = ctx.reconstruct(v, iters=60)
         assert np.array_equal(faces, f1) and np.array_equal(verts, v1)
+
+
+def test_cluster_kernel_sizes_and_sweep_parity(ctx, O, synth):
+    """k_qp_cluster (small bands, one thread-block cluster): odd and even sweep counts (the result lies in the other buffer),
+    one sweep, bands of a few strips, ragged grids; and contexts on several host threads with DIFFERENT sizes at once (the
+    shared-memory opt-in of a kernel is process-wide)."""
+    import mesh_reconstruction_b200 as mrb
+    for v, its in ((synth.sphere(52, 17.0), 1), (synth.sphere(52, 17.0), 7), (synth.sphere(42, 13.0), 500), (synth.sphere(30, 4.0), 33),
+                   (synth.ellipsoid((30, 26, 33), (6.0, 4.5, 7.5), (14.5, 12.0, 16.0)), 40), (synth.torus(56, 14.0, 5.0), 64)):
+        F, st = ctx.optimize(v, iters=its, return_stats=True)
+        assert np.array_equal(F, O.optimize(v, iters=its)), (v.shape, its)
+    vols = [synth.sphere(52, 17.0), synth.sphere(30, 4.0), synth.sphere(42, 13.0), synth.torus(56, 14.0, 5.0), synth.sphere(64, 24.0),
+            synth.sphere(36, 9.0)] * 3
+    refs = [ctx.reconstruct(v, iters=40) for v in vols[:6]]
+    with mrb.Pool(0, workers=4) as pool:
+        got = pool.map(vols, iters=40)
+    for i, (verts, faces) in enumerate(got):
+        assert np.array_equal(faces, refs[i % 6][1]) and np.array_equal(verts, refs[i % 6][0]), i
 
 
 @pytest.mark.gpu
