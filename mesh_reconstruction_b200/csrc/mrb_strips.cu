@@ -581,7 +581,7 @@ static int solve_strips(mrb_ctx* ctx, const StripBand& sb, int iters, float4** r
 // The per-voxel arithmetic is qp_voxel, the same instruction sequence as k_qp_strips: bit-identical results.
 static const int kClThreads = 512;
 static const int kClBytesPerStrip = 2 * 16 + 3 * 16 + 4 + 10 * 4;          // xa, xb, lb, ub, inv, code, 10 neighbour addresses
-static const int kClCapMax = (227 * 1024 - 64) / kClBytesPerStrip - 1;      // strips per CTA
+static const int kClCapMax = 2 * kClThreads;                               // strips per CTA: at most two per thread
 __device__ __forceinline__ float4 ld_cluster4(uint32_t addr) {
     float4 v;
     asm volatile("ld.shared::cluster.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr) : "memory");
@@ -595,13 +595,17 @@ __device__ __forceinline__ uint32_t mapa_cluster(uint32_t local_addr, uint32_t r
 __device__ __forceinline__ void cluster_sync_all() {
     asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
+// REGS: one strip per thread at most -- the thread keeps it for the whole solve, so its ten neighbour addresses, tight-mask word
+// and 1/d live in registers and shared memory holds the two iterate buffers and the bounds only.  !REGS: up to kClCapMax strips
+// per CTA, those per-strip words in shared memory as well.
+template <bool REGS>
 __global__ void __launch_bounds__(kClThreads, 1) k_qp_cluster(const uint32_t* __restrict__ code, const float4* __restrict__ lb4,
                                                               const float4* __restrict__ ub4, const float4* __restrict__ inv4,
                                                               const int4* __restrict__ nbA, const int4* __restrict__ nbB,
                                                               const int2* __restrict__ nbC, float4* xa, float4* xb, int S, int iters, int cap,
                                                               unsigned* __restrict__ maxdelta_bits) {
     extern __shared__ float4 s_cl[];
-    // layout (the same in every CTA of the cluster): xA[cap+1] | xB[cap+1] | lb[cap] | ub[cap] | inv[cap] | code[cap] | nb[cap][10]
+    // layout (the same in every CTA of the cluster): xA[cap+1] | xB[cap+1] | lb[cap] | ub[cap] | !REGS: inv[cap] | code[cap] | nb[cap][10]
     float4* s_xa = s_cl;
     float4* s_xb = s_xa + (cap + 1);
     float4* s_lb = s_xb + (cap + 1);
@@ -621,45 +625,63 @@ __global__ void __launch_bounds__(kClThreads, 1) k_qp_cluster(const uint32_t* __
         const uint32_t r = (uint32_t)(id / cap), l = (uint32_t)(id - (int)r * cap);
         return mapa_cluster(xa_local + l * 16u, r);
     };
+    uint32_t rnb[10], rcw = 0;
+    float4 rinv = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+#pragma unroll
+    for (int q = 0; q < 10; q++) rnb[q] = xa_local + (uint32_t)cap * 16u;
     for (int l = threadIdx.x; l < n_own; l += kClThreads) {
         const int s = s_begin + l;
         s_xa[l] = xa[s];
         s_xb[l] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-        s_lb[l] = __ldg(lb4 + s); s_ub[l] = __ldg(ub4 + s); s_inv[l] = __ldg(inv4 + s);
-        s_code[l] = __ldg(code + s);
+        s_lb[l] = __ldg(lb4 + s); s_ub[l] = __ldg(ub4 + s);
         const int4 a = __ldg(nbA + s), b = __ldg(nbB + s);
         const int2 c = __ldg(nbC + s);
-        uint32_t* nb = s_nb + (size_t)l * 10;
-        nb[0] = slot_addr(a.x); nb[1] = slot_addr(a.y); nb[2] = slot_addr(a.z); nb[3] = slot_addr(a.w);
-        nb[4] = slot_addr(b.x); nb[5] = slot_addr(b.y); nb[6] = slot_addr(b.z); nb[7] = slot_addr(b.w);
-        nb[8] = slot_addr(c.x); nb[9] = slot_addr(c.y);
+        const uint32_t n[10] = {slot_addr(a.x), slot_addr(a.y), slot_addr(a.z), slot_addr(a.w), slot_addr(b.x),
+                                slot_addr(b.y), slot_addr(b.z), slot_addr(b.w), slot_addr(c.x), slot_addr(c.y)};
+        if (REGS) {
+            rinv = __ldg(inv4 + s); rcw = __ldg(code + s);
+#pragma unroll
+            for (int q = 0; q < 10; q++) rnb[q] = n[q];
+        } else {
+            s_inv[l] = __ldg(inv4 + s); s_code[l] = __ldg(code + s);
+#pragma unroll
+            for (int q = 0; q < 10; q++) s_nb[(size_t)l * 10 + q] = n[q];
+        }
     }
     if (threadIdx.x == 0) { s_xa[cap] = make_float4(0.0f, 0.0f, 0.0f, 0.0f); s_xb[cap] = make_float4(0.0f, 0.0f, 0.0f, 0.0f); }
     cluster_sync_all();
     uint32_t off = 0;                                                          // buffer the sweep reads: 0 = A, buf_off = B
     float dmax = 0.0f;
+    auto update = [&](int l, uint32_t c, const float4 iv, const uint32_t (&n)[10], float4* s_out, bool last) {
+        const float4 xc = ld_cluster4(xa_local + (uint32_t)l * 16u + off);
+        const float4 xm2 = ld_cluster4(n[0] + off), xm1 = ld_cluster4(n[1] + off), ym2 = ld_cluster4(n[2] + off), ym1 = ld_cluster4(n[3] + off);
+        const float4 zlo = ld_cluster4(n[4] + off), zhi = ld_cluster4(n[5] + off), yp1 = ld_cluster4(n[6] + off), yp2 = ld_cluster4(n[7] + off);
+        const float4 xp1 = ld_cluster4(n[8] + off), xp2 = ld_cluster4(n[9] + off);
+        const float4 lb = s_lb[l], ub = s_ub[l];
+        float4 r;
+        r.x = qp_voxel<1u << 0, 1u << 6, 1u << 10, 1u << 14, 1u << 18, 1u << 4, 1u << 1>(
+            c, xc.x, xm2.x, xm1.x, ym2.x, ym1.x, zlo.z, zlo.w, xc.y, xc.z, yp1.x, yp2.x, xp1.x, xp2.x, iv.x, lb.x, ub.x);
+        r.y = qp_voxel<1u << 1, 1u << 7, 1u << 11, 1u << 15, 1u << 19, 1u << 0, 1u << 2>(
+            c, xc.y, xm2.y, xm1.y, ym2.y, ym1.y, zlo.w, xc.x, xc.z, xc.w, yp1.y, yp2.y, xp1.y, xp2.y, iv.y, lb.y, ub.y);
+        r.z = qp_voxel<1u << 2, 1u << 8, 1u << 12, 1u << 16, 1u << 20, 1u << 1, 1u << 3>(
+            c, xc.z, xm2.z, xm1.z, ym2.z, ym1.z, xc.x, xc.y, xc.w, zhi.x, yp1.z, yp2.z, xp1.z, xp2.z, iv.z, lb.z, ub.z);
+        r.w = qp_voxel<1u << 3, 1u << 9, 1u << 13, 1u << 17, 1u << 21, 1u << 2, 1u << 5>(
+            c, xc.w, xm2.w, xm1.w, ym2.w, ym1.w, xc.y, xc.z, zhi.x, zhi.y, yp1.w, yp2.w, xp1.w, xp2.w, iv.w, lb.w, ub.w);
+        s_out[l] = r;
+        if (last) dmax = fmaxf(fmaxf(dmax, fmaxf(fabsf(r.x - xc.x), fabsf(r.y - xc.y))), fmaxf(fabsf(r.z - xc.z), fabsf(r.w - xc.w)));
+    };
     for (int it = 0; it < iters; it++) {
         float4* s_out = off ? s_xa : s_xb;
-        for (int l = threadIdx.x; l < n_own; l += kClThreads) {
-            const uint32_t* nb = s_nb + (size_t)l * 10;
-            const uint32_t c = s_code[l];
-            const float4 xc = ld_cluster4(xa_local + (uint32_t)l * 16u + off);
-            const float4 xm2 = ld_cluster4(nb[0] + off), xm1 = ld_cluster4(nb[1] + off), ym2 = ld_cluster4(nb[2] + off), ym1 = ld_cluster4(nb[3] + off);
-            const float4 zlo = ld_cluster4(nb[4] + off), zhi = ld_cluster4(nb[5] + off), yp1 = ld_cluster4(nb[6] + off), yp2 = ld_cluster4(nb[7] + off);
-            const float4 xp1 = ld_cluster4(nb[8] + off), xp2 = ld_cluster4(nb[9] + off);
-            const float4 lb = s_lb[l], ub = s_ub[l], inv = s_inv[l];
-            float4 r;
-            r.x = qp_voxel<1u << 0, 1u << 6, 1u << 10, 1u << 14, 1u << 18, 1u << 4, 1u << 1>(
-                c, xc.x, xm2.x, xm1.x, ym2.x, ym1.x, zlo.z, zlo.w, xc.y, xc.z, yp1.x, yp2.x, xp1.x, xp2.x, inv.x, lb.x, ub.x);
-            r.y = qp_voxel<1u << 1, 1u << 7, 1u << 11, 1u << 15, 1u << 19, 1u << 0, 1u << 2>(
-                c, xc.y, xm2.y, xm1.y, ym2.y, ym1.y, zlo.w, xc.x, xc.z, xc.w, yp1.y, yp2.y, xp1.y, xp2.y, inv.y, lb.y, ub.y);
-            r.z = qp_voxel<1u << 2, 1u << 8, 1u << 12, 1u << 16, 1u << 20, 1u << 1, 1u << 3>(
-                c, xc.z, xm2.z, xm1.z, ym2.z, ym1.z, xc.x, xc.y, xc.w, zhi.x, yp1.z, yp2.z, xp1.z, xp2.z, inv.z, lb.z, ub.z);
-            r.w = qp_voxel<1u << 3, 1u << 9, 1u << 13, 1u << 17, 1u << 21, 1u << 2, 1u << 5>(
-                c, xc.w, xm2.w, xm1.w, ym2.w, ym1.w, xc.y, xc.z, zhi.x, zhi.y, yp1.w, yp2.w, xp1.w, xp2.w, inv.w, lb.w, ub.w);
-            s_out[l] = r;
-            if (it == iters - 1)
-                dmax = fmaxf(fmaxf(dmax, fmaxf(fabsf(r.x - xc.x), fabsf(r.y - xc.y))), fmaxf(fabsf(r.z - xc.z), fabsf(r.w - xc.w)));
+        const bool last = it == iters - 1;
+        if (REGS) {
+            if ((int)threadIdx.x < n_own) update((int)threadIdx.x, rcw, rinv, rnb, s_out, last);
+        } else {
+            for (int l = threadIdx.x; l < n_own; l += kClThreads) {
+                uint32_t n[10];
+#pragma unroll
+                for (int q = 0; q < 10; q++) n[q] = s_nb[(size_t)l * 10 + q];
+                update(l, s_code[l], s_inv[l], n, s_out, last);
+            }
         }
         off ^= buf_off;
         // every CTA's stores of this sweep before anybody's loads of the next (and their loads of this sweep before the next
@@ -686,8 +708,7 @@ static int solve_strips_cluster(mrb_ctx* ctx, const StripBand& sb, int iters, fl
     if (e && atoi(e) == 0) return MRB_OK;
     // Sixteen SMs do all the arithmetic: measured on B200 1.4 us per sweep with one strip per thread (42^3), 1.9 us with two
     // (52^3), 3.0 us with three (64^3) against 2.7 us for k_qp_strips on all SMs -- so up to two strips per thread.
-    const int kClStripsMax = e && atoi(e) > 1 ? 16 * kClCapMax : 2 * 16 * kClThreads;
-    if (S > kClStripsMax) return MRB_OK;
+    if (S > 16 * kClCapMax) return MRB_OK;
     int cs = 1;
     while (cs < 16 && (cs * kClThreads < S || (S + cs - 1) / cs > kClCapMax)) cs *= 2;
     if (e && atoi(e) > 1) cs = atoi(e);                       // tuning knob: the cluster size
@@ -700,8 +721,10 @@ static int solve_strips_cluster(mrb_ctx* ctx, const StripBand& sb, int iters, fl
         // threads launch this kernel with different sizes)
         static bool attr_set[64] = {false};
         if (!attr_set[ctx->device & 63]) {
-            MRB_CUDA(cudaFuncSetAttribute(k_qp_cluster, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-            MRB_CUDA(cudaFuncSetAttribute(k_qp_cluster, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+            MRB_CUDA(cudaFuncSetAttribute(k_qp_cluster<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+            MRB_CUDA(cudaFuncSetAttribute(k_qp_cluster<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+            MRB_CUDA(cudaFuncSetAttribute(k_qp_cluster<true>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+            MRB_CUDA(cudaFuncSetAttribute(k_qp_cluster<false>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
             attr_set[ctx->device & 63] = true;
         }
     }
@@ -717,14 +740,15 @@ static int solve_strips_cluster(mrb_ctx* ctx, const StripBand& sb, int iters, fl
     cfg.attrs = at;
     cfg.numAttrs = 1;
     int nclusters = 0;
-    if (cudaOccupancyMaxActiveClusters(&nclusters, k_qp_cluster, &cfg) != cudaSuccess || nclusters < 1) {
+    auto kern = cap <= kClThreads ? k_qp_cluster<true> : k_qp_cluster<false>;
+    if (cudaOccupancyMaxActiveClusters(&nclusters, kern, &cfg) != cudaSuccess || nclusters < 1) {
         cudaGetLastError();
         return MRB_OK;                                        // this GPU cannot co-schedule such a cluster
     }
     unsigned* md = (unsigned*)(ctx->d_mail + 8);
     MRB_CUDA(cudaMemsetAsync(md, 0, sizeof(unsigned), ctx->stream));
     MRB_CUDA(cudaEventRecord(ctx->ev[6], ctx->stream));
-    MRB_CUDA(cudaLaunchKernelEx(&cfg, k_qp_cluster, (const uint32_t*)sb.code, (const float4*)sb.lb4, (const float4*)sb.ub4,
+    MRB_CUDA(cudaLaunchKernelEx(&cfg, kern, (const uint32_t*)sb.code, (const float4*)sb.lb4, (const float4*)sb.ub4,
                                 (const float4*)sb.inv4, (const int4*)sb.nbA, (const int4*)sb.nbB, (const int2*)sb.nbC, sb.xa, sb.xb, S,
                                 iters, cap, md));
     MRB_CUDA(cudaEventRecord(ctx->ev[7], ctx->stream));
