@@ -62,8 +62,42 @@ __global__ void k_quiet_borders(const float* __restrict__ vol, int nx, size_t pl
     if (any) *bad = 1;
 }
 
+// The batch's host mesh: malloc'd arrays that become mrb_mesh.verts / .faces as they are (no second copy), grown by doubling;
+// a chunk's result goes device -> pinned staging (full PCIe rate) -> these arrays.
+struct HostMesh {
+    float* v = nullptr;
+    int* f = nullptr;
+    size_t nv3 = 0, nf3 = 0, capv = 0, capf = 0;
+    int append(mrb_ctx* ctx, const float* dverts, int nv, const int* dfaces, int nf) {
+        const size_t av = (size_t)nv * 3, af = (size_t)nf * 3;
+        if (nv3 + av > capv) {
+            size_t c = std::max(nv3 + av, capv * 2);
+            float* p = (float*)realloc(v, sizeof(float) * (c ? c : 1));
+            if (!p) { set_error("mrb_reconstruct_batch: host allocation failed"); return MRB_ENOMEM; }
+            v = p; capv = c;
+        }
+        if (nf3 + af > capf) {
+            size_t c = std::max(nf3 + af, capf * 2);
+            int* p = (int*)realloc(f, sizeof(int) * (c ? c : 1));
+            if (!p) { set_error("mrb_reconstruct_batch: host allocation failed"); return MRB_ENOMEM; }
+            f = p; capf = c;
+        }
+        const size_t vb = (sizeof(float) * av + 255) / 256 * 256, fb = sizeof(int) * af;
+        char* pin = nullptr;
+        MRB_TRY(pinned_reserve(ctx, vb + fb + 256, &pin));
+        if (av) MRB_CUDA(cudaMemcpyAsync(pin, dverts, sizeof(float) * av, cudaMemcpyDeviceToHost, ctx->stream));
+        if (af) MRB_CUDA(cudaMemcpyAsync(pin + vb, dfaces, fb, cudaMemcpyDeviceToHost, ctx->stream));
+        MRB_TRY(sync(ctx));
+        if (av) memcpy(v + nv3, pin, sizeof(float) * av);
+        if (af) memcpy(f + nf3, pin + vb, fb);
+        nv3 += av; nf3 += af;
+        return MRB_OK;
+    }
+    void release() { free(v); free(f); v = nullptr; f = nullptr; }
+};
+
 static int batch_sequential(mrb_ctx* ctx, const float* volumes, Dims d, int ob0, int ob1, const mrb_options& o,
-                            std::vector<float>& verts, std::vector<int>& faces, int* vert_off, int* face_off) {
+                            HostMesh& hm, int* vert_off, int* face_off) {
     for (int ob = ob0; ob < ob1; ob++) {
         MRB_TRY(ctx->arena.reset());
         const float* dv = nullptr;
@@ -76,12 +110,7 @@ static int batch_sequential(mrb_ctx* ctx, const float* volumes, Dims d, int ob0,
         int* dfaces = nullptr;
         int nv = 0, nf = 0;
         MRB_TRY(dev_mcubes(ctx, F, d, o.isolevel, &dverts, &dfaces, &nv, &nf));
-        size_t v0 = verts.size(), f0 = faces.size();
-        verts.resize(v0 + (size_t)nv * 3);
-        faces.resize(f0 + (size_t)nf * 3);
-        if (nv) MRB_CUDA(cudaMemcpyAsync(verts.data() + v0, dverts, sizeof(float) * 3 * (size_t)nv, cudaMemcpyDeviceToHost, ctx->stream));
-        if (nf) MRB_CUDA(cudaMemcpyAsync(faces.data() + f0, dfaces, sizeof(int) * 3 * (size_t)nf, cudaMemcpyDeviceToHost, ctx->stream));
-        MRB_TRY(sync(ctx));
+        MRB_TRY(hm.append(ctx, dverts, nv, dfaces, nf));
         vert_off[ob + 1] = vert_off[ob] + nv;
         face_off[ob + 1] = face_off[ob] + nf;
     }
@@ -90,7 +119,7 @@ static int batch_sequential(mrb_ctx* ctx, const float* volumes, Dims d, int ob0,
 
 // One chunk of objects as one stacked grid.  *done = 0 if the chunk does not qualify (the caller runs it object by object).
 static int batch_stacked(mrb_ctx* ctx, const float* volumes, Dims d, int ob0, int ob1, const mrb_options& o,
-                         std::vector<float>& verts, std::vector<int>& faces, int* vert_off, int* face_off, int* done) {
+                         HostMesh& hm, int* vert_off, int* face_off, int* done) {
     *done = 0;
     const int n = ob1 - ob0, margin = o.band_size + 2;
     if (n < 2 || d.nx < 2 * margin + 1 || !(fabsf(o.isolevel) < (float)(o.band_size + 1))) return MRB_OK;
@@ -121,12 +150,7 @@ static int batch_stacked(mrb_ctx* ctx, const float* volumes, Dims d, int ob0, in
     int nv = 0, nf = 0;
     MRB_TRY(dev_mcubes(ctx, F, ds, o.isolevel, &dverts, &dfaces, &nv, &nf, &st));
     if (seam) return MRB_OK;
-    const size_t v0 = verts.size(), f0 = faces.size();
-    verts.resize(v0 + (size_t)nv * 3);
-    faces.resize(f0 + (size_t)nf * 3);
-    if (nv) MRB_CUDA(cudaMemcpyAsync(verts.data() + v0, dverts, sizeof(float) * 3 * (size_t)nv, cudaMemcpyDeviceToHost, ctx->stream));
-    if (nf) MRB_CUDA(cudaMemcpyAsync(faces.data() + f0, dfaces, sizeof(int) * 3 * (size_t)nf, cudaMemcpyDeviceToHost, ctx->stream));
-    MRB_TRY(sync(ctx));
+    MRB_TRY(hm.append(ctx, dverts, nv, dfaces, nf));
     for (int i = 0; i < n; i++) {
         vert_off[ob0 + i + 1] = vert_off[ob0] + voff[(size_t)i + 1];
         face_off[ob0 + i + 1] = face_off[ob0] + foff[(size_t)i + 1];
@@ -229,28 +253,30 @@ int mrb_reconstruct_batch(mrb_ctx* ctx, const float* volumes, const int dims[3],
     memset(out, 0, sizeof(*out));
     Dims d = mkdims(dims);
     MRB_REQUIRE(d.count() <= (size_t)0x7fffffff, "grid too large");
-    std::vector<float> verts;
-    std::vector<int> faces;
+    HostMesh hm;
     vert_off[0] = 0; face_off[0] = 0;
-    // chunks of at most 2^28 voxels (1900 objects of 52^3): bounds the scratch and keeps every index in 31 bits
+    // Chunks of at most 2^28 voxels (1900 objects of 52^3; MRB_BATCH_CHUNK_LOG2 = 20..28 overrides): bounds the scratch and keeps
+    // every index in 31 bits.  Smaller chunks (whose stage-3 working set would stay in L2) were measured and are no faster: 1024 x
+    // 52^3 takes 153 ms in one chunk, 163 ms in 2^24-voxel chunks, 240 ms in 2^22-voxel chunks (per-chunk host round trips).
     const bool stack = !getenv("MRB_BATCH_SEQUENTIAL");
-    size_t per_chunk = ((size_t)1 << 28) / (d.count() ? d.count() : 1);
+    int chunk_log2 = 28;
+    if (const char* e = getenv("MRB_BATCH_CHUNK_LOG2")) { chunk_log2 = atoi(e); if (chunk_log2 < 20) chunk_log2 = 20; if (chunk_log2 > 28) chunk_log2 = 28; }
+    size_t per_chunk = ((size_t)1 << chunk_log2) / (d.count() ? d.count() : 1);
     if (per_chunk < 1) per_chunk = 1;
     for (int ob0 = 0; ob0 < nobj;) {
         const int ob1 = (int)std::min<size_t>((size_t)nobj, (size_t)ob0 + per_chunk);
-        int done = 0;
-        if (stack) MRB_TRY(batch_stacked(ctx, volumes, d, ob0, ob1, o, verts, faces, vert_off, face_off, &done));
-        if (!done) MRB_TRY(batch_sequential(ctx, volumes, d, ob0, ob1, o, verts, faces, vert_off, face_off));
+        int done = 0, rc = MRB_OK;
+        if (stack) rc = batch_stacked(ctx, volumes, d, ob0, ob1, o, hm, vert_off, face_off, &done);
+        if (rc == MRB_OK && !done) rc = batch_sequential(ctx, volumes, d, ob0, ob1, o, hm, vert_off, face_off);
+        if (rc != MRB_OK) { hm.release(); return rc; }
         ob0 = ob1;
     }
-    out->nverts = (int)(verts.size() / 3);
-    out->nfaces = (int)(faces.size() / 3);
+    out->nverts = (int)(hm.nv3 / 3);
+    out->nfaces = (int)(hm.nf3 / 3);
     out->on_device = 0;
-    out->verts = (float*)malloc(sizeof(float) * (verts.size() ? verts.size() : 1));
-    out->faces = (int*)malloc(sizeof(int) * (faces.size() ? faces.size() : 1));
+    out->verts = hm.v ? hm.v : (float*)malloc(sizeof(float));
+    out->faces = hm.f ? hm.f : (int*)malloc(sizeof(int));
     if (!out->verts || !out->faces) { set_error("mrb_reconstruct_batch: host malloc failed"); return MRB_ENOMEM; }
-    if (!verts.empty()) memcpy(out->verts, verts.data(), sizeof(float) * verts.size());
-    if (!faces.empty()) memcpy(out->faces, faces.data(), sizeof(int) * faces.size());
     return MRB_OK;
 }
 
