@@ -388,10 +388,33 @@ def _batch(self, volumes, band_size=4, iters=500, isolevel=0.0):
     voff = (C.c_int * (nobj + 1))()
     foff = (C.c_int * (nobj + 1))()
     self._check(self.lib.mrb_reconstruct_batch(self.h, pv, self._dims(shape[1:]), nobj, C.byref(opt), C.byref(m), voff, foff))
-    verts = np.ctypeslib.as_array(m.verts, shape=(max(m.nverts, 1), 3))[:m.nverts].copy()
-    faces = np.ctypeslib.as_array(m.faces, shape=(max(m.nfaces, 1), 3))[:m.nfaces].copy()
-    self.lib.mrb_mesh_free(C.byref(m))
+    # No copy: the per-object arrays are views of the library's malloc'd result, which is freed when the last view dies
+    # (copying 90 MB of meshes of a 1024-object batch cost 25 ms of a 115 ms call).
+    owner = _MeshOwner(self.lib, m)
+    verts = _view(m.verts, C.c_float, m.nverts * 3, np.float32, owner).reshape(-1, 3)
+    faces = _view(m.faces, C.c_int, m.nfaces * 3, np.int32, owner).reshape(-1, 3)
     return [(verts[voff[o]:voff[o + 1]], faces[foff[o]:foff[o + 1]]) for o in range(nobj)]
+
+
+class _MeshOwner:
+    """Keeps an mrb_mesh with malloc'd arrays alive for the numpy views made of it."""
+
+    def __init__(self, lib, mesh):
+        self.lib, self.mesh = lib, mesh
+
+    def __del__(self):
+        try:
+            self.lib.mrb_mesh_free(C.byref(self.mesh))
+        except Exception:
+            pass
+
+
+def _view(ptr, ctype, count, dtype, owner):
+    if count == 0:
+        return np.empty(0, dtype)
+    buf = (ctype * count).from_address(C.addressof(ptr.contents))
+    buf._owner = owner                      # the numpy array keeps `buf` alive, `buf` keeps the owner
+    return np.frombuffer(buf, dtype=dtype)
 
 
 Context.reconstruct_batch = _batch

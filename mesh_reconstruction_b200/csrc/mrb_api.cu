@@ -10,6 +10,7 @@
 #include <string.h>
 #include <algorithm>
 #include <string>
+#include <chrono>
 #include <thread>
 #include <vector>
 
@@ -62,22 +63,40 @@ __global__ void k_quiet_borders(const float* __restrict__ vol, int nx, size_t pl
     if (any) *bad = 1;
 }
 
+// memcpy into freshly malloc'd memory is dominated by first-touch page faults (measured: 90 MB in 38 ms, 2.4 GB/s); several
+// threads fault their own slices in parallel.
+static void parallel_memcpy(void* dst, const void* src, size_t bytes) {
+    const size_t kSlice = (size_t)4 << 20;
+    unsigned hw = std::thread::hardware_concurrency();
+    size_t nth = std::min<size_t>(std::min<size_t>(hw ? hw : 4, 8), bytes / kSlice);
+    if (nth < 2) { memcpy(dst, src, bytes); return; }
+    std::vector<std::thread> th;
+    for (size_t t = 0; t < nth; t++) {
+        const size_t a = bytes * t / nth / 64 * 64, b = t + 1 == nth ? bytes : bytes * (t + 1) / nth / 64 * 64;
+        th.emplace_back([=] { memcpy((char*)dst + a, (const char*)src + a, b - a); });
+    }
+    for (auto& t : th) t.join();
+}
+
 // The batch's host mesh: malloc'd arrays that become mrb_mesh.verts / .faces as they are (no second copy), grown by doubling;
 // a chunk's result goes device -> pinned staging (full PCIe rate) -> these arrays.
 struct HostMesh {
     float* v = nullptr;
     int* f = nullptr;
     size_t nv3 = 0, nf3 = 0, capv = 0, capf = 0;
+    double grow_hint = 1.0;          // after the first chunk: (objects of the batch) / (objects of that chunk), so that one allocation holds all
     int append(mrb_ctx* ctx, const float* dverts, int nv, const int* dfaces, int nf) {
         const size_t av = (size_t)nv * 3, af = (size_t)nf * 3;
         if (nv3 + av > capv) {
             size_t c = std::max(nv3 + av, capv * 2);
+            if (capv == 0) c = std::max(c, (size_t)((double)av * grow_hint * 1.08) + 1024);
             float* p = (float*)realloc(v, sizeof(float) * (c ? c : 1));
             if (!p) { set_error("mrb_reconstruct_batch: host allocation failed"); return MRB_ENOMEM; }
             v = p; capv = c;
         }
         if (nf3 + af > capf) {
             size_t c = std::max(nf3 + af, capf * 2);
+            if (capf == 0) c = std::max(c, (size_t)((double)af * grow_hint * 1.08) + 1024);
             int* p = (int*)realloc(f, sizeof(int) * (c ? c : 1));
             if (!p) { set_error("mrb_reconstruct_batch: host allocation failed"); return MRB_ENOMEM; }
             f = p; capf = c;
@@ -88,8 +107,8 @@ struct HostMesh {
         if (av) MRB_CUDA(cudaMemcpyAsync(pin, dverts, sizeof(float) * av, cudaMemcpyDeviceToHost, ctx->stream));
         if (af) MRB_CUDA(cudaMemcpyAsync(pin + vb, dfaces, fb, cudaMemcpyDeviceToHost, ctx->stream));
         MRB_TRY(sync(ctx));
-        if (av) memcpy(v + nv3, pin, sizeof(float) * av);
-        if (af) memcpy(f + nf3, pin + vb, fb);
+        if (av) parallel_memcpy(v + nv3, pin, sizeof(float) * av);
+        if (af) parallel_memcpy(f + nf3, pin + vb, fb);
         nv3 += av; nf3 += af;
         return MRB_OK;
     }
@@ -121,6 +140,7 @@ static int batch_sequential(mrb_ctx* ctx, const float* volumes, Dims d, int ob0,
 static int batch_stacked(mrb_ctx* ctx, const float* volumes, Dims d, int ob0, int ob1, const mrb_options& o,
                          HostMesh& hm, int* vert_off, int* face_off, int* done) {
     *done = 0;
+    const double t_begin = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
     const int n = ob1 - ob0, margin = o.band_size + 2;
     if (n < 2 || d.nx < 2 * margin + 1 || !(fabsf(o.isolevel) < (float)(o.band_size + 1))) return MRB_OK;
     // hash keys of different objects must not collide: shift by a power of two above the largest key of one object
@@ -150,7 +170,12 @@ static int batch_stacked(mrb_ctx* ctx, const float* volumes, Dims d, int ob0, in
     int nv = 0, nf = 0;
     MRB_TRY(dev_mcubes(ctx, F, ds, o.isolevel, &dverts, &dfaces, &nv, &nf, &st));
     if (seam) return MRB_OK;
+    const bool verbose = getenv("MRB_BATCH_VERBOSE") != nullptr;
+    auto now = [] { return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    double t_gpu = 0;
+    if (verbose) { cudaStreamSynchronize(ctx->stream); t_gpu = now(); }
     MRB_TRY(hm.append(ctx, dverts, nv, dfaces, nf));
+    if (verbose) fprintf(stderr, "[mrb] batch chunk of %d objects: stages 1-4 %.2f ms, mesh to host %.2f ms (%d faces)\n", n, t_gpu - t_begin, now() - t_gpu, nf);
     for (int i = 0; i < n; i++) {
         vert_off[ob0 + i + 1] = vert_off[ob0] + voff[(size_t)i + 1];
         face_off[ob0 + i + 1] = face_off[ob0] + foff[(size_t)i + 1];
@@ -256,8 +281,8 @@ int mrb_reconstruct_batch(mrb_ctx* ctx, const float* volumes, const int dims[3],
     HostMesh hm;
     vert_off[0] = 0; face_off[0] = 0;
     // Chunks of at most 2^28 voxels (1900 objects of 52^3; MRB_BATCH_CHUNK_LOG2 = 20..28 overrides): bounds the scratch and keeps
-    // every index in 31 bits.  Smaller chunks (whose stage-3 working set would stay in L2) were measured and are no faster: 1024 x
-    // 52^3 takes 153 ms in one chunk, 163 ms in 2^24-voxel chunks, 240 ms in 2^22-voxel chunks (per-chunk host round trips).
+    // every index in 31 bits.  Chunks of 2^24 voxels keep the stage-3 working set in L2 (1024 x 52^3: stages 1-4 take 9 x 4.85 = 44
+    // ms instead of 58 ms) but pay nine times the per-chunk round trips: 81 ms against 78 ms for the whole call, so one chunk it is.
     const bool stack = !getenv("MRB_BATCH_SEQUENTIAL");
     int chunk_log2 = 28;
     if (const char* e = getenv("MRB_BATCH_CHUNK_LOG2")) { chunk_log2 = atoi(e); if (chunk_log2 < 20) chunk_log2 = 20; if (chunk_log2 > 28) chunk_log2 = 28; }
@@ -265,6 +290,7 @@ int mrb_reconstruct_batch(mrb_ctx* ctx, const float* volumes, const int dims[3],
     if (per_chunk < 1) per_chunk = 1;
     for (int ob0 = 0; ob0 < nobj;) {
         const int ob1 = (int)std::min<size_t>((size_t)nobj, (size_t)ob0 + per_chunk);
+        if (ob0 == 0) hm.grow_hint = (double)nobj / (double)(ob1 - ob0);
         int done = 0, rc = MRB_OK;
         if (stack) rc = batch_stacked(ctx, volumes, d, ob0, ob1, o, hm, vert_off, face_off, &done);
         if (rc == MRB_OK && !done) rc = batch_sequential(ctx, volumes, d, ob0, ob1, o, hm, vert_off, face_off);
