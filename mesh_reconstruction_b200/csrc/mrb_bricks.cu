@@ -383,10 +383,10 @@ __device__ __forceinline__ float brick_voxel_x(const BrickRegs& r, uint32_t pw, 
     t = t * 0.5f;
     // clamp to [lb, ub] from the signed margin (see BrickConstsX); differs from "if (t < lb) t = lb; if (t > ub) t = ub"
     // at most in the sign of a zero, as in brick_voxel
+    // [lb, ub] = volume == 0 ? [-1000, sm] : [sm, 1000]; min(max(t, lb), ub) is one three-input FMNMX3 on sm_100
     const bool outside = __float_as_int(sm) < 0;
-    const float far = __int_as_float((__float_as_int(sm) & 0x80000000) ^ 0x447a0000);      // volume==0 ? -1000 : 1000
-    const float u = outside ? fminf(t, sm) : fmaxf(t, sm);
-    return outside ? fmaxf(u, far) : fminf(u, far);
+    const float lb = outside ? -1000.0f : sm, ub = outside ? sm : 1000.0f;
+    return fminf(fmaxf(t, lb), ub);
 }
 
 template <int K>
