@@ -338,7 +338,9 @@ __device__ __forceinline__ BrickConstsX brick_expand(const uint2 c, const uint4 
             iv[v] = s_inv[(field >> 8) & 31u];
             // band voxel of a binary volume: exactly one of bit 13 (volume == 0) / bit 14 (volume == 1)
             sm[v] = (field & (1u << 15)) ? ((field & (1u << 13)) ? -m : m) : 0.0f;
-            pw[k] |= brick_pred_byte(k >> 1, k & 1, j, c.x, c.y) << (8 * j);
+            // bit 7: band voxel of the outside (volume == 0): its bounds are [-1000, sm] instead of [sm, 1000]
+            const uint32_t outside = ((field >> 15) & (field >> 13) & 1u) << 7;
+            pw[k] |= (brick_pred_byte(k >> 1, k & 1, j, c.x, c.y) | outside) << (8 * j);
         }
         x.sm[k] = make_float4(sm[k * 4], sm[k * 4 + 1], sm[k * 4 + 2], sm[k * 4 + 3]);
         x.inv[k] = make_float4(iv[k * 4], iv[k * 4 + 1], iv[k * 4 + 2], iv[k * 4 + 3]);
@@ -384,7 +386,7 @@ __device__ __forceinline__ float brick_voxel_x(const BrickRegs& r, uint32_t pw, 
     // clamp to [lb, ub] from the signed margin (see BrickConstsX); differs from "if (t < lb) t = lb; if (t > ub) t = ub"
     // at most in the sign of a zero, as in brick_voxel
     // [lb, ub] = volume == 0 ? [-1000, sm] : [sm, 1000]; min(max(t, lb), ub) is one three-input FMNMX3 on sm_100
-    const bool outside = __float_as_int(sm) < 0;
+    const bool outside = pb & 128u;
     const float lb = outside ? -1000.0f : sm, ub = outside ? sm : 1000.0f;
     return fminf(fmaxf(t, lb), ub);
 }
